@@ -1,0 +1,148 @@
+/*
+ * matfact_b200.h -- C ABI of the B200 factorization path (libmatfact_b200.so).
+ *
+ * The reference (vladstojna/recommender-system) has no plugin or FFI layer; the
+ * seam this library replaces is two consecutive calls in its main():
+ *
+ *     matrix_factorization(B, L, R, entries, non_zero, iters, alpha);   matFact.c:124 (def. :29-59)
+ *     print_output(B, entries);                                         matFact.c:127 (def. :10-27)
+ *
+ * together with the three mat2d routines those call (mat2d_copy mat2d.c:34-36,
+ * mat2d_dot_product :126-139, mat2d_prod :100-113).  Everything here is plain
+ * C: pointers, ints, doubles.  All matrices are row-major doubles exactly as
+ * the reference's mat2d (mat2d.h:6-11): L is users x features, R is
+ * items x features (the reference keeps R transposed, matFact.c:117-120).
+ * B (users x items) is never materialised.
+ *
+ * Every function returns 0 on success or a negative MFGPU_E* code;
+ * mfgpu_last_error() gives the message (thread local).  There is no CPU
+ * fallback: without a usable sm_100 device every compute entry fails with
+ * MFGPU_ENODEV.  The reference reports errors by die() -> exit(-1)
+ * (util.c:7-10); the host program (host/matFact.c) maps non-zero returns to the
+ * same behaviour.
+ */
+#ifndef MATFACT_B200_H
+#define MATFACT_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MFGPU_OK        0
+#define MFGPU_EINVAL   -1   /* bad argument (negative size, entry out of range, ...) */
+#define MFGPU_ENOMEM   -2   /* host or device allocation failed                      */
+#define MFGPU_ENODEV   -3   /* no CUDA device / not an sm_100 device                 */
+#define MFGPU_ECUDA    -4   /* a CUDA runtime call failed                            */
+#define MFGPU_ECOMM    -5   /* a collective (NCCL) call failed                       */
+
+/* Same layout as the reference's non_zero_entry (datatypes.h:10-15;
+ * deliverables/serial/matFact.c:148-153): 16 bytes, no padding. */
+typedef struct {
+	int row;      /* user, 0-based  */
+	int col;      /* item, 0-based  */
+	double value; /* rating a_ij    */
+} mfgpu_entry;
+
+typedef struct mfgpu_plan mfgpu_plan;   /* device-resident problem           */
+typedef struct mfgpu_comm mfgpu_comm;   /* one rank of a multi-process group */
+
+/* ---- library state --------------------------------------------------------- */
+
+/* Number of usable devices (compute capability 10.x); 0 if none. */
+int mfgpu_device_count(void);
+/* Message of the last failure on the calling thread ("" if none). */
+const char *mfgpu_last_error(void);
+/* Library version string. */
+const char *mfgpu_version(void);
+
+/* ---- one-shot entries with HOST buffers (what the reference's main() calls) -- */
+
+/* Replaces matrix_factorization (matFact.c:29-53, without the trailing
+ * mat2d_prod): runs `iters` iterations over `entries` (file order; the
+ * accumulation order of the reference is preserved for any order) and
+ * overwrites L and R in place.  ngpus <= 0 means "all visible devices";
+ * ngpus == 1 reproduces the reference's doubles bit for bit. */
+int mfgpu_factorize(int users, int items, int features, int nnz,
+                    const mfgpu_entry *entries, int iters, double alpha,
+                    double *L, double *R, int ngpus);
+
+/* Replaces mat2d_prod + print_output (matFact.c:55,127; mat2d.c:100-113;
+ * matFact.c:10-27): best[i] = the item the reference would print for user i,
+ * or -1 where it prints nothing (every item rated). */
+int mfgpu_recommend(int users, int items, int features, int nnz,
+                    const mfgpu_entry *entries,
+                    const double *L, const double *R, int *best, int ngpus);
+
+/* Both of the above with L and R staying on the device in between.
+ * L, R are in/out; best is out. */
+int mfgpu_run(int users, int items, int features, int nnz,
+              const mfgpu_entry *entries, int iters, double alpha,
+              double *L, double *R, int *best, int ngpus);
+
+/* ---- plan API: keep the problem resident in HBM across calls ---------------- */
+
+/* Builds the by-user / by-item groupings of `entries`, uploads them, and
+ * allocates the factor buffers on `ngpus` devices of this process (users are
+ * cut into contiguous, nonzero-balanced ranges, one per device). */
+int mfgpu_plan_create(mfgpu_plan **out, int users, int items, int features, int nnz,
+                      const mfgpu_entry *entries, double alpha, int ngpus);
+/* Same for ONE rank of a multi-process group (one process per GPU): this
+ * process owns the users of rank comm->rank and a replica of R. */
+int mfgpu_plan_create_rank(mfgpu_plan **out, int users, int items, int features, int nnz,
+                           const mfgpu_entry *entries, double alpha, mfgpu_comm *comm);
+void mfgpu_plan_destroy(mfgpu_plan *plan);
+
+/* Host -> device copy of the full L (users x features) and R (items x features). */
+int mfgpu_plan_set_factors(mfgpu_plan *plan, const double *L, const double *R);
+/* Device -> host.  In rank mode only the rows of L owned by this rank are
+ * written (the others are left untouched); R is complete on every rank. */
+int mfgpu_plan_get_factors(mfgpu_plan *plan, double *L, double *R);
+/* Enqueue `iters` iterations; returns once they are enqueued. */
+int mfgpu_plan_iterate(mfgpu_plan *plan, int iters);
+/* Wait for everything enqueued on the plan. */
+int mfgpu_plan_sync(mfgpu_plan *plan);
+/* Device time (CUDA events on the plan's stream) of the last mfgpu_plan_iterate
+ * call, max over the plan's devices.  Implies a sync. */
+int mfgpu_plan_last_loop_ms(mfgpu_plan *plan, float *ms);
+/* Masked arg-max on the resident factors; best has `users` ints.  In rank mode
+ * only the entries of the rank's users are written. */
+int mfgpu_plan_recommend(mfgpu_plan *plan, int *best);
+/* Device time of the last mfgpu_plan_recommend call. */
+int mfgpu_plan_last_recommend_ms(mfgpu_plan *plan, float *ms);
+/* [lo, hi) of the users owned by local shard `shard` (0 in rank mode). */
+int mfgpu_plan_user_range(mfgpu_plan *plan, int shard, int *lo, int *hi);
+/* Kernel launches issued by this plan so far (for bench.py's gpu_launches). */
+long long mfgpu_plan_launch_count(mfgpu_plan *plan);
+/* Algorithmic bytes of ONE iteration, SURVEY.md section 8(d):
+ * 16*F*(U_t + I_t) + 12*nnz, with U_t / I_t the users / items having >=1 nonzero. */
+long long mfgpu_plan_bytes_per_iter(mfgpu_plan *plan);
+/* Tuning knob for experiments: name = "l_warps", "r_warps", "graph" ... */
+int mfgpu_plan_set_option(mfgpu_plan *plan, const char *name, int value);
+
+/* ---- multi-process groups (one process per GPU, e.g. under torchrun) -------- */
+
+#define MFGPU_UID_BYTES 128
+/* Rank 0 creates the id and ships it to the other ranks by any side channel
+ * (bench.py broadcasts it with torch.distributed). */
+int mfgpu_comm_unique_id(unsigned char uid[MFGPU_UID_BYTES]);
+int mfgpu_comm_create(mfgpu_comm **out, int nranks, int rank,
+                      const unsigned char uid[MFGPU_UID_BYTES], int device);
+void mfgpu_comm_destroy(mfgpu_comm *comm);
+
+/* ---- host-side helpers exported for tests and tools (no GPU needed) --------- */
+
+/* Contiguous user ranges with balanced nonzero counts; cut has nshards+1 ints. */
+int mfgpu_split_users(int users, int nnz, const mfgpu_entry *entries, int nshards, int *cut);
+/* The reference's initialisation, kept on the host: srandom(0), L then R_init
+ * drawn as (double)random()/RAND_MAX/features, R stored transposed
+ * (mat2d.c:61-72,115-124; matFact.c:113-120). */
+void mfgpu_random_fill_LR(int users, int items, int features, double *L, double *R);
+/* Rated-item mask of print_output for user range [0, users): fills
+ * mask_count[i] and first_free[i]; returns total matched entries or <0. */
+int mfgpu_mask_stats(int users, int items, int nnz, const mfgpu_entry *entries,
+                     int *mask_count, int *first_free);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,96 @@
+"""ctypes binding of the CPU oracle -- TEST INFRASTRUCTURE ONLY.
+
+May be imported from tests/, __graft_entry__.smoke() and bench.py's
+cpu_baseline / --impl reference legs, never from the product package.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB = os.path.join(HERE, "_build", "liboracle.so")
+CLI = os.path.join(HERE, "_build", "matfact_oracle")
+REF_DIR = os.path.join(HERE, "_ref")
+
+_lib = None
+
+
+def build(ref: bool = True) -> None:
+    """Compile the restatement (and oracle/_ref when /root/reference exists)."""
+    targets = ["all"] + (["ref"] if ref else [])
+    subprocess.run(["make", "-C", HERE] + targets, check=True,
+                   stdout=subprocess.DEVNULL, stderr=subprocess.PIPE)
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB):
+            build(ref=False)
+        L = ctypes.CDLL(LIB)
+        dp = ctypes.POINTER(ctypes.c_double)
+        ip = ctypes.POINTER(ctypes.c_int)
+        vp = ctypes.c_void_p
+        i = ctypes.c_int
+        L.oracle_init_LR.argtypes = [i, i, i, dp, dp]
+        L.oracle_init_LR.restype = None
+        L.oracle_factorize.argtypes = [i, i, i, i, vp, i, ctypes.c_double, dp, dp]
+        L.oracle_factorize.restype = i
+        L.oracle_factorize_sharded.argtypes = [i, i, i, i, vp, i, ctypes.c_double, dp, dp, i, ip]
+        L.oracle_factorize_sharded.restype = i
+        L.oracle_recommend.argtypes = [i, i, i, i, vp, dp, dp, ip]
+        L.oracle_recommend.restype = i
+        _lib = L
+    return _lib
+
+
+def _dp(a):
+    return a.ctypes.data_as(ctypes.POINTER(ctypes.c_double))
+
+
+def init_LR(users, items, features):
+    L = np.empty((users, features), dtype=np.float64)
+    R = np.empty((items, features), dtype=np.float64)
+    lib().oracle_init_LR(users, items, features, _dp(L), _dp(R))
+    return L, R
+
+
+def factorize(users, items, features, entries, iters, alpha, L, R):
+    entries = np.ascontiguousarray(entries)
+    assert entries.dtype.itemsize == 16 and L.flags.c_contiguous and R.flags.c_contiguous
+    rc = lib().oracle_factorize(users, items, features, len(entries), entries.ctypes.data,
+                                iters, alpha, _dp(L), _dp(R))
+    if rc:
+        raise MemoryError("oracle_factorize")
+
+
+def factorize_sharded(users, items, features, entries, iters, alpha, L, R, shard_lo):
+    entries = np.ascontiguousarray(entries)
+    lo = np.ascontiguousarray(shard_lo, dtype=np.int32)
+    rc = lib().oracle_factorize_sharded(users, items, features, len(entries), entries.ctypes.data,
+                                        iters, alpha, _dp(L), _dp(R), len(lo) - 1,
+                                        lo.ctypes.data_as(ctypes.POINTER(ctypes.c_int)))
+    if rc:
+        raise MemoryError("oracle_factorize_sharded")
+
+
+def recommend(users, items, features, entries, L, R):
+    entries = np.ascontiguousarray(entries)
+    best = np.empty(users, dtype=np.int32)
+    rc = lib().oracle_recommend(users, items, features, len(entries), entries.ctypes.data,
+                                _dp(L), _dp(R), best.ctypes.data_as(ctypes.POINTER(ctypes.c_int)))
+    if rc:
+        raise MemoryError("oracle_recommend")
+    return best
+
+
+def run_instance(inst):
+    """Whole reference program on an Instance: returns (L, R, best)."""
+    L, R = init_LR(inst.users, inst.items, inst.features)
+    factorize(inst.users, inst.items, inst.features, inst.entries, inst.iters, inst.alpha, L, R)
+    best = recommend(inst.users, inst.items, inst.features, inst.entries, L, R)
+    return L, R, best

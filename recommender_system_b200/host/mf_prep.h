@@ -1,0 +1,65 @@
+/*
+ * host/mf_prep.h -- host-side (plain C) preparation of the sparse pattern.
+ *
+ * The reference walks A as a COO list in file order (matFact.c:41-53).  The
+ * device kernels need the same nonzeros grouped by user (for the L update) and
+ * by item (for the R update) WITHOUT changing the order in which the updates
+ * of one L row / one R row are accumulated, because that order fixes the bits
+ * of the result.  Both groupings are therefore stable with respect to the file
+ * order.  Nothing in this file touches the GPU.
+ */
+#ifndef MF_PREP_H
+#define MF_PREP_H
+
+#include "matfact_b200.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct {
+	int users, items, nnz;      /* nnz = nonzeros of THIS shard                      */
+	int user_lo, user_hi;       /* users owned by this shard: [user_lo, user_hi)     */
+
+	/* by-user grouping ("CSR"); rows are the users with >=1 nonzero, stored
+	 * longest row first so that the longest serial chains start first */
+	int n_rows;
+	int *row_id;                /* [n_rows]   user index of stored row r             */
+	int *row_ptr;               /* [n_rows+1] start of row r in col_idx/val          */
+	int *col_idx;               /* [nnz]      item of each nonzero (file order in row) */
+	double *val;                /* [nnz]      rating a_ij                            */
+
+	/* by-item grouping ("CSC"), longest column first */
+	int n_cols;
+	int *col_id;                /* [n_cols]   item index of stored column c          */
+	int *col_ptr;               /* [n_cols+1]                                        */
+	int *row_idx;               /* [nnz]      user of each nonzero (file order in column) */
+	int *perm;                  /* [nnz]      by-item position -> by-user position   */
+
+	/* rated-item mask of print_output (matFact.c:14-22), users of this shard */
+	int *mask_ptr;              /* [users+1]  (only [user_lo..user_hi] meaningful)   */
+	int *mask_col;              /* [mask_ptr[users]] ascending items per user        */
+	int *first_free;            /* [users]    first item the cursor does not skip, -1 if none */
+
+	int max_row_len, max_col_len;
+} mf_pattern;
+
+/* Build the pattern of the entries whose row lies in [user_lo, user_hi).
+ * `entries` is the full list in file order.  Returns 0 or an MFGPU_E* code. */
+int mf_pattern_build(mf_pattern *p, int users, int items, int nnz,
+                     const mfgpu_entry *entries, int user_lo, int user_hi);
+void mf_pattern_free(mf_pattern *p);
+
+/* Contiguous user ranges with balanced nonzero counts (SURVEY.md section 8e;
+ * the reference's equal-count split is mpiutil.h:8-13 BLOCK_LOW).
+ * cut[] has nshards+1 elements, cut[0]=0, cut[nshards]=users. */
+int mf_split_users(int users, int nnz, const mfgpu_entry *entries, int nshards, int *cut);
+
+/* Items with at least one nonzero anywhere, ascending; returns the count.
+ * item_slot[j] = position of item j in that list or -1. */
+int mf_touched_items(int items, int nnz, const mfgpu_entry *entries, int *item_slot);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
