@@ -1,0 +1,104 @@
+/*
+ * csrc/mf_internal.h -- private state behind the opaque handles of
+ * include/matfact_b200.h.  Not part of the ABI.
+ */
+#pragma once
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdio.h>
+
+#include "matfact_b200.h"
+#include "../host/mf_prep.h"
+#include "mf_types.h"
+
+#define MF_MAX_SHARDS 16
+
+/* ---- NCCL, bound at run time (only rank mode needs it) ---------------------- */
+typedef struct ncclComm *mf_ncclComm_t;
+typedef struct { char internal[128]; } mf_ncclUniqueId;
+struct mf_nccl_api {
+	void *handle;
+	int (*GetUniqueId)(mf_ncclUniqueId *);
+	int (*CommInitRank)(mf_ncclComm_t *, int, mf_ncclUniqueId, int);
+	int (*CommDestroy)(mf_ncclComm_t);
+	int (*AllReduce)(const void *, void *, size_t, int, int, mf_ncclComm_t, cudaStream_t);
+	int (*AllGather)(const void *, void *, size_t, int, mf_ncclComm_t, cudaStream_t);
+	const char *(*GetErrorString)(int);
+};
+
+struct mfgpu_comm {
+	int nranks, rank, device;
+	mf_ncclComm_t nccl;
+};
+
+struct mf_shard {
+	int dev;
+	cudaStream_t st;
+	mf_pattern pat;
+	int user_lo, user_hi;
+	/* sparse pattern on the device */
+	int *d_row_id, *d_row_ptr, *d_col_idx, *d_epos, *d_col_id, *d_col_ptr, *d_row_idx;
+	double *d_val, *d_e_csc, *d_e_csr;
+	int *d_mask_ptr, *d_mask_col, *d_first_free;
+	int *d_item_slot, *d_touched_item;       /* N-shard only */
+	/* factors, double buffered; L holds the shard's users only */
+	double *L[2], *R[2];
+	double *G[2];                            /* N-shard only: partial R gradient */
+	mf::LoopArgs la;
+	int warps;                               /* 8 or 1: k_update_L template      */
+	int k1_blocks, k2_blocks;
+	size_t k1_smem;
+	cudaGraphExec_t gexec[2];                /* by starting parity                */
+	cudaEvent_t ev0, ev1, ev_g[2];
+	/* arg-max scratch */
+	double *part_v;
+	int *part_j, *nan_first, *d_best;
+	int am_splits;
+};
+
+struct mfgpu_plan {
+	int users, items, F, ld, nnz;
+	double alpha;
+	int nshards;
+	int cut[MF_MAX_SHARDS + 1];
+	mf_shard sh[MF_MAX_SHARDS];
+	mfgpu_comm *comm;            /* rank mode, else NULL   */
+	int n_touched;               /* items with >=1 nonzero */
+	int cur;                     /* buffer holding the current factors */
+	int have_factors;
+	long long launches;
+	float loop_ms, rec_ms;
+	/* options */
+	int opt_graph, opt_graph_iters, opt_long_row, opt_ch;
+};
+
+/* ---- shared helpers (defined in mf_capi.cu) ----------------------------------- */
+int mf_fail(int code, const char *fmt, ...);
+int mf_load_nccl(void);
+int mf_usable_devices(int *ids, int cap);
+int mf_configure_shard(mfgpu_plan *pl, mf_shard *s);      /* mf_plan.cu */
+int mf_k1_prepare(int warps, size_t smem);                 /* mf_iter.cu: kernels live in that TU only */
+extern mf_nccl_api g_nccl;
+
+#define CK(call)                                                                        \
+	do {                                                                                \
+		cudaError_t e_ = (call);                                                        \
+		if (e_ != cudaSuccess)                                                          \
+			return mf_fail(e_ == cudaErrorMemoryAllocation ? MFGPU_ENOMEM : MFGPU_ECUDA, \
+			               "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_),      \
+			               __FILE__, __LINE__);                                         \
+	} while (0)
+
+#define TRY(call)                 \
+	do {                          \
+		int rc_ = (call);         \
+		if (rc_ != MFGPU_OK)      \
+			return rc_;           \
+	} while (0)
+
+#define NCK(call)                                                                          \
+	do {                                                                                   \
+		int r_ = (call);                                                                   \
+		if (r_ != 0)                                                                       \
+			return mf_fail(MFGPU_ECOMM, "%s failed: %s", #call, g_nccl.GetErrorString(r_)); \
+	} while (0)

@@ -1,0 +1,362 @@
+/*
+ * csrc/mf_iter.cu -- the only translation unit that instantiates and launches
+ * kernels: the iteration loop (matFact.c:36-53), the masked arg-max
+ * (matFact.c:55 + :10-27) and the one-shot entries of the C ABI.
+ *
+ * One iteration on one shard is two launches on the double-buffered factors:
+ *     k_update_L(L[c] -> L[1-c], R[c])      writes e_n
+ *     k_update_R(L[c], R[c] -> R[1-c])      reads  e_n
+ * With N shards the second launch writes the partial gradient G instead and
+ * is followed by the exchange:
+ *   - one process, N GPUs: every GPU reads all G over peer memory (NVLink) in
+ *     k_apply_R_peer and adds them in shard order, so all replicas of R are
+ *     bit-identical and equal to the N-shard ordering of the oracle;
+ *   - one process per GPU (rank mode): ncclAllReduce(G) + k_apply_R.
+ * Sequences of iterations are captured in a CUDA graph (launch latency is the
+ * first bound on the small inputs: one iteration of instML100k is ~10 us).
+ */
+#include "mf_internal.h"
+#include "mf_loop.cuh"
+#include "mf_argmax.cuh"
+
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+
+namespace mf {
+
+struct PeerG {
+	const double *g[MF_MAX_SHARDS];
+	int n;
+};
+
+/* one process, N GPUs: R_new = R_old + ((G_0 + G_1) + ...), G_h read over NVLink */
+__global__ void __launch_bounds__(256)
+k_apply_R_peer(int n_touched, int F, int ld, const int *__restrict__ touched_item,
+               const double *__restrict__ Rold, const PeerG pg, double *__restrict__ Rnew)
+{
+	const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
+	const long total = (long)n_touched * F;
+	if (t >= total)
+		return;
+	const int s = (int)(t / F), k = (int)(t % F);
+	const size_t gi = (size_t)s * ld + k;
+	double sum = pg.g[0][gi];
+	for (int h = 1; h < pg.n; h++)
+		sum = __dadd_rn(sum, pg.g[h][gi]);
+	const size_t o = (size_t)touched_item[s] * ld + k;
+	Rnew[o] = __dadd_rn(Rold[o], sum);
+}
+
+} // namespace mf
+
+int mf_k1_prepare(int warps, size_t smem)
+{
+	if (warps == 8)
+		CK(cudaFuncSetAttribute(mf::k_update_L<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+	else
+		CK(cudaFuncSetAttribute(mf::k_update_L<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+	return MFGPU_OK;
+}
+
+static int local_shards(const mfgpu_plan *pl) { return pl->comm ? 1 : pl->nshards; }
+
+/* ---- launches ------------------------------------------------------------------ */
+
+static int launch_update_L(mfgpu_plan *pl, mf_shard *s, int c)
+{
+	if (s->k1_blocks <= 0)
+		return MFGPU_OK;
+	if (s->warps == 8)
+		mf::k_update_L<8><<<s->k1_blocks, 256, s->k1_smem, s->st>>>(s->la, s->L[c], s->L[1 - c], s->R[c]);
+	else
+		mf::k_update_L<1><<<s->k1_blocks, 32, s->k1_smem, s->st>>>(s->la, s->L[c], s->L[1 - c], s->R[c]);
+	CK(cudaGetLastError());
+	pl->launches++;
+	return MFGPU_OK;
+}
+
+static int launch_update_R(mfgpu_plan *pl, mf_shard *s, int c, double *out)
+{
+	if (s->k2_blocks <= 0)
+		return MFGPU_OK;
+	mf::k_update_R<8><<<s->k2_blocks, 256, 0, s->st>>>(s->la, s->L[c], s->R[c], out);
+	CK(cudaGetLastError());
+	pl->launches++;
+	return MFGPU_OK;
+}
+
+/* one iteration of a 1-shard plan, or of one rank in rank mode */
+static int enqueue_iteration(mfgpu_plan *pl, mf_shard *s, int c)
+{
+	TRY(launch_update_L(pl, s, c));
+	if (pl->nshards == 1)
+		return launch_update_R(pl, s, c, s->R[1 - c]);
+	/* rank mode */
+	TRY(launch_update_R(pl, s, c, s->G[0]));
+	const size_t count = (size_t)pl->n_touched * pl->ld;
+	if (count == 0)
+		return MFGPU_OK;
+	/* out of place: the columns this rank never writes must stay 0.0 in G[0] */
+	NCK(g_nccl.AllReduce(s->G[0], s->G[1], count, /*ncclDouble*/ 8, /*ncclSum*/ 0, pl->comm->nccl, s->st));
+	const long total = (long)pl->n_touched * pl->F;
+	mf::k_apply_R<<<(unsigned)((total + 255) / 256), 256, 0, s->st>>>(pl->n_touched, pl->F, pl->ld,
+	                                                                 s->d_touched_item, s->R[c], s->G[1],
+	                                                                 s->R[1 - c]);
+	CK(cudaGetLastError());
+	pl->launches++;
+	return MFGPU_OK;
+}
+
+/* one iteration of a one-process N-GPU plan; `t` picks the G buffer */
+static int enqueue_iteration_peer(mfgpu_plan *pl, int c, int t)
+{
+	const int gb = t & 1;
+	for (int g = 0; g < pl->nshards; g++) {
+		mf_shard *s = &pl->sh[g];
+		CK(cudaSetDevice(s->dev));
+		TRY(launch_update_L(pl, s, c));
+		TRY(launch_update_R(pl, s, c, s->G[gb]));
+		CK(cudaEventRecord(s->ev_g[gb], s->st));
+	}
+	const long total = (long)pl->n_touched * pl->F;
+	if (total == 0)
+		return MFGPU_OK;
+	mf::PeerG pg;
+	pg.n = pl->nshards;
+	for (int h = 0; h < pl->nshards; h++)
+		pg.g[h] = pl->sh[h].G[gb];
+	for (int g = 0; g < pl->nshards; g++) {
+		mf_shard *s = &pl->sh[g];
+		CK(cudaSetDevice(s->dev));
+		for (int h = 0; h < pl->nshards; h++)
+			if (h != g)
+				CK(cudaStreamWaitEvent(s->st, pl->sh[h].ev_g[gb], 0));
+		mf::k_apply_R_peer<<<(unsigned)((total + 255) / 256), 256, 0, s->st>>>(
+		    pl->n_touched, pl->F, pl->ld, s->d_touched_item, s->R[c], pg, s->R[1 - c]);
+		CK(cudaGetLastError());
+		pl->launches++;
+	}
+	return MFGPU_OK;
+}
+
+/* graph of `n` (even) iterations starting at parity c, single shard or rank mode */
+static int build_graph(mfgpu_plan *pl, mf_shard *s, int c, int n)
+{
+	cudaGraph_t graph = nullptr;
+	const long long before = pl->launches;
+	CK(cudaStreamBeginCapture(s->st, cudaStreamCaptureModeThreadLocal));
+	int rc = MFGPU_OK;
+	for (int it = 0; it < n && rc == MFGPU_OK; it++)
+		rc = enqueue_iteration(pl, s, (c + it) & 1);
+	cudaError_t e = cudaStreamEndCapture(s->st, &graph);
+	pl->launches = before;       /* captured, not launched */
+	if (rc != MFGPU_OK) {
+		if (graph) cudaGraphDestroy(graph);
+		return rc;
+	}
+	if (e != cudaSuccess)
+		return mf_fail(MFGPU_ECUDA, "cudaStreamEndCapture: %s", cudaGetErrorString(e));
+	e = cudaGraphInstantiate(&s->gexec[c], graph, 0);
+	cudaGraphDestroy(graph);
+	if (e != cudaSuccess)
+		return mf_fail(MFGPU_ECUDA, "cudaGraphInstantiate: %s", cudaGetErrorString(e));
+	return MFGPU_OK;
+}
+
+static long long launches_per_iteration(const mfgpu_plan *pl, const mf_shard *s)
+{
+	long long n = (s->k1_blocks > 0) + (s->k2_blocks > 0);
+	if (pl->nshards > 1 && (long)pl->n_touched * pl->F > 0)
+		n += 1;
+	return n;
+}
+
+extern "C" int mfgpu_plan_iterate(mfgpu_plan *pl, int iters)
+{
+	if (!pl || iters < 0)
+		return mf_fail(MFGPU_EINVAL, "bad argument");
+	if (!pl->have_factors)
+		return mf_fail(MFGPU_EINVAL, "mfgpu_plan_set_factors has not been called");
+	const int nl = local_shards(pl);
+	for (int g = 0; g < nl; g++) {
+		CK(cudaSetDevice(pl->sh[g].dev));
+		CK(cudaEventRecord(pl->sh[g].ev0, pl->sh[g].st));
+	}
+	int c = pl->cur;
+	if (pl->F == 0 || pl->nnz == 0) {
+		/* nothing changes (matFact.c:41 loop is empty / rows have no columns) */
+	} else if (nl > 1) {
+		for (int t = 0; t < iters; t++, c ^= 1)
+			TRY(enqueue_iteration_peer(pl, c, t));
+	} else {
+		mf_shard *s = &pl->sh[0];
+		CK(cudaSetDevice(s->dev));
+		int left = iters;
+		const int gi = pl->opt_graph_iters;
+		if (pl->opt_graph && left >= gi) {
+			if (!s->gexec[c])
+				TRY(build_graph(pl, s, c, gi));
+			const long long per = launches_per_iteration(pl, s) * gi;
+			for (; left >= gi; left -= gi) {
+				CK(cudaGraphLaunch(s->gexec[c], s->st));
+				pl->launches += per;
+			}
+		}
+		for (; left > 0; left--, c ^= 1)
+			TRY(enqueue_iteration(pl, s, c));
+	}
+	pl->cur = c;
+	for (int g = 0; g < nl; g++) {
+		CK(cudaSetDevice(pl->sh[g].dev));
+		CK(cudaEventRecord(pl->sh[g].ev1, pl->sh[g].st));
+	}
+	return MFGPU_OK;
+}
+
+extern "C" int mfgpu_plan_last_loop_ms(mfgpu_plan *pl, float *ms)
+{
+	if (!pl || !ms)
+		return mf_fail(MFGPU_EINVAL, "null argument");
+	float best = 0.f;
+	for (int g = 0; g < local_shards(pl); g++) {
+		mf_shard *s = &pl->sh[g];
+		CK(cudaSetDevice(s->dev));
+		CK(cudaEventSynchronize(s->ev1));
+		float t = 0.f;
+		CK(cudaEventElapsedTime(&t, s->ev0, s->ev1));
+		best = std::max(best, t);
+	}
+	*ms = pl->loop_ms = best;
+	return MFGPU_OK;
+}
+
+/* ---- masked arg-max -------------------------------------------------------------- */
+
+extern "C" int mfgpu_plan_recommend(mfgpu_plan *pl, int *best)
+{
+	if (!pl || !best)
+		return mf_fail(MFGPU_EINVAL, "null argument");
+	if (!pl->have_factors)
+		return mf_fail(MFGPU_EINVAL, "mfgpu_plan_set_factors has not been called");
+	const int nl = local_shards(pl);
+	const int c = pl->cur;
+	const bool on_device = pl->F > 0 && pl->items > 0;
+	for (int g = 0; g < nl; g++) {
+		mf_shard *s = &pl->sh[g];
+		const int nu = s->user_hi - s->user_lo;
+		CK(cudaSetDevice(s->dev));
+		CK(cudaEventRecord(s->ev0, s->st));
+		if (on_device && nu > 0) {
+			CK(cudaMemsetAsync(s->nan_first, 0, (size_t)nu * sizeof(int), s->st));
+			const int n_tiles = (pl->items + mf::AM_TJ - 1) / mf::AM_TJ;
+			mf::ArgmaxArgs a;
+			a.l_row0 = s->user_lo;
+			a.items = pl->items;
+			a.F = pl->F;
+			a.ld = pl->ld;
+			a.n_splits = s->am_splits;
+			a.tiles_per_split = (n_tiles + s->am_splits - 1) / s->am_splits;
+			a.mask_ptr = s->d_mask_ptr;
+			a.mask_col = s->d_mask_col;
+			a.first_free = s->d_first_free;
+			const int chunk = 65535 * mf::AM_TI;      /* grid.y limit */
+			for (int lo = s->user_lo; lo < s->user_hi; lo += chunk) {
+				a.users_lo = lo;
+				a.users_hi = std::min(s->user_hi, lo + chunk);
+				const size_t off = (size_t)(lo - s->user_lo);
+				a.part_v = s->part_v + off * s->am_splits;
+				a.part_j = s->part_j + off * s->am_splits;
+				a.nan_first = s->nan_first + off;
+				const int cnt = a.users_hi - a.users_lo;
+				dim3 grid((unsigned)s->am_splits, (unsigned)((cnt + mf::AM_TI - 1) / mf::AM_TI));
+				mf::k_masked_argmax<<<grid, 256, 0, s->st>>>(a, s->L[c], s->R[c]);
+				CK(cudaGetLastError());
+				mf::k_argmax_final<<<(cnt + 255) / 256, 256, 0, s->st>>>(a, s->d_best + off);
+				CK(cudaGetLastError());
+				pl->launches += 2;
+			}
+			CK(cudaMemcpyAsync(best + s->user_lo, s->d_best, (size_t)nu * sizeof(int),
+			                   cudaMemcpyDeviceToHost, s->st));
+		} else {
+			/* B has no columns, or is all +0.0 (features == 0): print_output keeps
+			 * the first item its cursor does not skip (matFact.c:17) */
+			for (int i = s->user_lo; i < s->user_hi; i++)
+				best[i] = pl->items > 0 ? s->pat.first_free[i] : -1;
+		}
+		CK(cudaEventRecord(s->ev1, s->st));
+	}
+	float worst = 0.f;
+	for (int g = 0; g < nl; g++) {
+		mf_shard *s = &pl->sh[g];
+		CK(cudaSetDevice(s->dev));
+		CK(cudaStreamSynchronize(s->st));
+		float t = 0.f;
+		CK(cudaEventElapsedTime(&t, s->ev0, s->ev1));
+		worst = std::max(worst, t);
+	}
+	pl->rec_ms = worst;
+	return MFGPU_OK;
+}
+
+extern "C" int mfgpu_plan_last_recommend_ms(mfgpu_plan *pl, float *ms)
+{
+	if (!pl || !ms)
+		return mf_fail(MFGPU_EINVAL, "null argument");
+	*ms = pl->rec_ms;
+	return MFGPU_OK;
+}
+
+/* ---- one-shot entries with host buffers ------------------------------------------- */
+
+static int run_all(int users, int items, int features, int nnz, const mfgpu_entry *entries,
+                   int iters, double alpha, double *L, double *R, int *best, int ngpus,
+                   bool factorize, bool writeback)
+{
+	if (!L || !R)
+		return mf_fail(MFGPU_EINVAL, "null factor pointer");
+	mfgpu_plan *pl = nullptr;
+	TRY(mfgpu_plan_create(&pl, users, items, features, nnz, entries, alpha, ngpus));
+	int rc = mfgpu_plan_set_factors(pl, L, R);
+	if (rc == MFGPU_OK && factorize)
+		rc = mfgpu_plan_iterate(pl, iters);
+	if (rc == MFGPU_OK && writeback)
+		rc = mfgpu_plan_get_factors(pl, L, R);
+	if (rc == MFGPU_OK && best)
+		rc = mfgpu_plan_recommend(pl, best);
+	if (rc == MFGPU_OK)
+		rc = mfgpu_plan_sync(pl);
+	char keep[512];
+	snprintf(keep, sizeof keep, "%s", mfgpu_last_error());
+	mfgpu_plan_destroy(pl);
+	return rc == MFGPU_OK ? rc : mf_fail(rc, "%s", keep);
+}
+
+extern "C" int mfgpu_factorize(int users, int items, int features, int nnz,
+                               const mfgpu_entry *entries, int iters, double alpha,
+                               double *L, double *R, int ngpus)
+{
+	if (iters < 0)
+		return mf_fail(MFGPU_EINVAL, "negative iteration count");
+	return run_all(users, items, features, nnz, entries, iters, alpha, L, R, nullptr, ngpus, true, true);
+}
+
+extern "C" int mfgpu_recommend(int users, int items, int features, int nnz,
+                               const mfgpu_entry *entries, const double *L, const double *R,
+                               int *best, int ngpus)
+{
+	if (!best)
+		return mf_fail(MFGPU_EINVAL, "null output pointer");
+	return run_all(users, items, features, nnz, entries, 0, 0.0, const_cast<double *>(L),
+	               const_cast<double *>(R), best, ngpus, false, false);
+}
+
+extern "C" int mfgpu_run(int users, int items, int features, int nnz,
+                         const mfgpu_entry *entries, int iters, double alpha,
+                         double *L, double *R, int *best, int ngpus)
+{
+	if (iters < 0 || !best)
+		return mf_fail(MFGPU_EINVAL, "bad argument");
+	return run_all(users, items, features, nnz, entries, iters, alpha, L, R, best, ngpus, true, true);
+}

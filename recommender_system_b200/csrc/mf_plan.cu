@@ -1,0 +1,438 @@
+/*
+ * csrc/mf_plan.cu -- plan life cycle: pattern upload, factor buffers, launch geometry.
+ *
+ * Data layout in HBM (per shard = per GPU):
+ *   L[2]   (users of the shard) x ld doubles, row-major, double buffered
+ *   R[2]   items x ld doubles, row-major (the reference's transposed R,
+ *          matFact.c:117-120), double buffered, replicated on every shard
+ *   by-user grouping  row_id / row_ptr / col_idx / val / epos   (longest row first)
+ *   by-item grouping  col_id / col_ptr / row_idx                (longest column first)
+ *   e_csc  nnz doubles, e_n at by-item positions; e_csr the same at by-user positions
+ *   G[2]   (N shards) touched items x ld doubles: partial R gradient
+ * ld = features rounded up to even so every row starts 16-byte aligned.
+ */
+#include "mf_internal.h"
+
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+#include <new>
+
+template <typename T>
+static int upload(T **dst, const T *src, size_t n, cudaStream_t st)
+{
+	CK(cudaMalloc((void **)dst, (n ? n : 1) * sizeof(T)));
+	if (n)
+		CK(cudaMemcpyAsync(*dst, src, n * sizeof(T), cudaMemcpyHostToDevice, st));
+	return MFGPU_OK;
+}
+
+static int pow2_ceil(int x)
+{
+	int p = 1;
+	while (p < x) p <<= 1;
+	return p;
+}
+
+/* Launch geometry of k_update_L / k_update_R for one shard (see mf_loop.cuh). */
+int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
+{
+	const int F = pl->F;
+	int S = (F + 1) & ~1;
+	if (S % 4 == 0)
+		S += 2;              /* S = 2 (mod 4): 16-byte reads of 8 lanes hit 8 distinct bank groups */
+	if (S < 2)
+		S = 2;
+	int max_smem = 0;
+	CK(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, s->dev));
+	const int want = pl->opt_ch > 0 ? pl->opt_ch : 32;
+	int ch_cap = std::min(32, pow2_ceil(std::max(1, s->pat.max_row_len)));
+	ch_cap = std::min(ch_cap, pow2_ceil(want));
+	int warps = 8, CH = 0;
+	/* prefer two resident CTAs per SM, then one, then a single-warp CTA */
+	const size_t budgets[2] = {(size_t)100 * 1024, (size_t)max_smem};
+	for (int b = 0; b < 2 && !CH; b++)
+		for (int ch = ch_cap; ch >= 1; ch >>= 1) {
+			size_t bytes = (size_t)warps * ((size_t)ch * S + S + 32) * sizeof(double);
+			if (bytes <= budgets[b] && (b == 1 || ch >= std::min(ch_cap, 8))) {
+				CH = ch;
+				break;
+			}
+		}
+	if (!CH) {
+		warps = 1;
+		for (int ch = ch_cap; ch >= 1; ch >>= 1)
+			if (((size_t)ch * S + S + 32) * sizeof(double) <= (size_t)max_smem) {
+				CH = ch;
+				break;
+			}
+	}
+	if (!CH)
+		return mf_fail(MFGPU_EINVAL, "features=%d does not fit the shared-memory staging (%d bytes)",
+		               F, max_smem);
+	s->warps = warps;
+	s->k1_smem = (size_t)warps * ((size_t)CH * S + S + 32) * sizeof(double);
+	TRY(mf_k1_prepare(warps, s->k1_smem));
+
+	/* rows longer than the threshold get a whole CTA (their dots run on all warps) */
+	const int thresh = pl->opt_long_row > 0 ? pl->opt_long_row : std::max(8 * CH, 64);
+	int n_long = 0;
+	if (warps > 1)
+		while (n_long < s->pat.n_rows &&
+		       s->pat.row_ptr[n_long + 1] - s->pat.row_ptr[n_long] > thresh)
+			n_long++;
+
+	mf::LoopArgs &a = s->la;
+	a.F = F;
+	a.ld = pl->ld;
+	a.S = S;
+	a.CH = CH;
+	a.n_rows = s->pat.n_rows;
+	a.n_long = n_long;
+	a.n_cols = s->pat.n_cols;
+	a.user_lo = s->user_lo;
+	a.alpha2 = pl->alpha * 2;     /* matFact.c:45: alpha * 2 * (...) associates left, exact */
+	a.row_id = s->d_row_id;
+	a.row_ptr = s->d_row_ptr;
+	a.col_idx = s->d_col_idx;
+	a.epos = s->d_epos;
+	a.val = s->d_val;
+	a.col_id = s->d_col_id;
+	a.col_ptr = s->d_col_ptr;
+	a.row_idx = s->d_row_idx;
+	a.item_slot = pl->nshards > 1 ? s->d_item_slot : nullptr;
+	a.e_csc = s->d_e_csc;
+	a.e_csr = s->d_e_csr;
+	s->k1_blocks = n_long + (a.n_rows - n_long + warps - 1) / warps;
+	const long k2_warps = (long)a.n_cols * ((F + 31) / 32);
+	s->k2_blocks = (int)((k2_warps + 7) / 8);
+	for (int g = 0; g < 2; g++)
+		if (s->gexec[g]) {
+			cudaGraphExecDestroy(s->gexec[g]);
+			s->gexec[g] = nullptr;
+		}
+	return MFGPU_OK;
+}
+
+static int shard_create(mfgpu_plan *pl, mf_shard *s, int dev, const mfgpu_entry *entries,
+                        const int *item_slot, const int *touched_item)
+{
+	s->dev = dev;
+	CK(cudaSetDevice(dev));
+	CK(cudaStreamCreateWithFlags(&s->st, cudaStreamNonBlocking));
+	CK(cudaEventCreate(&s->ev0));
+	CK(cudaEventCreate(&s->ev1));
+	for (int g = 0; g < 2; g++)
+		CK(cudaEventCreateWithFlags(&s->ev_g[g], cudaEventDisableTiming));
+	int rc = mf_pattern_build(&s->pat, pl->users, pl->items, pl->nnz, entries, s->user_lo, s->user_hi);
+	if (rc != MFGPU_OK)
+		return mf_fail(rc, rc == MFGPU_EINVAL ? "an entry lies outside the users x items matrix"
+		                                      : "out of host memory building the pattern");
+	const mf_pattern &p = s->pat;
+	TRY(upload(&s->d_row_id, p.row_id, (size_t)p.n_rows, s->st));
+	TRY(upload(&s->d_row_ptr, p.row_ptr, (size_t)p.n_rows + 1, s->st));
+	TRY(upload(&s->d_col_idx, p.col_idx, (size_t)p.nnz, s->st));
+	TRY(upload(&s->d_epos, p.epos, (size_t)p.nnz, s->st));
+	TRY(upload(&s->d_val, p.val, (size_t)p.nnz, s->st));
+	TRY(upload(&s->d_col_id, p.col_id, (size_t)p.n_cols, s->st));
+	TRY(upload(&s->d_col_ptr, p.col_ptr, (size_t)p.n_cols + 1, s->st));
+	TRY(upload(&s->d_row_idx, p.row_idx, (size_t)p.nnz, s->st));
+	TRY(upload(&s->d_mask_ptr, p.mask_ptr, (size_t)pl->users + 1, s->st));
+	TRY(upload(&s->d_mask_col, p.mask_col, (size_t)p.mask_ptr[pl->users], s->st));
+	TRY(upload(&s->d_first_free, p.first_free, (size_t)pl->users, s->st));
+	CK(cudaMalloc((void **)&s->d_e_csc, ((size_t)p.nnz + 1) * sizeof(double)));
+	CK(cudaMalloc((void **)&s->d_e_csr, ((size_t)p.nnz + 1) * sizeof(double)));
+
+	const size_t nu = (size_t)(s->user_hi - s->user_lo);
+	const size_t lbytes = (nu * pl->ld + 2) * sizeof(double);
+	const size_t rbytes = ((size_t)pl->items * pl->ld + 2) * sizeof(double);
+	for (int b = 0; b < 2; b++) {
+		CK(cudaMalloc((void **)&s->L[b], lbytes));
+		CK(cudaMalloc((void **)&s->R[b], rbytes));
+		CK(cudaMemsetAsync(s->L[b], 0, lbytes, s->st));
+		CK(cudaMemsetAsync(s->R[b], 0, rbytes, s->st));
+	}
+	if (pl->nshards > 1) {
+		TRY(upload(&s->d_item_slot, item_slot, (size_t)pl->items, s->st));
+		TRY(upload(&s->d_touched_item, touched_item, (size_t)pl->n_touched, s->st));
+		const size_t gbytes = ((size_t)pl->n_touched * pl->ld + 2) * sizeof(double);
+		for (int b = 0; b < 2; b++) {
+			CK(cudaMalloc((void **)&s->G[b], gbytes));
+			/* columns without a local nonzero are never written: they stay 0.0 */
+			CK(cudaMemsetAsync(s->G[b], 0, gbytes, s->st));
+		}
+	}
+	/* arg-max scratch */
+	const int tiles_y = (int)((nu + mf::AM_TI - 1) / mf::AM_TI);
+	const int n_tiles = (pl->items + mf::AM_TJ - 1) / mf::AM_TJ;
+	int splits = tiles_y > 0 ? (148 * 4 + tiles_y - 1) / tiles_y : 1;
+	splits = std::max(1, std::min(splits, std::max(1, n_tiles)));
+	s->am_splits = splits;
+	CK(cudaMalloc((void **)&s->part_v, (nu * splits + 1) * sizeof(double)));
+	CK(cudaMalloc((void **)&s->part_j, (nu * splits + 1) * sizeof(int)));
+	CK(cudaMalloc((void **)&s->nan_first, (nu + 1) * sizeof(int)));
+	CK(cudaMalloc((void **)&s->d_best, (nu + 1) * sizeof(int)));
+	TRY(mf_configure_shard(pl, s));
+	CK(cudaStreamSynchronize(s->st));
+	return MFGPU_OK;
+}
+
+static void shard_destroy(mf_shard *s)
+{
+	if (s->dev >= 0)
+		cudaSetDevice(s->dev);
+	for (int g = 0; g < 2; g++) {
+		if (s->gexec[g]) cudaGraphExecDestroy(s->gexec[g]);
+		if (s->ev_g[g]) cudaEventDestroy(s->ev_g[g]);
+		cudaFree(s->L[g]);
+		cudaFree(s->R[g]);
+		cudaFree(s->G[g]);
+	}
+	void *ptrs[] = {s->d_row_id, s->d_row_ptr, s->d_col_idx, s->d_epos, s->d_col_id, s->d_col_ptr,
+	                s->d_row_idx, s->d_val, s->d_e_csc, s->d_e_csr, s->d_mask_ptr, s->d_mask_col,
+	                s->d_first_free, s->d_item_slot, s->d_touched_item, s->part_v, s->part_j,
+	                s->nan_first, s->d_best};
+	for (void *q : ptrs)
+		cudaFree(q);
+	if (s->ev0) cudaEventDestroy(s->ev0);
+	if (s->ev1) cudaEventDestroy(s->ev1);
+	if (s->st) cudaStreamDestroy(s->st);
+	mf_pattern_free(&s->pat);
+	cudaGetLastError();
+}
+
+static int plan_create(mfgpu_plan **out, int users, int items, int features, int nnz,
+                       const mfgpu_entry *entries, double alpha, int ngpus, mfgpu_comm *comm)
+{
+	if (!out)
+		return mf_fail(MFGPU_EINVAL, "null plan pointer");
+	*out = nullptr;
+	if (users < 0 || items < 0 || features < 0 || nnz < 0 || (nnz > 0 && !entries))
+		return mf_fail(MFGPU_EINVAL, "negative size or missing entries");
+	if ((double)items * ((features + 1) & ~1) >= 2147483647.0 * 4 ||
+	    (double)users * ((features + 1) & ~1) >= 2147483647.0 * 4)
+		return mf_fail(MFGPU_EINVAL, "factor matrix too large");
+	int devs[MF_MAX_SHARDS];
+	const int avail = mf_usable_devices(devs, MF_MAX_SHARDS);
+	if (avail == 0)
+		return mf_fail(MFGPU_ENODEV, "no sm_100 (B200) device visible; this library has no CPU path");
+	int nshards = comm ? comm->nranks : (ngpus <= 0 ? avail : ngpus);
+	if (!comm && nshards > avail)
+		return mf_fail(MFGPU_ENODEV, "%d GPUs requested, %d usable", nshards, avail);
+	if (nshards > MF_MAX_SHARDS)
+		return mf_fail(MFGPU_EINVAL, "at most %d shards", MF_MAX_SHARDS);
+
+	mfgpu_plan *pl = new (std::nothrow) mfgpu_plan();
+	if (!pl)
+		return mf_fail(MFGPU_ENOMEM, "out of host memory");
+	for (int i = 0; i < MF_MAX_SHARDS; i++)
+		pl->sh[i].dev = -1;
+	pl->users = users;
+	pl->items = items;
+	pl->F = features;
+	pl->ld = std::max(2, (features + 1) & ~1);
+	pl->nnz = nnz;
+	pl->alpha = alpha;
+	pl->nshards = nshards;
+	pl->comm = comm;
+	pl->opt_graph = 1;
+	pl->opt_graph_iters = 16;
+
+	int rc = mf_split_users(users, nnz, entries, nshards, pl->cut);
+	int *item_slot = nullptr, *touched = nullptr;
+	if (rc == MFGPU_OK && nshards > 1) {
+		item_slot = (int *)malloc(sizeof(int) * (size_t)(items ? items : 1));
+		if (!item_slot)
+			rc = MFGPU_ENOMEM;
+		else {
+			int cnt = mf_touched_items(items, nnz, entries, item_slot);
+			if (cnt < 0)
+				rc = cnt;
+			else {
+				pl->n_touched = cnt;
+				touched = (int *)malloc(sizeof(int) * (size_t)(cnt ? cnt : 1));
+				if (!touched)
+					rc = MFGPU_ENOMEM;
+				else
+					for (int j = 0; j < items; j++)
+						if (item_slot[j] >= 0)
+							touched[item_slot[j]] = j;
+			}
+		}
+	}
+	if (rc != MFGPU_OK)
+		mf_fail(rc, rc == MFGPU_EINVAL ? "an entry lies outside the users x items matrix"
+		                               : "out of host memory");
+	if (rc == MFGPU_OK) {
+		if (comm) {
+			/* rank mode: this process holds one shard, the users of its rank */
+			pl->sh[0].user_lo = pl->cut[comm->rank];
+			pl->sh[0].user_hi = pl->cut[comm->rank + 1];
+			rc = shard_create(pl, &pl->sh[0], comm->device, entries, item_slot, touched);
+		} else {
+			for (int g = 0; g < nshards && rc == MFGPU_OK; g++) {
+				pl->sh[g].user_lo = pl->cut[g];
+				pl->sh[g].user_hi = pl->cut[g + 1];
+				rc = shard_create(pl, &pl->sh[g], devs[g], entries, item_slot, touched);
+			}
+			/* the peer exchange reads every other shard's G directly */
+			for (int g = 0; g < nshards && rc == MFGPU_OK && nshards > 1; g++) {
+				cudaSetDevice(devs[g]);
+				for (int h = 0; h < nshards; h++) {
+					if (h == g) continue;
+					int ok = 0;
+					cudaDeviceCanAccessPeer(&ok, devs[g], devs[h]);
+					if (!ok) {
+						rc = mf_fail(MFGPU_ECUDA, "no peer access between devices %d and %d", devs[g], devs[h]);
+						break;
+					}
+					cudaError_t e = cudaDeviceEnablePeerAccess(devs[h], 0);
+					if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) {
+						rc = mf_fail(MFGPU_ECUDA, "cudaDeviceEnablePeerAccess: %s", cudaGetErrorString(e));
+						break;
+					}
+					cudaGetLastError();
+				}
+			}
+		}
+	}
+	free(item_slot);
+	free(touched);
+	if (rc != MFGPU_OK) {
+		char keep[512];
+		snprintf(keep, sizeof keep, "%s", mfgpu_last_error());
+		mfgpu_plan_destroy(pl);
+		return mf_fail(rc, "%s", keep);
+	}
+	*out = pl;
+	return MFGPU_OK;
+}
+
+extern "C" int mfgpu_plan_create(mfgpu_plan **out, int users, int items, int features, int nnz,
+                                 const mfgpu_entry *entries, double alpha, int ngpus)
+{
+	return plan_create(out, users, items, features, nnz, entries, alpha, ngpus, nullptr);
+}
+
+extern "C" int mfgpu_plan_create_rank(mfgpu_plan **out, int users, int items, int features, int nnz,
+                                      const mfgpu_entry *entries, double alpha, mfgpu_comm *comm)
+{
+	if (!comm)
+		return mf_fail(MFGPU_EINVAL, "null communicator");
+	return plan_create(out, users, items, features, nnz, entries, alpha, comm->nranks, comm);
+}
+
+extern "C" void mfgpu_plan_destroy(mfgpu_plan *pl)
+{
+	if (!pl)
+		return;
+	const int n = pl->comm ? 1 : pl->nshards;
+	for (int g = 0; g < n; g++)
+		if (pl->sh[g].dev >= 0)
+			shard_destroy(&pl->sh[g]);
+	delete pl;
+}
+
+static int local_shards(const mfgpu_plan *pl) { return pl->comm ? 1 : pl->nshards; }
+
+extern "C" int mfgpu_plan_set_factors(mfgpu_plan *pl, const double *L, const double *R)
+{
+	if (!pl || !L || !R)
+		return mf_fail(MFGPU_EINVAL, "null argument");
+	const size_t F = (size_t)pl->F, ld = (size_t)pl->ld;
+	for (int g = 0; g < local_shards(pl); g++) {
+		mf_shard *s = &pl->sh[g];
+		CK(cudaSetDevice(s->dev));
+		const size_t nu = (size_t)(s->user_hi - s->user_lo);
+		if (F && nu)
+			CK(cudaMemcpy2DAsync(s->L[0], ld * 8, L + (size_t)s->user_lo * F, F * 8, F * 8, nu,
+			                     cudaMemcpyHostToDevice, s->st));
+		if (F && pl->items)
+			CK(cudaMemcpy2DAsync(s->R[0], ld * 8, R, F * 8, F * 8, (size_t)pl->items,
+			                     cudaMemcpyHostToDevice, s->st));
+		/* rows without a nonzero are never rewritten, so both buffers start equal */
+		CK(cudaMemcpyAsync(s->L[1], s->L[0], nu * ld * 8, cudaMemcpyDeviceToDevice, s->st));
+		CK(cudaMemcpyAsync(s->R[1], s->R[0], (size_t)pl->items * ld * 8, cudaMemcpyDeviceToDevice, s->st));
+	}
+	for (int g = 0; g < local_shards(pl); g++)
+		CK(cudaStreamSynchronize(pl->sh[g].st));
+	pl->cur = 0;
+	pl->have_factors = 1;
+	return MFGPU_OK;
+}
+
+extern "C" int mfgpu_plan_get_factors(mfgpu_plan *pl, double *L, double *R)
+{
+	if (!pl)
+		return mf_fail(MFGPU_EINVAL, "null plan");
+	const size_t F = (size_t)pl->F, ld = (size_t)pl->ld;
+	const int c = pl->cur;
+	for (int g = 0; g < local_shards(pl); g++) {
+		mf_shard *s = &pl->sh[g];
+		CK(cudaSetDevice(s->dev));
+		const size_t nu = (size_t)(s->user_hi - s->user_lo);
+		if (L && F && nu)
+			CK(cudaMemcpy2DAsync(L + (size_t)s->user_lo * F, F * 8, s->L[c], ld * 8, F * 8, nu,
+			                     cudaMemcpyDeviceToHost, s->st));
+		if (R && g == 0 && F && pl->items)
+			CK(cudaMemcpy2DAsync(R, F * 8, s->R[c], ld * 8, F * 8, (size_t)pl->items,
+			                     cudaMemcpyDeviceToHost, s->st));
+	}
+	for (int g = 0; g < local_shards(pl); g++)
+		CK(cudaStreamSynchronize(pl->sh[g].st));
+	return MFGPU_OK;
+}
+
+extern "C" int mfgpu_plan_sync(mfgpu_plan *pl)
+{
+	if (!pl)
+		return mf_fail(MFGPU_EINVAL, "null plan");
+	for (int g = 0; g < local_shards(pl); g++) {
+		CK(cudaSetDevice(pl->sh[g].dev));
+		CK(cudaStreamSynchronize(pl->sh[g].st));
+	}
+	return MFGPU_OK;
+}
+
+extern "C" int mfgpu_plan_user_range(mfgpu_plan *pl, int shard, int *lo, int *hi)
+{
+	if (!pl || shard < 0 || shard >= local_shards(pl))
+		return mf_fail(MFGPU_EINVAL, "bad shard index");
+	if (lo) *lo = pl->sh[shard].user_lo;
+	if (hi) *hi = pl->sh[shard].user_hi;
+	return MFGPU_OK;
+}
+
+extern "C" long long mfgpu_plan_launch_count(mfgpu_plan *pl) { return pl ? pl->launches : 0; }
+
+extern "C" long long mfgpu_plan_bytes_per_iter(mfgpu_plan *pl)
+{
+	if (!pl)
+		return 0;
+	/* 16*F*(U_t + I_t) + 12*nnz over the shards held by this process */
+	long long b = 0;
+	for (int g = 0; g < local_shards(pl); g++) {
+		const mf_pattern &p = pl->sh[g].pat;
+		b += 16LL * pl->F * ((long long)p.n_rows + p.n_cols) + 12LL * p.nnz;
+	}
+	return b;
+}
+
+extern "C" int mfgpu_plan_set_option(mfgpu_plan *pl, const char *name, int value)
+{
+	if (!pl || !name)
+		return mf_fail(MFGPU_EINVAL, "null argument");
+	if (!strcmp(name, "graph")) pl->opt_graph = value;
+	else if (!strcmp(name, "graph_iters")) pl->opt_graph_iters = std::max(2, value & ~1);
+	else if (!strcmp(name, "long_row")) pl->opt_long_row = value;
+	else if (!strcmp(name, "chunk")) pl->opt_ch = value;
+	else
+		return mf_fail(MFGPU_EINVAL, "unknown option '%s'", name);
+	for (int g = 0; g < local_shards(pl); g++) {
+		CK(cudaSetDevice(pl->sh[g].dev));
+		CK(cudaStreamSynchronize(pl->sh[g].st));
+		TRY(mf_configure_shard(pl, &pl->sh[g]));
+	}
+	return MFGPU_OK;
+}

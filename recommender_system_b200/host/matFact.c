@@ -1,0 +1,125 @@
+/*
+ * host/matFact.c -- the drop-in program:  matFact <file.in>
+ *
+ * Same command line, input format, error messages, initialisation sequence
+ * and stdout as the reference's serial program (matFact.c:61-137,
+ * util.c:7-34); the two calls matrix_factorization() + print_output()
+ * (matFact.c:124,127) are replaced by one call into the C ABI of
+ * libmatfact_b200.so, which runs them on the GPU(s).  B is never allocated.
+ * Plain C: this file knows nothing about CUDA.
+ *
+ * Environment (additions; the reference has none):
+ *   MATFACT_NGPUS   number of B200s to shard the users over (default 1: the
+ *                   bit-exact ordering; 0 = all visible)
+ *   MATFACT_DUMP    file that receives the final L then R as raw doubles
+ *   MATFACT_TIMING  if set, phase times go to stderr (stdout stays the
+ *                   recommendations only)
+ */
+#include "matfact_b200.h"
+
+#include <stdio.h>
+#include <stdlib.h>
+#include <time.h>
+
+static void die(const char *error)
+{
+	fprintf(stderr, "Error: %s\n", error);   /* util.c:7-10 */
+	exit(-1);
+}
+
+static void die_gpu(const char *what)
+{
+	fprintf(stderr, "Error: %s: %s\n", what, mfgpu_last_error());
+	exit(-1);
+}
+
+static double now_s(void)
+{
+	struct timespec ts;
+	clock_gettime(CLOCK_MONOTONIC, &ts);
+	return ts.tv_sec + 1e-9 * ts.tv_nsec;
+}
+
+int main(int argc, char **argv)
+{
+	if (argc != 2) {
+		fprintf(stderr, "Run ./matFact.out file");
+		die("Missing input file name.");
+	}
+	const double t_start = now_s();
+	FILE *fp = fopen(argv[1], "r");
+	if (fp == NULL)
+		die("Unable to open input file.");
+
+	int iters, features, users, items, non_zero;
+	double alpha;
+	if (fscanf(fp, "%d", &iters) != 1)
+		die("Error in int argument.");
+	if (fscanf(fp, "%lf", &alpha) != 1)
+		die("Error in double argument.");
+	if (fscanf(fp, "%d", &features) != 1)
+		die("Error in int argument.");
+	if (fscanf(fp, "%d %d %d", &users, &items, &non_zero) != 3)
+		die("Error in multiple int argument.");
+	if (users < 0 || items < 0 || non_zero < 0 || features < 0)
+		die("Error in multiple int argument.");
+
+	mfgpu_entry *entries = malloc(sizeof *entries * (non_zero > 0 ? (size_t)non_zero : 1));
+	if (!entries)
+		die("Out of memory.");
+	for (int n = 0; n < non_zero; n++)
+		if (fscanf(fp, "%d %d %lf", &entries[n].row, &entries[n].col, &entries[n].value) != 3)
+			die("Error in non-zero entry.");
+	if (fclose(fp) == EOF)
+		die("Unable to close input file.");
+	const double t_parsed = now_s();
+
+	const size_t nl = (size_t)users * features, nr = (size_t)items * features;
+	double *L = malloc(sizeof *L * (nl ? nl : 1));
+	double *R = malloc(sizeof *R * (nr ? nr : 1));
+	int *best = malloc(sizeof *best * (users > 0 ? (size_t)users : 1));
+	if (!L || !R || !best)
+		die("Out of memory.");          /* the reference does not check (mat2d.c:14-19) */
+	mfgpu_random_fill_LR(users, items, features, L, R);
+	const double t_init = now_s();
+
+	const char *env = getenv("MATFACT_NGPUS");
+	const int ngpus = env ? atoi(env) : 1;
+	const char *dump = getenv("MATFACT_DUMP");
+
+	mfgpu_plan *plan = NULL;
+	float loop_ms = 0.f, rec_ms = 0.f;
+	if (mfgpu_plan_create(&plan, users, items, features, non_zero, entries, alpha, ngpus))
+		die_gpu("cannot set up the GPU factorization");
+	if (mfgpu_plan_set_factors(plan, L, R))
+		die_gpu("cannot upload the factors");
+	if (mfgpu_plan_iterate(plan, iters < 0 ? 0 : iters) || mfgpu_plan_last_loop_ms(plan, &loop_ms))
+		die_gpu("factorization failed");
+	if (dump) {
+		if (mfgpu_plan_get_factors(plan, L, R))
+			die_gpu("cannot read the factors back");
+		FILE *out = fopen(dump, "wb");
+		if (!out || fwrite(L, sizeof *L, nl, out) != nl || fwrite(R, sizeof *R, nr, out) != nr ||
+		    fclose(out) == EOF)
+			die("Unable to write the factor dump.");
+	}
+	if (mfgpu_plan_recommend(plan, best) || mfgpu_plan_last_recommend_ms(plan, &rec_ms))
+		die_gpu("recommendation failed");
+	mfgpu_plan_destroy(plan);
+	const double t_gpu = now_s();
+
+	/* matFact.c:24-25: one line per user that has an unrated item */
+	for (int i = 0; i < users; i++)
+		if (best[i] != -1)
+			printf("%d\n", best[i]);
+
+	if (getenv("MATFACT_TIMING"))
+		fprintf(stderr,
+		        "parse_s %.6f\ninit_s %.6f\ngpu_total_s %.6f\nloop_ms %.3f\nargmax_ms %.3f\ntotal_s %.6f\n",
+		        t_parsed - t_start, t_init - t_parsed, t_gpu - t_init, loop_ms, rec_ms, now_s() - t_start);
+	free(best);
+	free(R);
+	free(L);
+	free(entries);
+	return 0;
+}

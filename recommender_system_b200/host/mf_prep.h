@@ -21,23 +21,23 @@ typedef struct {
 	int users, items, nnz;      /* nnz = nonzeros of THIS shard                      */
 	int user_lo, user_hi;       /* users owned by this shard: [user_lo, user_hi)     */
 
-	/* by-user grouping ("CSR"); rows are the users with >=1 nonzero, stored
+	/* by-user grouping; rows are the users with >=1 nonzero, stored
 	 * longest row first so that the longest serial chains start first */
 	int n_rows;
 	int *row_id;                /* [n_rows]   user index of stored row r             */
-	int *row_ptr;               /* [n_rows+1] start of row r in col_idx/val          */
+	int *row_ptr;               /* [n_rows+1] start of row r in col_idx/val/epos     */
 	int *col_idx;               /* [nnz]      item of each nonzero (file order in row) */
 	double *val;                /* [nnz]      rating a_ij                            */
+	int *epos;                  /* [nnz]      by-user position -> by-item position   */
 
-	/* by-item grouping ("CSC"), longest column first */
+	/* by-item grouping, longest column first */
 	int n_cols;
 	int *col_id;                /* [n_cols]   item index of stored column c          */
 	int *col_ptr;               /* [n_cols+1]                                        */
 	int *row_idx;               /* [nnz]      user of each nonzero (file order in column) */
-	int *perm;                  /* [nnz]      by-item position -> by-user position   */
 
 	/* rated-item mask of print_output (matFact.c:14-22), users of this shard */
-	int *mask_ptr;              /* [users+1]  (only [user_lo..user_hi] meaningful)   */
+	int *mask_ptr;              /* [users+1]  (entries outside [user_lo,user_hi] repeat the ends) */
 	int *mask_col;              /* [mask_ptr[users]] ascending items per user        */
 	int *first_free;            /* [users]    first item the cursor does not skip, -1 if none */
 
@@ -49,6 +49,11 @@ typedef struct {
 int mf_pattern_build(mf_pattern *p, int users, int items, int nnz,
                      const mfgpu_entry *entries, int user_lo, int user_hi);
 void mf_pattern_free(mf_pattern *p);
+
+/* Number of leading entries the cursor of print_output (matFact.c:14-22) ever
+ * matches: the longest prefix that is strictly increasing in (row, col).  For
+ * the (row, col)-sorted, duplicate-free files of the reference this is nnz. */
+int mf_mask_prefix(int users, int items, int nnz, const mfgpu_entry *entries);
 
 /* Contiguous user ranges with balanced nonzero counts (SURVEY.md section 8e;
  * the reference's equal-count split is mpiutil.h:8-13 BLOCK_LOW).
