@@ -1,0 +1,220 @@
+"""Parity of the CUDA path (through the C ABI) with the oracle and the
+reference's golden vectors.  Bar: bit-exact recommendations everywhere;
+L and R bit-identical to the serial reference on one GPU (tolerance 0), and
+for N shards bit-identical to the oracle's N-shard ordering, which itself is
+within 1e-9 norm-wise of the serial one (tests/test_oracle.py)."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from conftest import ROOT, gold_path, load_instance, load_out, lr_sha256
+from recommender_system_b200 import synth
+from recommender_system_b200.io import ENTRY_DTYPE, Instance, format_output
+
+pytestmark = pytest.mark.gpu
+
+SAMPLES = ["inst0", "inst1", "inst2", "inst30-40-10-2-10", "inst500-500-20-2-100",
+           "inst1000-1000-100-2-30", "inst200-10000-50-100-300", "inst400-50000-30-200-500",
+           "inst600-10000-10-40-400", "inst50000-5000-100-2-5", "instML100k"]
+
+
+def bits_equal(a, b):
+    return np.array_equal(a.view(np.uint64), b.view(np.uint64))
+
+
+@pytest.mark.parametrize("sample", SAMPLES)
+def test_golden_samples(gpu, expected, sample):
+    """Every sample of the reference that has an input and a golden output:
+    stdout identical, final L||R bit-identical to the serial reference."""
+    inst = load_instance(sample)
+    L, R, best = gpu.run_instance(inst)
+    assert format_output(best) == load_out(sample)
+    assert lr_sha256(L, R) == expected[sample]["lr_sha256"]
+
+
+def _check_against_oracle(gpu, oracle, inst, iters=None, options=None):
+    iters = inst.iters if iters is None else iters
+    L0, R0 = oracle.init_LR(inst.users, inst.items, inst.features)
+    L1, R1 = L0.copy(), R0.copy()
+    oracle.factorize(inst.users, inst.items, inst.features, inst.entries, iters, inst.alpha, L0, R0)
+    ref_best = oracle.recommend(inst.users, inst.items, inst.features, inst.entries, L0, R0)
+    with gpu.Plan(inst.users, inst.items, inst.features, inst.entries, inst.alpha) as plan:
+        for k, v in (options or {}).items():
+            plan.set_option(k, v)
+        plan.set_factors(L1, R1)
+        plan.iterate(iters)
+        plan.get_factors(L1, R1)
+        best = plan.recommend()
+    assert bits_equal(L0, L1), "L differs: max |d| = %g" % np.max(np.abs(L0 - L1))
+    assert bits_equal(R0, R1), "R differs: max |d| = %g" % np.max(np.abs(R0 - R1))
+    assert np.array_equal(best, ref_best)
+
+
+SHAPES = [
+    # users, items, F, density, iters
+    (1, 1, 1, 1.0, 3),
+    (7, 5, 1, 0.5, 9),
+    (33, 65, 3, 0.3, 7),          # odd F: padded row stride
+    (40, 130, 31, 0.2, 5),
+    (64, 64, 32, 0.5, 4),
+    (50, 70, 33, 0.4, 5),         # F just over one lane group
+    (20, 300, 100, 0.6, 3),       # rows of ~180 nonzeros: several chunks per row
+    (129, 257, 16, 0.05, 6),      # many empty rows and columns
+    (10, 2000, 8, 0.9, 3),        # very long rows (whole-CTA path), short columns
+    (2000, 10, 8, 0.9, 3),        # very long columns
+    (12, 9, 200, 0.5, 3),
+    (5, 6, 1000, 0.5, 2),         # F=1000 as in inst1000-1e6-1000-1-3
+]
+
+
+@pytest.mark.parametrize("shape", SHAPES)
+def test_random_instances_bit_exact(gpu, oracle, shape):
+    users, items, F, dens, iters = shape
+    inst = synth.random_instance(users, items, F, dens, iters, 0.002, seed=users * 7 + items)
+    _check_against_oracle(gpu, oracle, inst)
+
+
+@pytest.mark.parametrize("options", [
+    {"graph": 0}, {"graph_iters": 2}, {"long_row": 1}, {"long_row": 1000000},
+    {"chunk": 1}, {"chunk": 4}, {"chunk": 16, "long_row": 20},
+])
+def test_launch_options_do_not_change_bits(gpu, oracle, options):
+    inst = synth.random_instance(60, 400, 24, 0.3, 37, 0.001, seed=5, values="real")
+    _check_against_oracle(gpu, oracle, inst, options=options)
+
+
+def test_edge_cases(gpu, oracle):
+    # no nonzeros at all; a user who rated everything (prints nothing); empty matrices
+    e = np.zeros(0, dtype=ENTRY_DTYPE)
+    _check_against_oracle(gpu, oracle, Instance(5, 0.01, 4, 3, 6, e))
+    full = synth.random_instance(4, 9, 5, 1.0, 3, 0.01, seed=1)
+    L, R, best = gpu.run_instance(full)
+    assert np.all(best == -1) and format_output(best) == ""
+    _check_against_oracle(gpu, oracle, full)
+    one_free = synth.random_instance(6, 70, 5, 1.0, 2, 0.01, seed=2)
+    one_free.entries = one_free.entries[np.arange(one_free.nnz) % 71 != 3]
+    _check_against_oracle(gpu, oracle, one_free)
+    _check_against_oracle(gpu, oracle, Instance(3, 0.01, 4, 0, 6, e))
+    _check_against_oracle(gpu, oracle, Instance(3, 0.01, 4, 5, 0, e))
+    _check_against_oracle(gpu, oracle, Instance(0, 0.01, 4, 5, 7, e))
+
+
+def test_unsorted_and_duplicate_entries(gpu, oracle):
+    """The loop takes entries in file order whatever it is (matFact.c:41-53) and
+    print_output's cursor only ever matches a sorted prefix (matFact.c:14-22)."""
+    inst = synth.random_instance(25, 40, 6, 0.3, 11, 0.003, seed=9, values="real")
+    rng = np.random.default_rng(3)
+    e = inst.entries.copy()
+    k = len(e) // 2
+    tail = e[k:].copy()
+    rng.shuffle(tail)
+    e2 = np.concatenate([e[:k], tail, e[5:9]])          # sorted prefix, shuffled rest, duplicates
+    _check_against_oracle(gpu, oracle, Instance(inst.iters, inst.alpha, inst.features, 25, 40, e2))
+    e3 = e.copy()
+    rng.shuffle(e3)
+    _check_against_oracle(gpu, oracle, Instance(inst.iters, inst.alpha, inst.features, 25, 40, e3))
+
+
+def test_recommend_nan_inf_ties(gpu, oracle):
+    """print_output semantics on hostile values: ties -> lowest index, NaN never
+    displaces, a NaN at the first unrated item is never displaced."""
+    users, items, F = 8, 150, 3
+    inst = synth.random_instance(users, items, F, 0.2, 0, 0.0, seed=4)
+    rng = np.random.default_rng(0)
+    L = rng.standard_normal((users, F))
+    R = rng.standard_normal((items, F))
+    R[40] = R[10]; R[90] = R[10]                 # exact ties
+    L[1] = 0.0                                   # whole row of +0.0: first unrated wins
+    L[2, 0] = np.nan                             # whole row NaN: first unrated wins
+    R[5, 1] = np.nan                             # NaN column inside ordinary rows
+    R[0, 2] = np.inf
+    R[140] = -R[0]
+    L[3] = np.abs(L[3])
+    L[4] = -np.abs(L[4])
+    ref = oracle.recommend(users, items, F, inst.entries, L, R)
+    got = gpu.recommend(L, R, inst.entries)
+    assert np.array_equal(ref, got)
+    R[0, :] = np.nan                             # first item NaN for users that did not rate it
+    ref = oracle.recommend(users, items, F, inst.entries, L, R)
+    got = gpu.recommend(L, R, inst.entries)
+    assert np.array_equal(ref, got)
+
+
+def test_diverging_run_matches(gpu, oracle):
+    """alpha far too large: values overflow to inf/NaN; the bits still agree."""
+    inst = synth.random_instance(30, 30, 4, 0.5, 40, 5.0, seed=12)
+    L0, R0 = oracle.init_LR(30, 30, 4)
+    L1, R1 = L0.copy(), R0.copy()
+    oracle.factorize(30, 30, 4, inst.entries, inst.iters, inst.alpha, L0, R0)
+    gpu.matrix_factorization(L1, R1, inst.entries, inst.iters, inst.alpha)
+    assert not np.all(np.isfinite(L0))
+    assert bits_equal(L0, L1) and bits_equal(R0, R1)
+    assert np.array_equal(oracle.recommend(30, 30, 4, inst.entries, L0, R0),
+                          gpu.recommend(L1, R1, inst.entries))
+
+
+def test_full_size_inst60000_shape(gpu, oracle):
+    """BASELINE.json configs[3] shape (synthetic stand-in, input blob missing):
+    two iterations bit-exact against the oracle; L is 96 MB."""
+    inst = synth.inst60000_like(iters=2)
+    _check_against_oracle(gpu, oracle, inst)
+
+
+def test_full_size_ml1m_shape(gpu, oracle):
+    """BASELINE.json configs[2] shape (synthetic stand-in): heavy-tailed rows and
+    columns (max 2314 / ~3400 nonzeros) exercise the whole-CTA path."""
+    inst = synth.ml_like(iters=2)
+    _check_against_oracle(gpu, oracle, inst)
+
+
+def test_iterate_is_resumable(gpu, oracle):
+    """T iterations in one call == the same T split over several calls (odd
+    counts flip the double buffer)."""
+    inst = synth.random_instance(40, 50, 12, 0.3, 45, 0.002, seed=21)
+    L0, R0 = oracle.init_LR(40, 50, 12)
+    L1, R1 = L0.copy(), R0.copy()
+    oracle.factorize(40, 50, 12, inst.entries, 45, inst.alpha, L0, R0)
+    with gpu.Plan(40, 50, 12, inst.entries, inst.alpha) as plan:
+        plan.set_factors(L1, R1)
+        for n in (1, 16, 3, 17, 8):
+            plan.iterate(n)
+        plan.get_factors(L1, R1)
+        assert plan.launch_count() == 2 * 45
+    assert bits_equal(L0, L1) and bits_equal(R0, R1)
+
+
+def test_cli_is_a_drop_in(gpu, tmp_path):
+    """bin/matFact <file.in>: stdout is the golden, errors are the reference's."""
+    exe = os.path.join(ROOT, "bin", "matFact")
+    src = gold_path("inst30-40-10-2-10.in")
+    p = subprocess.run([exe, src], capture_output=True, text=True)
+    assert p.returncode == 0 and p.stdout == load_out("inst30-40-10-2-10")
+    dump = tmp_path / "lr.bin"
+    p = subprocess.run([exe, src], capture_output=True, text=True,
+                       env=dict(os.environ, MATFACT_DUMP=str(dump), MATFACT_TIMING="1"))
+    assert p.returncode == 0 and "loop_ms" in p.stderr
+    assert p.stdout == load_out("inst30-40-10-2-10")
+    assert dump.stat().st_size == (30 + 40) * 10 * 8
+
+
+@pytest.mark.parametrize("nshards", [2, 4, 8])
+def test_multi_gpu_matches_sharded_oracle(gpu, oracle, nshards):
+    """One process, N GPUs, peer exchange in shard order == oracle N-shard ordering, bit for bit."""
+    if gpu.device_count() < nshards:
+        pytest.skip("needs %d GPUs" % nshards)
+    inst = synth.random_instance(300, 200, 20, 0.1, 25, 0.002, seed=33)
+    cut = gpu.split_users(inst.users, inst.entries, nshards)
+    L0, R0 = oracle.init_LR(inst.users, inst.items, inst.features)
+    L1, R1 = L0.copy(), R0.copy()
+    oracle.factorize_sharded(inst.users, inst.items, inst.features, inst.entries, inst.iters,
+                             inst.alpha, L0, R0, cut)
+    with gpu.Plan(inst.users, inst.items, inst.features, inst.entries, inst.alpha, ngpus=nshards) as plan:
+        plan.set_factors(L1, R1)
+        plan.iterate(inst.iters)
+        plan.get_factors(L1, R1)
+        best = plan.recommend()
+    assert bits_equal(L0, L1) and bits_equal(R0, R1)
+    assert np.array_equal(best, oracle.recommend(inst.users, inst.items, inst.features,
+                                                 inst.entries, L0, R0))
