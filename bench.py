@@ -1,0 +1,380 @@
+#!/usr/bin/env python
+"""bench.py -- nonzero-updates/s of the factorization loop (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--impl reference]
+
+A "step" is one complete factorization of the workload: T iterations of the
+hot path (matFact.c:36-53) starting from the reference's initial factors.
+`value` = nnz * T * K / device time of the K steps, inputs resident in HBM.
+`e2e`   = the same metric through the public host-buffer call sequence
+(plan create with the COO entries, factors H2D from pinned memory, T
+iterations, factors + recommendations D2H), wall clock per step.
+Under torchrun (N > 1) every rank owns a contiguous user range, R is
+replicated and the partial R gradient is all-reduced each iteration; the
+problem size is fixed, so scaling is "strong".
+
+Workloads (BASELINE.json configs):
+  inst60000  synthetic stand-in for inst60000-2000-200-10-20 (input blob missing
+             upstream): U=60000 I=2000 F=200 nnz~0.9M, T=100.  DEFAULT: the one
+             named shape whose factors (2 x 96 MB of L) do not fit the 126 MB L2.
+  ml1m       synthetic stand-in for instML1M (blob missing): U=6040 I=3952 F=100
+             nnz=1000209, T=100
+  ml100k     the reference's samples/instML100k.in as is (T=3000, F=30)
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "nonzero-updates/sec (nnz*iters/s)"
+UNIT = "nnz*iters/s"
+
+
+def load_workload(name, iters_override=None):
+    from recommender_system_b200 import synth
+    from recommender_system_b200.io import read_instance
+    if name == "inst60000":
+        inst = synth.inst60000_like()
+        desc = "inst60000-2000-200-10-20 shape, synthetic (seed 12346): U=60000 I=2000 F=200"
+    elif name == "ml1m":
+        inst = synth.ml_like()
+        desc = "instML1M shape, synthetic (seed 12345): U=6040 I=3952 F=100"
+    elif name == "ml100k":
+        inst = read_instance(os.path.join(ROOT, "tests", "golden", "instML100k.in.gz"))
+        desc = "samples/instML100k.in (reference sample): U=943 I=1682 F=30"
+    else:
+        raise SystemExit("unknown workload %r" % name)
+    if iters_override:
+        inst.iters = iters_override
+    return inst, desc
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as fh:
+            return float(json.load(fh)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi style clock / throttle-reason samples during the timed region."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.stop_flag, self.samples, self.reasons = index, False, [], set()
+        self.sm_max = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.sm_max = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if not self.nv:
+            return
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4): "sw_power_cap",
+        }
+        while not self.stop_flag:
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, nm in names.items():
+                    if r & bit:
+                        self.reasons.add(nm)
+            except Exception:
+                pass
+            time.sleep(0.05)
+
+    def result(self):
+        self.stop_flag = True
+        if self.is_alive():
+            self.join()
+        med = float(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.sm_max, "reasons": sorted(self.reasons),
+                "samples": len(self.samples)}
+
+
+def cpu_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def time_reference(inst, kind, budget_s, threads):
+    """Loop-only nonzero-updates/s of the reference's own matrix_factorization
+    (oracle/_ref/libref_<kind>.so, see oracle/ref_driver.c) on a bounded number of
+    iterations of the same workload; the call's trailing mat2d_prod is removed by
+    subtracting a 0-iteration call.  Falls back to the oracle port if the
+    reference could not be compiled here."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import pyoracle
+    os.environ["OMP_NUM_THREADS"] = str(threads)
+    os.environ.setdefault("OMP_PROC_BIND", "close")
+    U, I, F = inst.users, inst.items, inst.features
+    L0, R0 = pyoracle.init_LR(U, I, F)
+    if pyoracle.ref_available(kind):
+        def call(n):
+            L, R = L0.copy(), R0.copy()
+            return pyoracle.ref_factorize(kind, U, I, F, inst.entries, n, inst.alpha, L, R)
+        label = "reference"
+    else:
+        def call(n):
+            L, R = L0.copy(), R0.copy()
+            t0 = time.perf_counter()
+            pyoracle.factorize(U, I, F, inst.entries, n, inst.alpha, L, R)
+            return time.perf_counter() - t0
+        label, threads = "port", 1
+    t_zero = min(call(0), call(0))
+    t_two = call(2)
+    per_iter = max((t_two - t_zero) / 2, 1e-6)
+    n = int(max(2, min(inst.iters, budget_s / per_iter)))
+    t_n = call(n)
+    loop_s = max(t_n - t_zero, 1e-9)
+    return {"value": inst.nnz * n / loop_s, "unit": UNIT, "cores": threads, "kind": label,
+            "sample": "%d of %d iterations of the same workload, %s matrix_factorization "
+                      "(%.2f s; 0-iteration call of %.2f s subtracted)"
+                      % (n, inst.iters, "matFact-omp.c" if kind == "omp" else "matFact.c", loop_s, t_zero)}
+
+
+def kernel_bytes(F, U_t, I_t, nnz):
+    """Algorithmic (compulsory) HBM bytes of ONE launch of each loop kernel, DESIGN.md section 4:
+    by-user pass : L row read + written once, every touched R row read once, per nonzero
+                   item index + rating + by-item position read and e written (4+8+4+8);
+    by-item pass : R row read + written once, every touched L row read once, per nonzero
+                   user index + e read (4+8).
+    iteration    : SURVEY.md 8(d) figure 16*F*(U_t+I_t) + 12*nnz (one fused pass; stricter)."""
+    k1 = 16 * F * U_t + 8 * F * I_t + 24 * nnz
+    k2 = 16 * F * I_t + 8 * F * U_t + 12 * nnz
+    it = 16 * F * (U_t + I_t) + 12 * nnz
+    return k1, k2, it
+
+
+def ncu_traffic(workload, kernel):
+    p = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if not os.path.exists(p):
+        return None
+    with open(p) as fh:
+        return json.load(fh).get(workload, {}).get(kernel)
+
+
+def run_reference_arm(args, rank):
+    if rank != 0:
+        return
+    inst, desc = load_workload(args.workload, args.iters)
+    threads = cpu_threads()
+    budget = max(2.0, min(20.0, 150.0 / max(1, args.steps + args.warmup)))
+    for _ in range(min(args.warmup, 1)):
+        time_reference(inst, "omp", 2.0, threads)
+    vals, last = [], None
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        last = time_reference(inst, "omp", budget, threads)
+        vals.append(last["value"])
+        if time.perf_counter() - t0 > 240:
+            break
+    v = float(np.mean(vals))
+    last["value"] = v
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": len(vals), "warmup": args.warmup,
+            "ms_per_step": 1e3 * inst.nnz * inst.iters / v, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic"
+            if args.workload != "ml100k" else "reference sample file",
+            "config": {"workload": desc, "iters": inst.iters, "nnz": inst.nnz,
+                       "note": "reference CPU implementation (OpenMP, all host threads); "
+                               "ms_per_step extrapolated to the full iteration count"},
+            "cpu_baseline": last,
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="inst60000", choices=["inst60000", "ml1m", "ml100k"])
+    ap.add_argument("--iters", type=int, default=None, help="override the workload's iteration count")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--option", action="append", default=[], help="plan option name=value")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference_arm(args, rank)
+        return
+
+    import torch
+    import torch.distributed as dist
+    from recommender_system_b200 import api
+
+    if api.device_count() < 1:
+        raise SystemExit("bench.py: no B200 visible and there is no CPU path")
+    inst, desc = load_workload(args.workload, args.iters)
+    U, I, F, T = inst.users, inst.items, inst.features, inst.iters
+    torch.cuda.set_device(local)
+    comm = None
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        uid = torch.zeros(api.UID_BYTES, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            uid.copy_(torch.frombuffer(bytearray(api.Comm.unique_id()), dtype=torch.uint8))
+        dist.broadcast(uid, 0)
+        comm = api.Comm(world, rank, bytes(uid.cpu().numpy().tobytes()), local)
+    n_gpus = world if world > 1 else args.gpus
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # the reference's host-side initialisation, kept in pinned memory for the e2e legs
+    L0, R0 = api.random_fill_LR(U, I, F)
+    Lp = torch.empty((U, F), dtype=torch.float64, pin_memory=True).numpy()
+    Rp = torch.empty((I, F), dtype=torch.float64, pin_memory=True).numpy()
+    Lo = torch.empty((U, F), dtype=torch.float64, pin_memory=True).numpy()
+    Ro = torch.empty((I, F), dtype=torch.float64, pin_memory=True).numpy()
+    Lp[...] = L0
+    Rp[...] = R0
+
+    def make_plan():
+        pl = api.Plan(U, I, F, inst.entries, inst.alpha, ngpus=(1 if comm else args.gpus), comm=comm)
+        for kv in args.option:
+            k, v = kv.split("=")
+            pl.set_option(k, int(v))
+        return pl
+
+    # ---- device-resident leg: `value` -------------------------------------------------
+    plan = make_plan()
+    plan.set_factors(Lp, Rp)
+    plan.save_factors()
+    for _ in range(args.warmup):
+        plan.restore_factors()
+        plan.iterate(T)
+    plan.sync()
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    launches0 = plan.launch_count()
+    plan.timer_start()
+    for _ in range(args.steps):
+        plan.restore_factors()
+        plan.iterate(T)
+    region_ms = plan.timer_stop()
+    barrier()
+    clocks = sampler.result()
+    region_ms = max_over_ranks(region_ms)
+    launches = plan.launch_count() - launches0
+    value = inst.nnz * T * args.steps / (region_ms * 1e-3)
+
+    # per-kernel device times for the roofline (all ranks: the exchange is collective)
+    k_ms = plan.profile_kernels(20)
+    lo, hi = plan.user_range(0)
+    e = inst.entries
+    mine = e[(e["row"] >= lo) & (e["row"] < hi)] if (comm or args.gpus == 1) else e
+    U_t, I_t = len(np.unique(mine["row"])), len(np.unique(mine["col"]))
+    b1, b2, b_it = kernel_bytes(F, U_t, I_t, len(mine))
+    peak, peak_src = peaks()
+    dom = 0 if k_ms[0] >= k_ms[1] else 1
+    dom_name = ["k_update_L", "k_update_R"][dom]
+    dom_bytes = [b1, b2][dom]
+    ach = dom_bytes / (k_ms[dom] * 1e-3) / 1e9 if k_ms[dom] > 0 else 0.0
+    it_ms = region_ms / (args.steps * T)
+    roofline = {"bound": "hbm", "kernel": dom_name, "achieved": ach, "peak": peak, "unit": "GB/s",
+                "frac": ach / peak, "traffic": ncu_traffic(args.workload, dom_name),
+                "peak_source": peak_src, "algorithmic_bytes_per_launch": dom_bytes,
+                "kernel_ms": {"k_update_L": k_ms[0], "k_update_R": k_ms[1], "exchange_apply": k_ms[2]},
+                "iteration": {"algorithmic_bytes": b_it, "ms": it_ms,
+                              "achieved": b_it / (it_ms * 1e-3) / 1e9,
+                              "frac": b_it / (it_ms * 1e-3) / 1e9 / peak}}
+    # determinism check outside the timed region: the K-th factorization equals the first
+    best = plan.recommend()
+    plan.close()
+
+    # ---- end-to-end leg: host buffers in, host buffers out, every step ------------------
+    e2e_steps = max(3, min(args.steps, 10))
+    best2 = np.full(U, -2, dtype=np.int32)
+
+    def e2e_step():
+        pl = make_plan()
+        pl.set_factors(Lp, Rp)
+        pl.iterate(T)
+        pl.get_factors(Lo, Ro)
+        pl.recommend(best2)
+        pl.close()
+
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    barrier()
+    e2e_s = max_over_ranks(time.perf_counter() - t0)
+    e2e_value = inst.nnz * T * e2e_steps / e2e_s
+    nu = hi - lo if (comm or args.gpus == 1) else U
+    nloc = len(mine)
+    h2d = nloc * (4 + 8 + 4 + 4) + nloc * 4 + 4 * (2 * U + 2 + U_t + I_t) * 2 + 8 * F * (nu + I)
+    d2h = 8 * F * (nu + I) + 4 * nu
+    if not np.array_equal(best[lo:hi] if comm else best, best2[lo:hi] if comm else best2):
+        raise SystemExit("bench.py: device-resident and end-to-end legs disagree")
+
+    cpu = None
+    if rank == 0 and n_gpus == 1 and not args.no_cpu_baseline:
+        cpu = time_reference(inst, "omp", 15.0, cpu_threads())
+    if comm:
+        comm.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank != 0:
+        return
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": region_ms / args.steps, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic" if args.workload != "ml100k" else "reference sample file",
+            "config": {"workload": desc, "iters": T, "nnz": inst.nnz, "alpha": inst.alpha,
+                       "sharding": "users" if n_gpus > 1 else "none",
+                       "exchange": ("nccl allreduce of the R gradient" if comm else
+                                    "peer-memory reduce in shard order") if n_gpus > 1 else "none",
+                       "l2": "factor buffers %.0f MB vs 126 MB L2; no flush (the loop re-reads "
+                             "its own output by construction)" % (32e-6 * F * (U + I))},
+            "roofline": roofline, "cpu_baseline": cpu,
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+                    "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
+                    "ms_per_step": 1e3 * e2e_s / e2e_steps},
+            "gpu_launches": int(launches), "clocks": clocks}
+    print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    main()

@@ -116,6 +116,21 @@ long long mfgpu_plan_launch_count(mfgpu_plan *plan);
 /* Algorithmic bytes of ONE iteration, SURVEY.md section 8(d):
  * 16*F*(U_t + I_t) + 12*nnz, with U_t / I_t the users / items having >=1 nonzero. */
 long long mfgpu_plan_bytes_per_iter(mfgpu_plan *plan);
+/* Keep a device-side copy of the current factors / put that copy back (both
+ * buffers).  Lets a benchmark repeat the same factorization without a host
+ * round trip; the copy is allocated on the first save. */
+int mfgpu_plan_save_factors(mfgpu_plan *plan);
+int mfgpu_plan_restore_factors(mfgpu_plan *plan);
+/* Average device time (CUDA events on the plan's stream, shard 0) of `reps`
+ * back-to-back launches of each loop kernel on the current factors; the factors
+ * are left unchanged.  ms[0] = by-user pass (k_update_L), ms[1] = by-item pass
+ * (k_update_R), ms[2] = exchange + apply (N shards, else 0). */
+int mfgpu_plan_profile_kernels(mfgpu_plan *plan, int reps, float ms[3]);
+/* Device stopwatch on the plan's stream(s): start records an event, stop records
+ * another, waits for it and returns the elapsed device time (max over the
+ * plan's devices).  Everything enqueued on the plan in between is covered. */
+int mfgpu_plan_timer_start(mfgpu_plan *plan);
+int mfgpu_plan_timer_stop(mfgpu_plan *plan, float *ms);
 /* Tuning knob for experiments: name = "l_warps", "r_warps", "graph" ... */
 int mfgpu_plan_set_option(mfgpu_plan *plan, const char *name, int value);
 

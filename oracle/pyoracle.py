@@ -94,3 +94,35 @@ def run_instance(inst):
     factorize(inst.users, inst.items, inst.features, inst.entries, inst.iters, inst.alpha, L, R)
     best = recommend(inst.users, inst.items, inst.features, inst.entries, L, R)
     return L, R, best
+
+
+# ---- the UNMODIFIED reference, in process (oracle/_ref/libref_*.so) -------------------
+
+_ref_libs = {}
+
+
+def ref_available(kind="serial"):
+    return os.path.exists(os.path.join(REF_DIR, "libref_%s.so" % kind))
+
+
+def _ref_lib(kind):
+    if kind not in _ref_libs:
+        L = ctypes.CDLL(os.path.join(REF_DIR, "libref_%s.so" % kind))
+        i = ctypes.c_int
+        L.ref_factorize.argtypes = [i, i, i, i, ctypes.c_void_p, i, ctypes.c_double,
+                                    ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double)]
+        L.ref_factorize.restype = ctypes.c_double
+        _ref_libs[kind] = L
+    return _ref_libs[kind]
+
+
+def ref_factorize(kind, users, items, features, entries, iters, alpha, L, R):
+    """The reference's own matrix_factorization (kind: 'serial' = matFact.c:29-59,
+    'omp' = matFact-omp.c:35-144; OMP_NUM_THREADS picks its threads) on L, R in
+    place.  Returns the seconds of the call (includes its trailing mat2d_prod)."""
+    entries = np.ascontiguousarray(entries)
+    s = _ref_lib(kind).ref_factorize(users, items, features, len(entries), entries.ctypes.data,
+                                     iters, alpha, _dp(L), _dp(R))
+    if s < 0:
+        raise MemoryError("ref_factorize")
+    return s

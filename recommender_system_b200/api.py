@@ -29,7 +29,8 @@ EXPORTS = [
     "mfgpu_plan_set_factors", "mfgpu_plan_get_factors", "mfgpu_plan_iterate", "mfgpu_plan_sync",
     "mfgpu_plan_last_loop_ms", "mfgpu_plan_recommend", "mfgpu_plan_last_recommend_ms",
     "mfgpu_plan_user_range", "mfgpu_plan_launch_count", "mfgpu_plan_bytes_per_iter",
-    "mfgpu_plan_set_option",
+    "mfgpu_plan_set_option", "mfgpu_plan_save_factors", "mfgpu_plan_restore_factors",
+    "mfgpu_plan_profile_kernels", "mfgpu_plan_timer_start", "mfgpu_plan_timer_stop",
     "mfgpu_comm_unique_id", "mfgpu_comm_create", "mfgpu_comm_destroy",
     "mfgpu_split_users", "mfgpu_random_fill_LR", "mfgpu_mask_stats",
 ]
@@ -79,6 +80,11 @@ def lib():
     L.mfgpu_plan_bytes_per_iter.argtypes = [vp]
     L.mfgpu_plan_bytes_per_iter.restype = ctypes.c_longlong
     L.mfgpu_plan_set_option.argtypes = [vp, cp, i]
+    L.mfgpu_plan_save_factors.argtypes = [vp]
+    L.mfgpu_plan_restore_factors.argtypes = [vp]
+    L.mfgpu_plan_profile_kernels.argtypes = [vp, i, ctypes.POINTER(ctypes.c_float)]
+    L.mfgpu_plan_timer_start.argtypes = [vp]
+    L.mfgpu_plan_timer_stop.argtypes = [vp, ctypes.POINTER(ctypes.c_float)]
     L.mfgpu_comm_unique_id.argtypes = [vp]
     L.mfgpu_comm_create.argtypes = [pp, i, i, vp, i]
     L.mfgpu_comm_destroy.argtypes = [vp]
@@ -262,6 +268,25 @@ class Plan:
 
     def set_option(self, name, value):
         _check(lib().mfgpu_plan_set_option(self._h, name.encode(), int(value)))
+
+    def timer_start(self):
+        _check(lib().mfgpu_plan_timer_start(self._h))
+
+    def timer_stop(self) -> float:
+        ms = ctypes.c_float()
+        _check(lib().mfgpu_plan_timer_stop(self._h, ctypes.byref(ms)))
+        return ms.value
+
+    def save_factors(self):
+        _check(lib().mfgpu_plan_save_factors(self._h))
+
+    def restore_factors(self):
+        _check(lib().mfgpu_plan_restore_factors(self._h))
+
+    def profile_kernels(self, reps=20):
+        ms = (ctypes.c_float * 3)()
+        _check(lib().mfgpu_plan_profile_kernels(self._h, reps, ms))
+        return [ms[0], ms[1], ms[2]]
 
     def close(self):
         if self._h:

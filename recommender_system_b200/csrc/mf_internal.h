@@ -44,12 +44,13 @@ struct mf_shard {
 	/* factors, double buffered; L holds the shard's users only */
 	double *L[2], *R[2];
 	double *G[2];                            /* N-shard only: partial R gradient */
+	double *L_keep, *R_keep;                 /* mfgpu_plan_save_factors           */
 	mf::LoopArgs la;
 	int warps;                               /* 8 or 1: k_update_L template      */
 	int k1_blocks, k2_blocks;
 	size_t k1_smem;
 	cudaGraphExec_t gexec[2];                /* by starting parity                */
-	cudaEvent_t ev0, ev1, ev_g[2];
+	cudaEvent_t ev0, ev1, ev_g[2], ev_t0, ev_t1;
 	/* arg-max scratch */
 	double *part_v;
 	int *part_j, *nan_first, *d_best;

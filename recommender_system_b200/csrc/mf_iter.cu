@@ -232,6 +232,49 @@ extern "C" int mfgpu_plan_last_loop_ms(mfgpu_plan *pl, float *ms)
 	return MFGPU_OK;
 }
 
+/* Per-kernel device times for the roofline report of bench.py. */
+extern "C" int mfgpu_plan_profile_kernels(mfgpu_plan *pl, int reps, float ms[3])
+{
+	if (!pl || !ms || reps < 1)
+		return mf_fail(MFGPU_EINVAL, "bad argument");
+	if (!pl->have_factors)
+		return mf_fail(MFGPU_EINVAL, "mfgpu_plan_set_factors has not been called");
+	ms[0] = ms[1] = ms[2] = 0.f;
+	if (pl->F == 0 || pl->nnz == 0)
+		return MFGPU_OK;
+	mf_shard *s = &pl->sh[0];
+	const int c = pl->cur;
+	const long long before = pl->launches;
+	CK(cudaSetDevice(s->dev));
+	double *rout = pl->nshards == 1 ? s->R[1 - c] : s->G[0];
+	for (int phase = 0; phase < 3; phase++) {
+		if (phase == 2 && !(pl->comm && (size_t)pl->n_touched * pl->ld > 0))
+			break;
+		CK(cudaEventRecord(s->ev0, s->st));
+		for (int r = 0; r < reps; r++) {
+			if (phase == 0)
+				TRY(launch_update_L(pl, s, c));
+			else if (phase == 1)
+				TRY(launch_update_R(pl, s, c, rout));
+			else {
+				NCK(g_nccl.AllReduce(s->G[0], s->G[1], (size_t)pl->n_touched * pl->ld, 8, 0,
+				                     pl->comm->nccl, s->st));
+				const long total = (long)pl->n_touched * pl->F;
+				mf::k_apply_R<<<(unsigned)((total + 255) / 256), 256, 0, s->st>>>(
+				    pl->n_touched, pl->F, pl->ld, s->d_touched_item, s->R[c], s->G[1], s->R[1 - c]);
+				CK(cudaGetLastError());
+			}
+		}
+		CK(cudaEventRecord(s->ev1, s->st));
+		CK(cudaEventSynchronize(s->ev1));
+		float t = 0.f;
+		CK(cudaEventElapsedTime(&t, s->ev0, s->ev1));
+		ms[phase] = t / reps;
+	}
+	pl->launches = before;     /* diagnostic launches are not part of any timed step */
+	return MFGPU_OK;
+}
+
 /* ---- masked arg-max -------------------------------------------------------------- */
 
 extern "C" int mfgpu_plan_recommend(mfgpu_plan *pl, int *best)

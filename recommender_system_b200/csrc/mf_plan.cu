@@ -123,6 +123,8 @@ static int shard_create(mfgpu_plan *pl, mf_shard *s, int dev, const mfgpu_entry 
 	CK(cudaStreamCreateWithFlags(&s->st, cudaStreamNonBlocking));
 	CK(cudaEventCreate(&s->ev0));
 	CK(cudaEventCreate(&s->ev1));
+	CK(cudaEventCreate(&s->ev_t0));
+	CK(cudaEventCreate(&s->ev_t1));
 	for (int g = 0; g < 2; g++)
 		CK(cudaEventCreateWithFlags(&s->ev_g[g], cudaEventDisableTiming));
 	int rc = mf_pattern_build(&s->pat, pl->users, pl->items, pl->nnz, entries, s->user_lo, s->user_hi);
@@ -192,11 +194,13 @@ static void shard_destroy(mf_shard *s)
 	void *ptrs[] = {s->d_row_id, s->d_row_ptr, s->d_col_idx, s->d_epos, s->d_col_id, s->d_col_ptr,
 	                s->d_row_idx, s->d_val, s->d_e_csc, s->d_e_csr, s->d_mask_ptr, s->d_mask_col,
 	                s->d_first_free, s->d_item_slot, s->d_touched_item, s->part_v, s->part_j,
-	                s->nan_first, s->d_best};
+	                s->nan_first, s->d_best, s->L_keep, s->R_keep};
 	for (void *q : ptrs)
 		cudaFree(q);
 	if (s->ev0) cudaEventDestroy(s->ev0);
 	if (s->ev1) cudaEventDestroy(s->ev1);
+	if (s->ev_t0) cudaEventDestroy(s->ev_t0);
+	if (s->ev_t1) cudaEventDestroy(s->ev_t1);
 	if (s->st) cudaStreamDestroy(s->st);
 	mf_pattern_free(&s->pat);
 	cudaGetLastError();
@@ -434,5 +438,70 @@ extern "C" int mfgpu_plan_set_option(mfgpu_plan *pl, const char *name, int value
 		CK(cudaStreamSynchronize(pl->sh[g].st));
 		TRY(mf_configure_shard(pl, &pl->sh[g]));
 	}
+	return MFGPU_OK;
+}
+
+extern "C" int mfgpu_plan_save_factors(mfgpu_plan *pl)
+{
+	if (!pl || !pl->have_factors)
+		return mf_fail(MFGPU_EINVAL, "no factors to save");
+	for (int g = 0; g < local_shards(pl); g++) {
+		mf_shard *s = &pl->sh[g];
+		CK(cudaSetDevice(s->dev));
+		const size_t lb = ((size_t)(s->user_hi - s->user_lo) * pl->ld + 2) * sizeof(double);
+		const size_t rb = ((size_t)pl->items * pl->ld + 2) * sizeof(double);
+		if (!s->L_keep) CK(cudaMalloc((void **)&s->L_keep, lb));
+		if (!s->R_keep) CK(cudaMalloc((void **)&s->R_keep, rb));
+		CK(cudaMemcpyAsync(s->L_keep, s->L[pl->cur], lb, cudaMemcpyDeviceToDevice, s->st));
+		CK(cudaMemcpyAsync(s->R_keep, s->R[pl->cur], rb, cudaMemcpyDeviceToDevice, s->st));
+	}
+	return MFGPU_OK;
+}
+
+extern "C" int mfgpu_plan_restore_factors(mfgpu_plan *pl)
+{
+	if (!pl || !pl->sh[0].L_keep)
+		return mf_fail(MFGPU_EINVAL, "mfgpu_plan_save_factors has not been called");
+	for (int g = 0; g < local_shards(pl); g++) {
+		mf_shard *s = &pl->sh[g];
+		CK(cudaSetDevice(s->dev));
+		const size_t lb = ((size_t)(s->user_hi - s->user_lo) * pl->ld + 2) * sizeof(double);
+		const size_t rb = ((size_t)pl->items * pl->ld + 2) * sizeof(double);
+		for (int b = 0; b < 2; b++) {
+			CK(cudaMemcpyAsync(s->L[b], s->L_keep, lb, cudaMemcpyDeviceToDevice, s->st));
+			CK(cudaMemcpyAsync(s->R[b], s->R_keep, rb, cudaMemcpyDeviceToDevice, s->st));
+		}
+	}
+	return MFGPU_OK;
+}
+
+extern "C" int mfgpu_plan_timer_start(mfgpu_plan *pl)
+{
+	if (!pl)
+		return mf_fail(MFGPU_EINVAL, "null plan");
+	for (int g = 0; g < local_shards(pl); g++) {
+		CK(cudaSetDevice(pl->sh[g].dev));
+		CK(cudaEventRecord(pl->sh[g].ev_t0, pl->sh[g].st));
+	}
+	return MFGPU_OK;
+}
+
+extern "C" int mfgpu_plan_timer_stop(mfgpu_plan *pl, float *ms)
+{
+	if (!pl || !ms)
+		return mf_fail(MFGPU_EINVAL, "null argument");
+	for (int g = 0; g < local_shards(pl); g++) {
+		CK(cudaSetDevice(pl->sh[g].dev));
+		CK(cudaEventRecord(pl->sh[g].ev_t1, pl->sh[g].st));
+	}
+	float worst = 0.f;
+	for (int g = 0; g < local_shards(pl); g++) {
+		CK(cudaSetDevice(pl->sh[g].dev));
+		CK(cudaEventSynchronize(pl->sh[g].ev_t1));
+		float t = 0.f;
+		CK(cudaEventElapsedTime(&t, pl->sh[g].ev_t0, pl->sh[g].ev_t1));
+		worst = std::max(worst, t);
+	}
+	*ms = worst;
 	return MFGPU_OK;
 }
