@@ -51,12 +51,19 @@ k_apply_R_peer(int n_touched, int F, int ld, const int *__restrict__ touched_ite
 
 } // namespace mf
 
-int mf_k1_prepare(int warps, size_t smem)
+int mf_kernels_prepare(int warps, size_t k1_smem, int tpb, size_t k2_smem)
 {
+	const auto attr = cudaFuncAttributeMaxDynamicSharedMemorySize;
 	if (warps == 8)
-		CK(cudaFuncSetAttribute(mf::k_update_L<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		CK(cudaFuncSetAttribute(mf::k_update_L<8>, attr, (int)k1_smem));
 	else
-		CK(cudaFuncSetAttribute(mf::k_update_L<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		CK(cudaFuncSetAttribute(mf::k_update_L<1>, attr, (int)k1_smem));
+	switch (tpb) {
+	case 32: CK(cudaFuncSetAttribute(mf::k_update_R<32>, attr, (int)k2_smem)); break;
+	case 64: CK(cudaFuncSetAttribute(mf::k_update_R<64>, attr, (int)k2_smem)); break;
+	case 128: CK(cudaFuncSetAttribute(mf::k_update_R<128>, attr, (int)k2_smem)); break;
+	default: CK(cudaFuncSetAttribute(mf::k_update_R<256>, attr, (int)k2_smem)); break;
+	}
 	return MFGPU_OK;
 }
 
@@ -81,7 +88,12 @@ static int launch_update_R(mfgpu_plan *pl, mf_shard *s, int c, double *out)
 {
 	if (s->k2_blocks <= 0)
 		return MFGPU_OK;
-	mf::k_update_R<8><<<s->k2_blocks, 256, 0, s->st>>>(s->la, s->L[c], s->R[c], out);
+	switch (s->la.tpb) {
+	case 32: mf::k_update_R<32><<<s->k2_blocks, 32, s->k2_smem, s->st>>>(s->la, s->L[c], s->R[c], out); break;
+	case 64: mf::k_update_R<64><<<s->k2_blocks, 64, s->k2_smem, s->st>>>(s->la, s->L[c], s->R[c], out); break;
+	case 128: mf::k_update_R<128><<<s->k2_blocks, 128, s->k2_smem, s->st>>>(s->la, s->L[c], s->R[c], out); break;
+	default: mf::k_update_R<256><<<s->k2_blocks, 256, s->k2_smem, s->st>>>(s->la, s->L[c], s->R[c], out); break;
+	}
 	CK(cudaGetLastError());
 	pl->launches++;
 	return MFGPU_OK;

@@ -46,42 +46,67 @@ int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
 		S = 2;
 	int max_smem = 0;
 	CK(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, s->dev));
+	const size_t bar_bytes = 128;     /* mf::BAR_BYTES */
 	const int want = pl->opt_ch > 0 ? pl->opt_ch : 32;
 	int ch_cap = std::min(32, pow2_ceil(std::max(1, s->pat.max_row_len)));
 	ch_cap = std::min(ch_cap, pow2_ceil(want));
+	/* lanes of the dot phase = nonzeros staged per chunk: take the largest chunk that fits */
 	int warps = 8, CH = 0;
-	/* prefer two resident CTAs per SM, then one, then a single-warp CTA */
-	const size_t budgets[2] = {(size_t)100 * 1024, (size_t)max_smem};
-	for (int b = 0; b < 2 && !CH; b++)
-		for (int ch = ch_cap; ch >= 1; ch >>= 1) {
-			size_t bytes = (size_t)warps * ((size_t)ch * S + S + 32) * sizeof(double);
-			if (bytes <= budgets[b] && (b == 1 || ch >= std::min(ch_cap, 8))) {
-				CH = ch;
-				break;
-			}
-		}
-	if (!CH) {
-		warps = 1;
+	for (int w = 8; w >= 1 && !CH; w = (w == 8 ? 1 : 0)) {
 		for (int ch = ch_cap; ch >= 1; ch >>= 1)
-			if (((size_t)ch * S + S + 32) * sizeof(double) <= (size_t)max_smem) {
+			if (bar_bytes + (size_t)w * ((size_t)ch * S + S + 32) * sizeof(double) <= (size_t)max_smem) {
 				CH = ch;
+				warps = w;
 				break;
 			}
 	}
 	if (!CH)
 		return mf_fail(MFGPU_EINVAL, "features=%d does not fit the shared-memory staging (%d bytes)",
 		               F, max_smem);
+	const size_t data_doubles = (size_t)warps * ((size_t)CH * S + S + 32);
 	s->warps = warps;
-	s->k1_smem = (size_t)warps * ((size_t)CH * S + S + 32) * sizeof(double);
-	TRY(mf_k1_prepare(warps, s->k1_smem));
+	s->k1_smem = bar_bytes + data_doubles * sizeof(double);
+
+	/* ring of the whole-CTA rows lives in the staging area: stages of rb rows of <= 256 features */
+	int rb_long = std::max(1, std::min(32, pl->opt_ring_rows > 0 ? pl->opt_ring_rows : 16)), nst_long = 0;
+	{
+		const size_t seg = (size_t)std::min(256, pl->ld);
+		for (; rb_long >= 1; rb_long >>= 1) {
+			nst_long = (int)std::min<size_t>(8, data_doubles / ((size_t)rb_long * (seg + 1)));
+			if (pl->opt_ring_stages > 0)
+				nst_long = std::min(nst_long, std::max(2, pl->opt_ring_stages));
+			if (nst_long >= 2)
+				break;
+		}
+		if (rb_long < 1) { rb_long = 1; nst_long = 0; }
+	}
 
 	/* rows longer than the threshold get a whole CTA (their dots run on all warps) */
 	const int thresh = pl->opt_long_row > 0 ? pl->opt_long_row : std::max(8 * CH, 64);
 	int n_long = 0;
-	if (warps > 1)
+	if (warps > 1 && nst_long >= 2)
 		while (n_long < s->pat.n_rows &&
 		       s->pat.row_ptr[n_long + 1] - s->pat.row_ptr[n_long] > thresh)
 			n_long++;
+
+	/* by-item pass: thread = feature, ring of L rows */
+	const int tpb = F <= 32 ? 32 : F <= 64 ? 64 : F <= 128 ? 128 : 256;
+	const int nfb = std::max(1, (F + tpb - 1) / tpb);
+	int rb = std::max(1, std::min(32, pl->opt_ring_rows > 0 ? pl->opt_ring_rows : 16));
+	int nst = std::max(2, std::min(8, pl->opt_ring_stages > 0 ? pl->opt_ring_stages : 4));
+	const size_t seg2 = (size_t)std::min(tpb, pl->ld);
+	auto k2_bytes = [&](int r, int n) { return bar_bytes + (size_t)n * r * (seg2 + 1) * sizeof(double); };
+	const size_t k2_budget = pl->opt_ring_rows > 0 ? (size_t)max_smem : (size_t)64 * 1024;
+	while (k2_bytes(rb, nst) > k2_budget) {
+		if (nst > 3) nst--;
+		else if (rb > 1) rb >>= 1;
+		else if (nst > 2) nst--;
+		else break;
+	}
+	if (k2_bytes(rb, nst) > (size_t)max_smem)
+		return mf_fail(MFGPU_EINVAL, "features=%d: ring does not fit shared memory", F);
+	s->k2_smem = k2_bytes(rb, nst);
+	TRY(mf_kernels_prepare(warps, s->k1_smem, tpb, s->k2_smem));
 
 	mf::LoopArgs &a = s->la;
 	a.F = F;
@@ -91,6 +116,12 @@ int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
 	a.n_rows = s->pat.n_rows;
 	a.n_long = n_long;
 	a.n_cols = s->pat.n_cols;
+	a.rb = rb;
+	a.nst = nst;
+	a.tpb = tpb;
+	a.nfb = nfb;
+	a.rb_long = rb_long;
+	a.nst_long = nst_long;
 	a.user_lo = s->user_lo;
 	a.alpha2 = pl->alpha * 2;     /* matFact.c:45: alpha * 2 * (...) associates left, exact */
 	a.row_id = s->d_row_id;
@@ -105,8 +136,9 @@ int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
 	a.e_csc = s->d_e_csc;
 	a.e_csr = s->d_e_csr;
 	s->k1_blocks = n_long + (a.n_rows - n_long + warps - 1) / warps;
-	const long k2_warps = (long)a.n_cols * ((F + 31) / 32);
-	s->k2_blocks = (int)((k2_warps + 7) / 8);
+	if ((long)a.n_cols * nfb > 2147483647L)
+		return mf_fail(MFGPU_EINVAL, "too many (item, feature block) work items");
+	s->k2_blocks = a.n_cols * nfb;
 	for (int g = 0; g < 2; g++)
 		if (s->gexec[g]) {
 			cudaGraphExecDestroy(s->gexec[g]);
@@ -431,6 +463,8 @@ extern "C" int mfgpu_plan_set_option(mfgpu_plan *pl, const char *name, int value
 	else if (!strcmp(name, "graph_iters")) pl->opt_graph_iters = std::max(2, value & ~1);
 	else if (!strcmp(name, "long_row")) pl->opt_long_row = value;
 	else if (!strcmp(name, "chunk")) pl->opt_ch = value;
+	else if (!strcmp(name, "ring_rows")) pl->opt_ring_rows = value;
+	else if (!strcmp(name, "ring_stages")) pl->opt_ring_stages = value;
 	else
 		return mf_fail(MFGPU_EINVAL, "unknown option '%s'", name);
 	for (int g = 0; g < local_shards(pl); g++) {
