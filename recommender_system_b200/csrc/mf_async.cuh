@@ -1,12 +1,12 @@
 /*
- * csrc/mf_async.cuh -- mbarrier + bulk-copy (TMA 1-D) primitives for sm_100a.
+ * csrc/mf_async.cuh -- asynchronous global -> shared copies for sm_100a.
  *
- * The loop kernels move whole factor rows (F doubles, 16-byte aligned, a
- * multiple of 16 bytes) from global to shared memory with one
- * cp.async.bulk per row; completion is tracked by an mbarrier's transaction
- * count, so no thread holds the data in registers while it is in flight.
- * Waits are bounded: a barrier that never completes traps instead of hanging
- * the device.
+ * Factor rows are gathered (one row per nonzero, 240 B .. 8 KB each).  Measured
+ * on B200 (profiles/r01_v2_*): one cp.async.bulk (TMA) per row sustains only
+ * about one copy per ~100 cycles per SM -- 16 B/clk for 1600-byte rows -- so
+ * gathers of rows this small go through the LSU instead: 16-byte cp.async
+ * (LDGSTS), which needs no registers for the data in flight and reaches the
+ * L2 -> SM bandwidth.
  */
 #pragma once
 #include <cuda_runtime.h>
@@ -19,54 +19,21 @@ __device__ __forceinline__ uint32_t smem_u32(const void *p)
 	return (uint32_t)__cvta_generic_to_shared(p);
 }
 
-__device__ __forceinline__ void mbar_init(uint64_t *bar, int count)
+/* 16-byte asynchronous copy, L2 only (the rows are not re-read through L1) */
+__device__ __forceinline__ void cp_async16(void *dst, const void *src)
 {
-	asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+	asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
 }
 
-/* make the initialised barriers visible to the async proxy before first use */
-__device__ __forceinline__ void mbar_fence_init()
+__device__ __forceinline__ void cp_async_commit()
 {
-	asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+	asm volatile("cp.async.commit_group;" ::: "memory");
 }
 
-__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t *bar, uint32_t bytes)
+template <int N>
+__device__ __forceinline__ void cp_async_wait()
 {
-	asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
-	             : "memory");
-}
-
-__device__ __forceinline__ void mbar_arrive(uint64_t *bar)
-{
-	asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-
-__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
-{
-	const uint32_t a = smem_u32(bar);
-	uint32_t done = 0;
-	for (int spin = 0; spin < (1 << 24); spin++) {
-		asm volatile(
-		    "{\n\t.reg .pred p;\n\t"
-		    "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-		    "selp.u32 %0, 1, 0, p;\n\t}"
-		    : "=r"(done)
-		    : "r"(a), "r"(parity)
-		    : "memory");
-		if (done)
-			return;
-	}
-	__trap();   /* a copy that never lands is a bug: fail the launch, do not hang the GPU */
-}
-
-/* global -> shared, `bytes` a multiple of 16, both addresses 16-byte aligned */
-__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar)
-{
-	asm volatile(
-	    "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-	        smem_u32(dst)),
-	    "l"(src), "r"(bytes), "r"(smem_u32(bar))
-	    : "memory");
+	asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
 } // namespace mf

@@ -33,7 +33,7 @@ struct mfgpu_comm {
 
 struct mf_shard {
 	int dev;
-	cudaStream_t st;
+	cudaStream_t st, st2;                    /* st2: the long-row launch runs beside the short rows */
 	mf_pattern pat;
 	int user_lo, user_hi;
 	/* sparse pattern on the device */
@@ -48,9 +48,9 @@ struct mf_shard {
 	mf::LoopArgs la;
 	int warps;                               /* 8 or 1: k_update_L template      */
 	int k1_blocks, k2_blocks;
-	size_t k1_smem, k2_smem;
+	size_t k1_smem;
 	cudaGraphExec_t gexec[2];                /* by starting parity                */
-	cudaEvent_t ev0, ev1, ev_g[2], ev_t0, ev_t1;
+	cudaEvent_t ev0, ev1, ev_g[2], ev_t0, ev_t1, ev_fork, ev_join;
 	/* arg-max scratch */
 	double *part_v;
 	int *part_j, *nan_first, *d_best;
@@ -70,7 +70,7 @@ struct mfgpu_plan {
 	long long launches;
 	float loop_ms, rec_ms;
 	/* options */
-	int opt_graph, opt_graph_iters, opt_long_row, opt_ch, opt_ring_rows, opt_ring_stages;
+	int opt_graph, opt_graph_iters, opt_long_row, opt_ch;
 };
 
 /* ---- shared helpers (defined in mf_capi.cu) ----------------------------------- */
@@ -78,7 +78,7 @@ int mf_fail(int code, const char *fmt, ...);
 int mf_load_nccl(void);
 int mf_usable_devices(int *ids, int cap);
 int mf_configure_shard(mfgpu_plan *pl, mf_shard *s);      /* mf_plan.cu */
-int mf_kernels_prepare(int warps, size_t k1_smem, int tpb, size_t k2_smem);   /* mf_iter.cu: kernels live in that TU only */
+int mf_kernels_prepare(int warps, size_t k1_smem);   /* mf_iter.cu: kernels live in that TU only */
 extern mf_nccl_api g_nccl;
 
 #define CK(call)                                                                        \

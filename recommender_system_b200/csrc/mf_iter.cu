@@ -51,18 +51,14 @@ k_apply_R_peer(int n_touched, int F, int ld, const int *__restrict__ touched_ite
 
 } // namespace mf
 
-int mf_kernels_prepare(int warps, size_t k1_smem, int tpb, size_t k2_smem)
+int mf_kernels_prepare(int warps, size_t k1_smem)
 {
 	const auto attr = cudaFuncAttributeMaxDynamicSharedMemorySize;
-	if (warps == 8)
-		CK(cudaFuncSetAttribute(mf::k_update_L<8>, attr, (int)k1_smem));
-	else
-		CK(cudaFuncSetAttribute(mf::k_update_L<1>, attr, (int)k1_smem));
-	switch (tpb) {
-	case 32: CK(cudaFuncSetAttribute(mf::k_update_R<32>, attr, (int)k2_smem)); break;
-	case 64: CK(cudaFuncSetAttribute(mf::k_update_R<64>, attr, (int)k2_smem)); break;
-	case 128: CK(cudaFuncSetAttribute(mf::k_update_R<128>, attr, (int)k2_smem)); break;
-	default: CK(cudaFuncSetAttribute(mf::k_update_R<256>, attr, (int)k2_smem)); break;
+	if (warps == 8) {
+		CK(cudaFuncSetAttribute(mf::k_update_L<8, false>, attr, (int)k1_smem));
+		CK(cudaFuncSetAttribute(mf::k_update_L<8, true>, attr, (int)k1_smem));
+	} else {
+		CK(cudaFuncSetAttribute(mf::k_update_L<1, false>, attr, (int)k1_smem));
 	}
 	return MFGPU_OK;
 }
@@ -73,14 +69,28 @@ static int local_shards(const mfgpu_plan *pl) { return pl->comm ? 1 : pl->nshard
 
 static int launch_update_L(mfgpu_plan *pl, mf_shard *s, int c)
 {
-	if (s->k1_blocks <= 0)
-		return MFGPU_OK;
-	if (s->warps == 8)
-		mf::k_update_L<8><<<s->k1_blocks, 256, s->k1_smem, s->st>>>(s->la, s->L[c], s->L[1 - c], s->R[c]);
-	else
-		mf::k_update_L<1><<<s->k1_blocks, 32, s->k1_smem, s->st>>>(s->la, s->L[c], s->L[1 - c], s->R[c]);
-	CK(cudaGetLastError());
-	pl->launches++;
+	const int n_long = s->la.n_long;
+	if (n_long > 0) {
+		/* the few whole-CTA rows run on a second stream beside the short-row launch */
+		CK(cudaEventRecord(s->ev_fork, s->st));
+		CK(cudaStreamWaitEvent(s->st2, s->ev_fork, 0));
+		mf::k_update_L<8, true><<<n_long, 256, s->k1_smem, s->st2>>>(s->la, s->L[c], s->L[1 - c], s->R[c]);
+		CK(cudaGetLastError());
+		CK(cudaEventRecord(s->ev_join, s->st2));
+		pl->launches++;
+	}
+	if (s->k1_blocks > 0) {
+		if (s->warps == 8)
+			mf::k_update_L<8, false><<<s->k1_blocks, 256, s->k1_smem, s->st>>>(s->la, s->L[c], s->L[1 - c],
+			                                                                  s->R[c]);
+		else
+			mf::k_update_L<1, false><<<s->k1_blocks, 32, s->k1_smem, s->st>>>(s->la, s->L[c], s->L[1 - c],
+			                                                                 s->R[c]);
+		CK(cudaGetLastError());
+		pl->launches++;
+	}
+	if (n_long > 0)
+		CK(cudaStreamWaitEvent(s->st, s->ev_join, 0));
 	return MFGPU_OK;
 }
 
@@ -88,12 +98,7 @@ static int launch_update_R(mfgpu_plan *pl, mf_shard *s, int c, double *out)
 {
 	if (s->k2_blocks <= 0)
 		return MFGPU_OK;
-	switch (s->la.tpb) {
-	case 32: mf::k_update_R<32><<<s->k2_blocks, 32, s->k2_smem, s->st>>>(s->la, s->L[c], s->R[c], out); break;
-	case 64: mf::k_update_R<64><<<s->k2_blocks, 64, s->k2_smem, s->st>>>(s->la, s->L[c], s->R[c], out); break;
-	case 128: mf::k_update_R<128><<<s->k2_blocks, 128, s->k2_smem, s->st>>>(s->la, s->L[c], s->R[c], out); break;
-	default: mf::k_update_R<256><<<s->k2_blocks, 256, s->k2_smem, s->st>>>(s->la, s->L[c], s->R[c], out); break;
-	}
+	mf::k_update_R<8><<<s->k2_blocks, 256, 0, s->st>>>(s->la, s->L[c], s->R[c], out);
 	CK(cudaGetLastError());
 	pl->launches++;
 	return MFGPU_OK;
@@ -179,7 +184,7 @@ static int build_graph(mfgpu_plan *pl, mf_shard *s, int c, int n)
 
 static long long launches_per_iteration(const mfgpu_plan *pl, const mf_shard *s)
 {
-	long long n = (s->k1_blocks > 0) + (s->k2_blocks > 0);
+	long long n = (s->la.n_long > 0) + (s->k1_blocks > 0) + (s->k2_blocks > 0);
 	if (pl->nshards > 1 && (long)pl->n_touched * pl->F > 0)
 		n += 1;
 	return n;

@@ -12,18 +12,17 @@
  * order, so one GPU reproduces the reference's doubles bit for bit:
  *
  *   k_update_L  by-user pass.  A warp owns a user row: the R rows of up to CH of
- *               its nonzeros are brought to shared memory by one cp.async.bulk
- *               each (mbarrier transaction count), e_n is computed with one
- *               lane per nonzero walking k sequentially (the dot of
- *               mat2d.c:133-137), then L_new[i][k] is accumulated with lanes
- *               over features walking the nonzeros sequentially.  Rows longer
- *               than a threshold get a whole CTA: all warps compute dots, then
- *               the sequential accumulation streams the R rows through the
- *               shared-memory ring below.  Writes e_n at its by-item position.
- *   k_update_R  by-item pass.  A CTA owns (item, block of <= 256 features),
- *               thread = feature; the L rows of the item's nonzeros stream
- *               through a ring of bulk copies kept several stages ahead of the
- *               strictly sequential accumulation (file order of the column).
+ *               its nonzeros are staged in shared memory with 16-byte cp.async,
+ *               e_n is computed with one lane per nonzero walking k
+ *               sequentially (the dot of mat2d.c:133-137), then L_new[i][k] is
+ *               accumulated with lanes over features walking the nonzeros
+ *               sequentially.  Rows longer than a threshold get a whole CTA:
+ *               all warps compute dots, then every warp runs the sequential
+ *               accumulation of 32 features with the register pipeline below.
+ *               Writes e_n at its by-item position.
+ *   k_update_R  by-item pass.  A warp owns (item, 32 features) and walks the
+ *               item's nonzeros in file order; the gathered L values run two
+ *               blocks of 32 rows ahead of the accumulation in registers.
  *   k_apply_R   N shards only: R_new = R_old + G (G = sum of the partial
  *               gradients, the MPI_Iallreduce of matFact-mpi.c:208).
  *
@@ -41,8 +40,7 @@
 
 namespace mf {
 
-constexpr int RING_MAX_STAGES = 8;
-constexpr int BAR_BYTES = 128;           /* barrier block at the start of dynamic shared memory */
+constexpr unsigned FULL = 0xffffffffu;
 
 __device__ __forceinline__ double2 ld2(const double *p)
 {
@@ -64,128 +62,178 @@ __device__ __forceinline__ double seq_dot_smem(const double *Ls, const double *R
 	return s;
 }
 
-/*
- * acc = ((acc + ev[0]*src[idx[0]][k]) + ev[1]*src[idx[1]][k]) + ...   for n < m, in order.
- *
- * Called by every thread of a CTA of TPB threads; thread `tid` owns feature
- * `tid` of the `seg` doubles copied from each row (src already points at the
- * first of them).  Rows move global -> shared in stages of RB rows, one
- * cp.async.bulk per row issued by the lanes of warp 0; a stage is reused only
- * after the whole CTA passed the barrier that ends its consumption.  `sbase`
- * counts the stages ever pushed through these barriers (phase bookkeeping
- * across calls).
- */
-template <int TPB>
-__device__ __forceinline__ double chain_pipeline(double acc, bool active, int tid,
-                                                 const int *__restrict__ idx,
-                                                 const double *__restrict__ ev, int m,
-                                                 const double *__restrict__ src, int ld, int row_off,
-                                                 int seg, double *ring, double *es, uint64_t *bars,
-                                                 int RB, int NST, uint32_t &sbase)
+constexpr int KT = 16;        /* features per staged tile of the dot phase          */
+constexpr int TS = KT + 2;    /* tile row stride in doubles: TS/2 odd, so the 16-byte reads
+                                 of 8 lanes (8 rows) fall in 8 distinct bank groups   */
+
+/* Issue the asynchronous staging of features [k0, k0+KT) of `cnt` rows of `src` (row of
+ * nonzero n = lane n's `j`) into `dst`, rows TS doubles apart: 8 lanes x 16 bytes per row. */
+__device__ __forceinline__ void stage_tile(double *dst, const double *__restrict__ src, int j, int cnt,
+                                           int k0, int ld, int lane)
 {
-	const int n_stages = (m + RB - 1) / RB;
-	const uint32_t seg_bytes = (uint32_t)seg * 8u;
-	auto issue = [&](int s) {
-		if (tid < 32) {
-			const uint32_t g = sbase + (uint32_t)s;
-			const int buf = (int)(g % (uint32_t)NST);
-			const int n = s * RB + tid;
-			if (tid < RB && n < m) {
-				const int i = idx[n] - row_off;
-				es[buf * RB + tid] = ev[n];
-				mbar_arrive_expect_tx(&bars[buf], seg_bytes);
-				bulk_g2s(ring + (size_t)(buf * RB + tid) * seg, src + (size_t)i * ld, seg_bytes, &bars[buf]);
-			} else {
-				mbar_arrive(&bars[buf]);
-			}
-		}
-	};
-	for (int s = 0; s < NST && s < n_stages; s++)
-		issue(s);
-	for (int s = 0; s < n_stages; s++) {
-		const uint32_t g = sbase + (uint32_t)s;
-		const int buf = (int)(g % (uint32_t)NST);
-		mbar_wait(&bars[buf], (g / (uint32_t)NST) & 1u);
-		const int rows = min(RB, m - s * RB);
-		if (active) {
-			const double *row = ring + (size_t)buf * RB * seg + tid;
-			const double *e = es + buf * RB;
-#pragma unroll 4
-			for (int r = 0; r < rows; r++)
-				acc = __dadd_rn(acc, __dmul_rn(e[r], row[(size_t)r * seg]));
-		}
-		if (TPB == 32)
-			__syncwarp();
-		else
-			__syncthreads();
-		if (s + NST < n_stages)
-			issue(s + NST);
+	const int pieces = cnt * (KT / 2);
+	for (int p0 = 0; p0 < pieces; p0 += 32) {
+		const int p = p0 + lane;
+		const int row = min(p >> 3, cnt - 1), pc = p & 7;
+		const int jn = __shfl_sync(FULL, j, row);
+		const int kk = k0 + 2 * pc;
+		if (p < pieces && kk < ld)
+			cp_async16(dst + row * TS + 2 * pc, src + (size_t)jn * ld + kk);
 	}
-	sbase += (uint32_t)n_stages;
-	return acc;
 }
 
-/* Lout[k] = ((init[k] + es[0]*Rs[0][k]) + es[1]*Rs[1][k]) + ...  for the NG feature
- * groups k = kb + g*32 + lane of this lane (matFact.c:48-49 order within the row). */
-template <int NG>
-__device__ __forceinline__ void row_update(const double *init, double *Lout, const double *Rs,
-                                           const double *es, int cnt, int S, int kb, int F, int lane)
+/* s = (s + l[0]*r[0]) + l[1]*r[1] + ... over one tile (mat2d.c:133-137 continued across tiles) */
+__device__ __forceinline__ double dot_tile(double s, const double *l, const double *r, int kc)
 {
-	double acc[NG];
-	const bool last_ok = kb + (NG - 1) * 32 + lane < F;   /* only the last group can be partial */
+	if (kc == KT) {
 #pragma unroll
-	for (int g = 0; g < NG; g++)
-		acc[g] = (g < NG - 1 || last_ok) ? init[kb + g * 32 + lane] : 0.0;
-	const double *col = Rs + kb + lane;
-	for (int n = 0; n < cnt; n++) {
-		const double e = es[n];
-		const double *x = col + (size_t)n * S;
+		for (int k = 0; k < KT; k += 2) {
+			const double2 a = ld2(l + k), b = ld2(r + k);
+			s = __dadd_rn(s, __dmul_rn(a.x, b.x));
+			s = __dadd_rn(s, __dmul_rn(a.y, b.y));
+		}
+	} else {
+		for (int k = 0; k < kc; k++)
+			s = __dadd_rn(s, __dmul_rn(l[k], r[k]));
+	}
+	return s;
+}
+
+/* Lout[k] = ((init[k] + es[0]*R[j_0][k]) + es[1]*R[j_1][k]) + ...  for the NG feature groups
+ * k = kb + g*32 + lane of this lane (matFact.c:48-49 order within the row).  The R values of
+ * nonzero n+1 are loaded (coalesced, 256 B per group) while those of n are being added. */
+template <int NG>
+__device__ __forceinline__ void row_update(const double *init, double *Lout,
+                                           const double *__restrict__ Rold, int j, const double *es,
+                                           int cnt, int ld, int kb, int F, int lane)
+{
+	double acc[NG], x[NG], xn[NG];
+	const bool last_ok = kb + (NG - 1) * 32 + lane < F;   /* only the last group can be partial */
+	size_t off[NG];
+#pragma unroll
+	for (int g = 0; g < NG; g++) {
+		const bool ok = g < NG - 1 || last_ok;
+		off[g] = ok ? (size_t)(kb + g * 32 + lane) : 0;    /* idle lanes read a valid address */
+		acc[g] = ok ? init[off[g]] : 0.0;
+	}
+	{
+		const double *row = Rold + (size_t)__shfl_sync(FULL, j, 0) * ld;
 #pragma unroll
 		for (int g = 0; g < NG; g++)
-			if (g < NG - 1 || last_ok)
-				acc[g] = __dadd_rn(acc[g], __dmul_rn(e, x[g * 32]));
+			x[g] = row[off[g]];
+	}
+	for (int n = 0; n < cnt; n++) {
+		const double e = es[n];
+		const double *row = Rold + (size_t)__shfl_sync(FULL, j, min(n + 1, cnt - 1)) * ld;
+#pragma unroll
+		for (int g = 0; g < NG; g++)
+			xn[g] = row[off[g]];
+#pragma unroll
+		for (int g = 0; g < NG; g++) {
+			acc[g] = __dadd_rn(acc[g], __dmul_rn(e, x[g]));
+			x[g] = xn[g];
+		}
 	}
 #pragma unroll
 	for (int g = 0; g < NG; g++)
 		if (g < NG - 1 || last_ok)
-			Lout[kb + g * 32 + lane] = acc[g];
+			Lout[off[g]] = acc[g];
+}
+
+/* ---- register pipeline of the sequential accumulations ----------------------------------
+ *
+ * acc = ((acc + ev[0]*x[0]) + ev[1]*x[1]) + ...  with x[n] = srck[idx[n]*ld], n < m, in order.
+ * One warp, lane = feature.  The additions form one dependent chain per lane, so the
+ * only way to go fast is to keep the operands ready: lane l holds (idx, ev) of nonzero
+ * 32q + l of block q and broadcasts them by shuffle, and the gathered x of the next block
+ * of 32 nonzeros are loaded into registers while the current block is being added.
+ */
+__device__ __forceinline__ void gather_block(double (&X)[32], int bi, const double *__restrict__ srck,
+                                             int ld)
+{
+	/* unconditional loads (every lane's bi is a valid row, see chain_regs): a predicated
+	 * load would be followed by a select that waits for it and serialise the gather */
+#pragma unroll
+	for (int r = 0; r < 32; r++)
+		X[r] = srck[(size_t)__shfl_sync(FULL, bi, r) * ld];
+}
+
+__device__ __forceinline__ double chain_block(double acc, const double (&X)[32], double be, int rows)
+{
+	if (rows == 32) {
+#pragma unroll
+		for (int r = 0; r < 32; r++)
+			acc = __dadd_rn(acc, __dmul_rn(__shfl_sync(FULL, be, r), X[r]));
+	} else {
+#pragma unroll
+		for (int r = 0; r < 32; r++) {
+			const double e = __shfl_sync(FULL, be, r);
+			if (r < rows)
+				acc = __dadd_rn(acc, __dmul_rn(e, X[r]));
+		}
+	}
+	return acc;
+}
+
+__device__ __forceinline__ double chain_regs(double acc, int lane,
+                                             const int *__restrict__ idx, const double *__restrict__ ev,
+                                             int m, const double *__restrict__ srck, int ld)
+{
+	const int nblk = (m + 31) >> 5;
+	int iA = 0, iB = 0, iC = 0;
+	double eA = 0.0, eB = 0.0, eC = 0.0;
+	auto load_blk = [&](int q, int &bi, double &be) {
+		const int n = min(q * 32 + lane, m - 1);   /* past the end: repeat the last row (never added) */
+		bi = idx[n];
+		be = ev[n];
+	};
+	auto rows_of = [&](int q) { return min(32, m - q * 32); };
+	double XA[32], XB[32];
+	load_blk(0, iA, eA);
+	load_blk(1, iB, eB);
+	gather_block(XA, iA, srck, ld);
+	for (int q = 0; q < nblk; q += 2) {
+		if (q + 1 < nblk)
+			gather_block(XB, iB, srck, ld);
+		load_blk(q + 2, iC, eC);
+		acc = chain_block(acc, XA, eA, rows_of(q));
+		if (q + 2 < nblk)
+			gather_block(XA, iC, srck, ld);
+		iA = iC;
+		eA = eC;
+		load_blk(q + 3, iC, eC);
+		if (q + 1 < nblk)
+			acc = chain_block(acc, XB, eB, rows_of(q + 1));
+		iB = iC;
+		eB = eC;
+	}
+	return acc;
 }
 
 /*
- * By-user pass.  Dynamic shared memory: [BAR_BYTES of mbarriers][WARPS x (Rs[CH*S] | Ls[S] | es[32])].
- * bars[w] (count 1) tracks warp w's row staging; bars[WARPS + s] (count 32) are the ring
- * stages of the whole-CTA rows, whose ring re-uses the staging area once the dots are done.
+ * By-user pass.  Dynamic shared memory per warp: two dot-phase tiles [CH][TS], the user's
+ * L row [ld], es[32].  LONG = true: block b takes stored row b (< n_long) with the whole
+ * CTA; LONG = false: every warp takes one of the remaining rows.  The dot of a nonzero streams its R row through the two tiles in
+ * pieces of KT features (next tile in flight while the current one is added); the
+ * accumulation of L_new then re-reads the R rows coalesced from L2.
  */
-template <int WARPS>
+template <int WARPS, bool LONG>
 __global__ void __launch_bounds__(WARPS * 32)
 k_update_L(const LoopArgs p, const double *__restrict__ Lold, double *__restrict__ Lnew,
            const double *__restrict__ Rold)
 {
-	extern __shared__ __align__(128) unsigned char smem_raw[];
-	uint64_t *bars = reinterpret_cast<uint64_t *>(smem_raw);
-	double *data = reinterpret_cast<double *>(smem_raw + BAR_BYTES);
+	extern __shared__ __align__(16) double smem[];
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-	const int F = p.F, ld = p.ld, S = p.S, CH = p.CH;
-	const uint32_t row_bytes = (uint32_t)ld * 8u;
-	const size_t per_warp = (size_t)CH * S + S + 32;
-	double *Rs = data + per_warp * warp;
-	double *Ls = Rs + (size_t)CH * S;
-	double *es = Ls + S;
-	uint64_t *bar = &bars[warp];
+	const int F = p.F, ld = p.ld, CH = p.CH;
+	const size_t per_warp = (size_t)2 * CH * TS + ld + 32;
+	double *T0 = smem + per_warp * warp;
+	double *T1 = T0 + (size_t)CH * TS;
+	double *Ls = T1 + (size_t)CH * TS;
+	double *es = Ls + ld;
 
-	const bool is_long = (int)blockIdx.x < p.n_long;
-	const int r = is_long ? (int)blockIdx.x : p.n_long + ((int)blockIdx.x - p.n_long) * WARPS + warp;
-	if (lane == 0) {
-		mbar_init(bar, 1);
-		if (is_long && warp == 0)
-			for (int s = 0; s < p.nst_long; s++)
-				mbar_init(&bars[WARPS + s], 32);
-		mbar_fence_init();
-	}
-	if (is_long)
-		__syncthreads();
-	else
-		__syncwarp();
+	constexpr bool is_long = LONG;    /* two kernels: the register-hungry pipeline of the long rows
+	                                     must not cap the occupancy of the short-row launch */
+	const int r = is_long ? (int)blockIdx.x : p.n_long + (int)blockIdx.x * WARPS + warp;
 	if (r >= p.n_rows)
 		return;                       /* whole warp leaves; short-path blocks never use a block barrier */
 	const int i = p.row_id[r] - p.user_lo;
@@ -193,11 +241,13 @@ k_update_L(const LoopArgs p, const double *__restrict__ Lold, double *__restrict
 	const int m = p.row_ptr[r + 1] - base;
 	const double *Lrow = Lold + (size_t)i * ld;
 	double *Lout = Lnew + (size_t)i * ld;
+	const int ntiles = (F + KT - 1) / KT;
 
-	uint32_t phase = 0;
-	bool first = true;
 	const int c_first = is_long ? warp * CH : 0;
 	const int c_step = is_long ? WARPS * CH : CH;
+	if (c_first < m)                  /* joins the first tile's copy group */
+		for (int q = lane; q < (ld >> 1); q += 32)
+			cp_async16(Ls + 2 * q, Lrow + 2 * q);
 	for (int c0 = c_first; c0 < m; c0 += c_step) {
 		const int cnt = min(CH, m - c0);
 		const int pos = base + c0 + lane;
@@ -207,20 +257,24 @@ k_update_L(const LoopArgs p, const double *__restrict__ Lold, double *__restrict
 			j = p.col_idx[pos];
 			a = p.val[pos];
 		}
-		/* stage: one bulk copy per R row (+ the user's own L row the first time) */
-		if (lane == 0) {
-			mbar_arrive_expect_tx(bar, row_bytes * (uint32_t)(cnt + (first ? 1 : 0)));
-			if (first)
-				bulk_g2s(Ls, Lrow, row_bytes, bar);
-		}
-		if (lane < cnt)
-			bulk_g2s(Rs + (size_t)lane * S, Rold + (size_t)j * ld, row_bytes, bar);
-		mbar_wait(bar, phase);
-		phase ^= 1u;
-		first = false;
+		j = __shfl_sync(FULL, j, min(lane, cnt - 1));   /* idle lanes mirror a valid item */
 
+		/* e_n = alpha2 * (a - dot): one lane per nonzero, k sequential, tiles double buffered */
+		stage_tile(T0, Rold, j, cnt, 0, ld, lane);
+		cp_async_commit();
+		double s = 0.0;
+		for (int t = 0; t < ntiles; t++) {
+			double *cur = (t & 1) ? T1 : T0;
+			if (t + 1 < ntiles)
+				stage_tile((t & 1) ? T0 : T1, Rold, j, cnt, (t + 1) * KT, ld, lane);
+			cp_async_commit();
+			cp_async_wait<1>();       /* everything but the tile just issued has landed */
+			__syncwarp();
+			if (lane < cnt)
+				s = dot_tile(s, Ls + t * KT, cur + lane * TS, min(KT, F - t * KT));
+			__syncwarp();             /* tile `cur` may be overwritten by the next issue */
+		}
 		if (lane < cnt) {
-			const double s = seq_dot_smem(Ls, Rs + (size_t)lane * S, F);
 			const double e = __dmul_rn(p.alpha2, __dsub_rn(a, s));
 			p.e_csc[p.epos[pos]] = e;
 			if (is_long)
@@ -235,77 +289,59 @@ k_update_L(const LoopArgs p, const double *__restrict__ Lold, double *__restrict
 			for (int kb = 0; kb < F; kb += 256) {
 				const double *init = (c0 == 0) ? Ls : Lout;
 				switch (min(8, (F - kb + 31) >> 5)) {
-				case 1: row_update<1>(init, Lout, Rs, es, cnt, S, kb, F, lane); break;
-				case 2: row_update<2>(init, Lout, Rs, es, cnt, S, kb, F, lane); break;
-				case 3: row_update<3>(init, Lout, Rs, es, cnt, S, kb, F, lane); break;
-				case 4: row_update<4>(init, Lout, Rs, es, cnt, S, kb, F, lane); break;
-				case 5: row_update<5>(init, Lout, Rs, es, cnt, S, kb, F, lane); break;
-				case 6: row_update<6>(init, Lout, Rs, es, cnt, S, kb, F, lane); break;
-				case 7: row_update<7>(init, Lout, Rs, es, cnt, S, kb, F, lane); break;
-				default: row_update<8>(init, Lout, Rs, es, cnt, S, kb, F, lane); break;
+				case 1: row_update<1>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
+				case 2: row_update<2>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
+				case 3: row_update<3>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
+				case 4: row_update<4>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
+				case 5: row_update<5>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
+				case 6: row_update<6>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
+				case 7: row_update<7>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
+				default: row_update<8>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
 				}
 			}
+			__syncwarp();             /* es is rewritten by the next chunk */
 		}
-		__syncwarp();   /* everyone is done with Rs / es before the next chunk overwrites them */
 	}
 	if (!is_long)
 		return;
 
-	/* whole-CTA row: every e_n is in e_csr; thread = feature, R rows stream through the ring */
+	/* whole-CTA row: every e_n is in e_csr (written above by this CTA); each warp now owns
+	 * 32 features and walks the row's nonzeros in order with the register pipeline */
 	__syncthreads();
-	uint32_t sbase = 0;
-	const int RB = p.rb_long, NST = p.nst_long;
-	double *ring = data;
-	for (int fb = 0; fb < F; fb += WARPS * 32) {
-		const int seg = min(WARPS * 32, ld - fb);
-		double *ring_es = ring + (size_t)NST * RB * seg;
-		const int k = fb + (int)threadIdx.x;
+	for (int kb = warp * 32; kb < F; kb += WARPS * 32) {
+		const int k = kb + lane;
 		const bool active = k < F;
 		double acc = active ? Lrow[k] : 0.0;
-		acc = chain_pipeline<WARPS * 32>(acc, active, (int)threadIdx.x, p.col_idx + base, p.e_csr + base, m,
-		                                 Rold + fb, ld, 0, seg, ring, ring_es, &bars[WARPS], RB, NST, sbase);
+		acc = chain_regs(acc, lane, p.col_idx + base, p.e_csr + base, m, Rold + (active ? k : 0), ld);
 		if (active)
 			Lout[k] = acc;
 	}
 }
 
 /*
- * By-item pass.  CTA = (stored column c, feature block fbi); thread = feature.
- * Dynamic shared memory: [BAR_BYTES of mbarriers][ring NST*RB rows of seg doubles][es NST*RB].
+ * By-item pass.  One warp per (stored column c, group of 32 features), lane = feature.
  * single-GPU: Rout = R_new, starts from R_old[j][k]        (matFact.c:50-51)
  * N shards:   Rout = G (rows by item_slot), starts from 0  (matFact-mpi.c:187-205)
  */
-template <int TPB>
-__global__ void __launch_bounds__(TPB)
+template <int WARPS>
+__global__ void __launch_bounds__(WARPS * 32)
 k_update_R(const LoopArgs p, const double *__restrict__ Lold, const double *__restrict__ Rold,
            double *__restrict__ Rout)
 {
-	extern __shared__ __align__(128) unsigned char smem_raw[];
-	uint64_t *bars = reinterpret_cast<uint64_t *>(smem_raw);
-	double *ring = reinterpret_cast<double *>(smem_raw + BAR_BYTES);
-	const int tid = threadIdx.x;
-	const int c = (int)(blockIdx.x / (unsigned)p.nfb), fb = (int)(blockIdx.x % (unsigned)p.nfb) * TPB;
-	const int RB = p.rb, NST = p.nst;
-	if (tid == 0) {
-		for (int s = 0; s < NST; s++)
-			mbar_init(&bars[s], 32);
-		mbar_fence_init();
-	}
-	if (TPB == 32)
-		__syncwarp();
-	else
-		__syncthreads();
+	const int lane = threadIdx.x & 31;
+	const int NG = (p.F + 31) >> 5;
+	const long gw = (long)blockIdx.x * WARPS + (threadIdx.x >> 5);
+	const int c = (int)(gw / NG), g = (int)(gw % NG);
+	if (c >= p.n_cols)
+		return;
+	const int k = g * 32 + lane;
+	const bool active = k < p.F;
 	const int ld = p.ld;
-	const int seg = min(TPB, ld - fb);
-	double *es = ring + (size_t)NST * RB * seg;
 	const int j = p.col_id[c];
 	const int b = p.col_ptr[c], m = p.col_ptr[c + 1] - b;
-	const int k = fb + tid;
-	const bool active = k < p.F;
+	const double *Lk = Lold + (active ? k : 0) - (size_t)p.user_lo * ld;
 	double acc = (p.item_slot || !active) ? 0.0 : Rold[(size_t)j * ld + k];
-	uint32_t sbase = 0;
-	acc = chain_pipeline<TPB>(acc, active, tid, p.row_idx + b, p.e_csc + b, m, Lold + fb, ld, p.user_lo,
-	                          seg, ring, es, bars, RB, NST, sbase);
+	acc = chain_regs(acc, lane, p.row_idx + b, p.e_csc + b, m, Lk, ld);
 	if (active) {
 		const size_t orow = p.item_slot ? (size_t)p.item_slot[j] : (size_t)j;
 		Rout[orow * ld + k] = acc;

@@ -28,100 +28,47 @@ static int upload(T **dst, const T *src, size_t n, cudaStream_t st)
 	return MFGPU_OK;
 }
 
-static int pow2_ceil(int x)
-{
-	int p = 1;
-	while (p < x) p <<= 1;
-	return p;
-}
-
 /* Launch geometry of k_update_L / k_update_R for one shard (see mf_loop.cuh). */
 int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
 {
 	const int F = pl->F;
-	int S = (F + 1) & ~1;
-	if (S % 4 == 0)
-		S += 2;              /* S = 2 (mod 4): 16-byte reads of 8 lanes hit 8 distinct bank groups */
-	if (S < 2)
-		S = 2;
+	const int TS = 18;               /* mf::TS: row stride of a dot-phase tile */
 	int max_smem = 0;
 	CK(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, s->dev));
-	const size_t bar_bytes = 128;     /* mf::BAR_BYTES */
-	const int want = pl->opt_ch > 0 ? pl->opt_ch : 32;
-	int ch_cap = std::min(32, pow2_ceil(std::max(1, s->pat.max_row_len)));
-	ch_cap = std::min(ch_cap, pow2_ceil(want));
-	/* lanes of the dot phase = nonzeros staged per chunk: take the largest chunk that fits */
-	int warps = 8, CH = 0;
-	for (int w = 8; w >= 1 && !CH; w = (w == 8 ? 1 : 0)) {
-		for (int ch = ch_cap; ch >= 1; ch >>= 1)
-			if (bar_bytes + (size_t)w * ((size_t)ch * S + S + 32) * sizeof(double) <= (size_t)max_smem) {
-				CH = ch;
-				warps = w;
-				break;
-			}
-	}
-	if (!CH)
-		return mf_fail(MFGPU_EINVAL, "features=%d does not fit the shared-memory staging (%d bytes)",
-		               F, max_smem);
-	const size_t data_doubles = (size_t)warps * ((size_t)CH * S + S + 32);
+	/* nonzeros per chunk = lanes of the dot phase: the whole row when it has <= 32 nonzeros */
+	int CH = std::max(1, std::min(32, s->pat.max_row_len));
+	if (pl->opt_ch > 0)
+		CH = std::max(1, std::min(32, pl->opt_ch));
+	auto warp_doubles = [&](int ch) { return (size_t)2 * ch * TS + pl->ld + 32; };
+	int warps = 8;
+	if (8 * warp_doubles(CH) * sizeof(double) > (size_t)max_smem)
+		warps = 1;
+	if (warps * warp_doubles(CH) * sizeof(double) > (size_t)max_smem)
+		return mf_fail(MFGPU_EINVAL, "features=%d does not fit shared memory (%d bytes)", F, max_smem);
 	s->warps = warps;
-	s->k1_smem = bar_bytes + data_doubles * sizeof(double);
+	s->k1_smem = warps * warp_doubles(CH) * sizeof(double);
+	TRY(mf_kernels_prepare(warps, s->k1_smem));
 
-	/* ring of the whole-CTA rows lives in the staging area: stages of rb rows of <= 256 features */
-	int rb_long = std::max(1, std::min(32, pl->opt_ring_rows > 0 ? pl->opt_ring_rows : 16)), nst_long = 0;
-	{
-		const size_t seg = (size_t)std::min(256, pl->ld);
-		for (; rb_long >= 1; rb_long >>= 1) {
-			nst_long = (int)std::min<size_t>(8, data_doubles / ((size_t)rb_long * (seg + 1)));
-			if (pl->opt_ring_stages > 0)
-				nst_long = std::min(nst_long, std::max(2, pl->opt_ring_stages));
-			if (nst_long >= 2)
-				break;
-		}
-		if (rb_long < 1) { rb_long = 1; nst_long = 0; }
-	}
-
-	/* rows longer than the threshold get a whole CTA (their dots run on all warps) */
-	const int thresh = pl->opt_long_row > 0 ? pl->opt_long_row : std::max(8 * CH, 64);
+	/* a warp spends ~100 cycles per nonzero, so a row much longer than the per-warp share of
+	 * the shard (nnz / (8 warps x SMs)) would outlast the rest of the launch on the warp path */
+	int n_sm = 148;
+	CK(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, s->dev));
+	const int share = (int)std::min<long>(1 << 30, (long)s->pat.nnz / (2L * 8 * std::max(1, n_sm)));
+	const int thresh = pl->opt_long_row > 0 ? pl->opt_long_row : std::max(2 * CH, share);
 	int n_long = 0;
-	if (warps > 1 && nst_long >= 2)
+	if (warps > 1)
 		while (n_long < s->pat.n_rows &&
 		       s->pat.row_ptr[n_long + 1] - s->pat.row_ptr[n_long] > thresh)
 			n_long++;
 
-	/* by-item pass: thread = feature, ring of L rows */
-	const int tpb = F <= 32 ? 32 : F <= 64 ? 64 : F <= 128 ? 128 : 256;
-	const int nfb = std::max(1, (F + tpb - 1) / tpb);
-	int rb = std::max(1, std::min(32, pl->opt_ring_rows > 0 ? pl->opt_ring_rows : 16));
-	int nst = std::max(2, std::min(8, pl->opt_ring_stages > 0 ? pl->opt_ring_stages : 4));
-	const size_t seg2 = (size_t)std::min(tpb, pl->ld);
-	auto k2_bytes = [&](int r, int n) { return bar_bytes + (size_t)n * r * (seg2 + 1) * sizeof(double); };
-	const size_t k2_budget = pl->opt_ring_rows > 0 ? (size_t)max_smem : (size_t)64 * 1024;
-	while (k2_bytes(rb, nst) > k2_budget) {
-		if (nst > 3) nst--;
-		else if (rb > 1) rb >>= 1;
-		else if (nst > 2) nst--;
-		else break;
-	}
-	if (k2_bytes(rb, nst) > (size_t)max_smem)
-		return mf_fail(MFGPU_EINVAL, "features=%d: ring does not fit shared memory", F);
-	s->k2_smem = k2_bytes(rb, nst);
-	TRY(mf_kernels_prepare(warps, s->k1_smem, tpb, s->k2_smem));
-
 	mf::LoopArgs &a = s->la;
 	a.F = F;
 	a.ld = pl->ld;
-	a.S = S;
+	a.S = TS;
 	a.CH = CH;
 	a.n_rows = s->pat.n_rows;
 	a.n_long = n_long;
 	a.n_cols = s->pat.n_cols;
-	a.rb = rb;
-	a.nst = nst;
-	a.tpb = tpb;
-	a.nfb = nfb;
-	a.rb_long = rb_long;
-	a.nst_long = nst_long;
 	a.user_lo = s->user_lo;
 	a.alpha2 = pl->alpha * 2;     /* matFact.c:45: alpha * 2 * (...) associates left, exact */
 	a.row_id = s->d_row_id;
@@ -135,10 +82,9 @@ int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
 	a.item_slot = pl->nshards > 1 ? s->d_item_slot : nullptr;
 	a.e_csc = s->d_e_csc;
 	a.e_csr = s->d_e_csr;
-	s->k1_blocks = n_long + (a.n_rows - n_long + warps - 1) / warps;
-	if ((long)a.n_cols * nfb > 2147483647L)
-		return mf_fail(MFGPU_EINVAL, "too many (item, feature block) work items");
-	s->k2_blocks = a.n_cols * nfb;
+	s->k1_blocks = (a.n_rows - n_long + warps - 1) / warps;      /* short-row launch; n_long CTAs more for the long rows */
+	const long k2_warps = (long)a.n_cols * ((F + 31) / 32);
+	s->k2_blocks = (int)((k2_warps + 7) / 8);
 	for (int g = 0; g < 2; g++)
 		if (s->gexec[g]) {
 			cudaGraphExecDestroy(s->gexec[g]);
@@ -153,6 +99,9 @@ static int shard_create(mfgpu_plan *pl, mf_shard *s, int dev, const mfgpu_entry 
 	s->dev = dev;
 	CK(cudaSetDevice(dev));
 	CK(cudaStreamCreateWithFlags(&s->st, cudaStreamNonBlocking));
+	CK(cudaStreamCreateWithFlags(&s->st2, cudaStreamNonBlocking));
+	CK(cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming));
+	CK(cudaEventCreateWithFlags(&s->ev_join, cudaEventDisableTiming));
 	CK(cudaEventCreate(&s->ev0));
 	CK(cudaEventCreate(&s->ev1));
 	CK(cudaEventCreate(&s->ev_t0));
@@ -233,6 +182,9 @@ static void shard_destroy(mf_shard *s)
 	if (s->ev1) cudaEventDestroy(s->ev1);
 	if (s->ev_t0) cudaEventDestroy(s->ev_t0);
 	if (s->ev_t1) cudaEventDestroy(s->ev_t1);
+	if (s->ev_fork) cudaEventDestroy(s->ev_fork);
+	if (s->ev_join) cudaEventDestroy(s->ev_join);
+	if (s->st2) cudaStreamDestroy(s->st2);
 	if (s->st) cudaStreamDestroy(s->st);
 	mf_pattern_free(&s->pat);
 	cudaGetLastError();
@@ -463,8 +415,6 @@ extern "C" int mfgpu_plan_set_option(mfgpu_plan *pl, const char *name, int value
 	else if (!strcmp(name, "graph_iters")) pl->opt_graph_iters = std::max(2, value & ~1);
 	else if (!strcmp(name, "long_row")) pl->opt_long_row = value;
 	else if (!strcmp(name, "chunk")) pl->opt_ch = value;
-	else if (!strcmp(name, "ring_rows")) pl->opt_ring_rows = value;
-	else if (!strcmp(name, "ring_stages")) pl->opt_ring_stages = value;
 	else
 		return mf_fail(MFGPU_EINVAL, "unknown option '%s'", name);
 	for (int g = 0; g < local_shards(pl); g++) {

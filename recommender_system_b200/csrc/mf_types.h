@@ -15,9 +15,6 @@ struct LoopArgs {
 	int n_rows;       /* stored user rows (users with >= 1 nonzero)       */
 	int n_long;       /* the first n_long stored rows get a whole CTA     */
 	int n_cols;       /* stored item columns                              */
-	int rb, nst;      /* by-item pass: rows per ring stage, ring stages   */
-	int tpb, nfb;     /* by-item pass: threads (= features) per CTA, feature blocks per column */
-	int rb_long, nst_long; /* by-user pass, whole-CTA rows: ring geometry */
 	int user_lo;      /* first user of this shard; L holds rows user_lo.. */
 	double alpha2;    /* alpha * 2, exact                                 */
 	const int *row_id, *row_ptr, *col_idx, *epos;
