@@ -47,7 +47,7 @@ struct mf_shard {
 	double *L_keep, *R_keep;                 /* mfgpu_plan_save_factors           */
 	mf::LoopArgs la;
 	int warps;                               /* 8 or 1: k_update_L template      */
-	int k1_blocks, k2_blocks;
+	int k1_blocks, k2_blocks, k2_long_blocks;
 	size_t k1_smem;
 	cudaGraphExec_t gexec[2];                /* by starting parity                */
 	cudaEvent_t ev0, ev1, ev_g[2], ev_t0, ev_t1, ev_fork, ev_join;
@@ -70,7 +70,7 @@ struct mfgpu_plan {
 	long long launches;
 	float loop_ms, rec_ms;
 	/* options */
-	int opt_graph, opt_graph_iters, opt_long_row, opt_ch;
+	int opt_graph, opt_graph_iters, opt_long_row, opt_long_col, opt_ch;
 };
 
 /* ---- shared helpers (defined in mf_capi.cu) ----------------------------------- */

@@ -96,11 +96,23 @@ static int launch_update_L(mfgpu_plan *pl, mf_shard *s, int c)
 
 static int launch_update_R(mfgpu_plan *pl, mf_shard *s, int c, double *out)
 {
-	if (s->k2_blocks <= 0)
-		return MFGPU_OK;
-	mf::k_update_R<8><<<s->k2_blocks, 256, 0, s->st>>>(s->la, s->L[c], s->R[c], out);
-	CK(cudaGetLastError());
-	pl->launches++;
+	const int n_long = s->la.n_long_cols;
+	if (s->k2_long_blocks > 0) {
+		/* the few longest columns: deep register pipeline, beside the bulk on the second stream */
+		CK(cudaEventRecord(s->ev_fork, s->st));
+		CK(cudaStreamWaitEvent(s->st2, s->ev_fork, 0));
+		mf::k_update_R<8, 32><<<s->k2_long_blocks, 256, 0, s->st2>>>(s->la, 0, n_long, s->L[c], s->R[c], out);
+		CK(cudaGetLastError());
+		CK(cudaEventRecord(s->ev_join, s->st2));
+		pl->launches++;
+	}
+	if (s->k2_blocks > 0) {
+		mf::k_update_R<8, 8><<<s->k2_blocks, 256, 0, s->st>>>(s->la, n_long, s->la.n_cols, s->L[c], s->R[c], out);
+		CK(cudaGetLastError());
+		pl->launches++;
+	}
+	if (s->k2_long_blocks > 0)
+		CK(cudaStreamWaitEvent(s->st, s->ev_join, 0));
 	return MFGPU_OK;
 }
 
@@ -184,7 +196,7 @@ static int build_graph(mfgpu_plan *pl, mf_shard *s, int c, int n)
 
 static long long launches_per_iteration(const mfgpu_plan *pl, const mf_shard *s)
 {
-	long long n = (s->la.n_long > 0) + (s->k1_blocks > 0) + (s->k2_blocks > 0);
+	long long n = (s->la.n_long > 0) + (s->k1_blocks > 0) + (s->k2_long_blocks > 0) + (s->k2_blocks > 0);
 	if (pl->nshards > 1 && (long)pl->n_touched * pl->F > 0)
 		n += 1;
 	return n;

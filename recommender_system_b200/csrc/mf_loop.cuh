@@ -66,20 +66,41 @@ constexpr int KT = 16;        /* features per staged tile of the dot phase      
 constexpr int TS = KT + 2;    /* tile row stride in doubles: TS/2 odd, so the 16-byte reads
                                  of 8 lanes (8 rows) fall in 8 distinct bank groups   */
 
-/* Issue the asynchronous staging of features [k0, k0+KT) of `cnt` rows of `src` (row of
- * nonzero n = lane n's `j`) into `dst`, rows TS doubles apart: 8 lanes x 16 bytes per row. */
-__device__ __forceinline__ void stage_tile(double *dst, const double *__restrict__ src, int j, int cnt,
-                                           int k0, int ld, int lane)
+/* Staging of the dot phase.  A chunk has cnt <= 32 nonzeros; a tile holds features
+ * [k0, k0+KT) of their R rows, rows TS doubles apart, moved as 16-byte pieces (8 per row).
+ * Lane l owns pieces l, l+32, ... (<= 8 of them): their source row and tile offset are fixed
+ * for the chunk, so they are computed once (StagePlan) and a tile costs one cp.async each. */
+struct StagePlan {
+	const double *src[8];     /* row start + 2*piece-in-row, k0 not yet added */
+	int dst[8];               /* offset in the tile, doubles                  */
+	int kofs[8];              /* 2*piece-in-row, to test against ld - k0      */
+	int n;                    /* pieces of this lane                          */
+};
+
+__device__ __forceinline__ void stage_plan(StagePlan &sp, const double *__restrict__ src, int j, int cnt,
+                                           int ld, int lane)
 {
 	const int pieces = cnt * (KT / 2);
-	for (int p0 = 0; p0 < pieces; p0 += 32) {
-		const int p = p0 + lane;
+	sp.n = 0;
+#pragma unroll
+	for (int u = 0; u < 8; u++) {
+		const int p = u * 32 + lane;
 		const int row = min(p >> 3, cnt - 1), pc = p & 7;
 		const int jn = __shfl_sync(FULL, j, row);
-		const int kk = k0 + 2 * pc;
-		if (p < pieces && kk < ld)
-			cp_async16(dst + row * TS + 2 * pc, src + (size_t)jn * ld + kk);
+		sp.src[u] = src + (size_t)jn * ld + 2 * pc;
+		sp.dst[u] = row * TS + 2 * pc;
+		sp.kofs[u] = 2 * pc;
+		if (p < pieces)
+			sp.n = u + 1;
 	}
+}
+
+__device__ __forceinline__ void stage_tile(double *dst, const StagePlan &sp, int k0, int ld)
+{
+#pragma unroll
+	for (int u = 0; u < 8; u++)
+		if (u < sp.n && k0 + sp.kofs[u] < ld)
+			cp_async16(dst + sp.dst[u], sp.src[u] + k0);
 }
 
 /* s = (s + l[0]*r[0]) + l[1]*r[1] + ... over one tile (mat2d.c:133-137 continued across tiles) */
@@ -210,6 +231,79 @@ __device__ __forceinline__ double chain_regs(double acc, int lane,
 	return acc;
 }
 
+/* Same accumulation with blocks of B = 8 or 16 nonzeros and two small register buffers:
+ * ~64 registers instead of ~170, so four times as many warps are resident.  This is the
+ * variant for launches with many more (item, feature group) chains than warp slots, where
+ * the other warps hide the gather latency; the 32-row variant above is for the few chains
+ * that are so long that they alone decide how long the launch lasts. */
+template <int B>
+__device__ __forceinline__ void gather_small(double (&X)[B], int bi, int lane0,
+                                             const double *__restrict__ srck, int ld)
+{
+#pragma unroll
+	for (int r = 0; r < B; r++)
+		X[r] = srck[(size_t)__shfl_sync(FULL, bi, lane0 + r) * ld];
+}
+
+template <int B>
+__device__ __forceinline__ double chain_small(double acc, const double (&X)[B], double be, int lane0, int rows)
+{
+	if (rows >= B) {
+#pragma unroll
+		for (int r = 0; r < B; r++)
+			acc = __dadd_rn(acc, __dmul_rn(__shfl_sync(FULL, be, lane0 + r), X[r]));
+	} else {
+#pragma unroll
+		for (int r = 0; r < B; r++) {
+			const double e = __shfl_sync(FULL, be, lane0 + r);
+			if (r < rows)
+				acc = __dadd_rn(acc, __dmul_rn(e, X[r]));
+		}
+	}
+	return acc;
+}
+
+template <int B>
+__device__ __forceinline__ double chain_regs_small(double acc, int lane, const int *__restrict__ idx,
+                                                   const double *__restrict__ ev, int m,
+                                                   const double *__restrict__ srck, int ld)
+{
+	constexpr int NSB = 32 / B;          /* sub-blocks per block of 32 (idx, e) pairs; even */
+	const int nib = (m + 31) >> 5;
+	int iCur, iNxt;
+	double eCur, eNxt;
+	auto load_blk = [&](int q, int &bi, double &be) {
+		const int n = min(q * 32 + lane, m - 1);
+		bi = idx[n];
+		be = ev[n];
+	};
+	load_blk(0, iCur, eCur);
+	load_blk(1, iNxt, eNxt);
+	double X0[B], X1[B];
+	gather_small<B>(X0, iCur, 0, srck, ld);
+	for (int ib = 0; ib < nib; ib++) {
+		const int rows_ib = min(32, m - ib * 32);
+#pragma unroll
+		for (int sb = 0; sb < NSB; sb++) {
+			/* next sub-block in flight while this one is added */
+			if (sb + 1 < NSB) {
+				if (sb & 1) gather_small<B>(X0, iCur, (sb + 1) * B, srck, ld);
+				else        gather_small<B>(X1, iCur, (sb + 1) * B, srck, ld);
+			} else {
+				gather_small<B>(X0, iNxt, 0, srck, ld);     /* NSB even: sub-block 0 lives in X0 */
+			}
+			const int rows = rows_ib - sb * B;
+			if (rows > 0)
+				acc = (sb & 1) ? chain_small<B>(acc, X1, eCur, sb * B, rows)
+				               : chain_small<B>(acc, X0, eCur, sb * B, rows);
+		}
+		iCur = iNxt;
+		eCur = eNxt;
+		load_blk(ib + 2, iNxt, eNxt);
+	}
+	return acc;
+}
+
 /*
  * By-user pass.  Dynamic shared memory per warp: two dot-phase tiles [CH][TS], the user's
  * L row [ld], es[32].  LONG = true: block b takes stored row b (< n_long) with the whole
@@ -260,13 +354,15 @@ k_update_L(const LoopArgs p, const double *__restrict__ Lold, double *__restrict
 		j = __shfl_sync(FULL, j, min(lane, cnt - 1));   /* idle lanes mirror a valid item */
 
 		/* e_n = alpha2 * (a - dot): one lane per nonzero, k sequential, tiles double buffered */
-		stage_tile(T0, Rold, j, cnt, 0, ld, lane);
+		StagePlan sp;
+		stage_plan(sp, Rold, j, cnt, ld, lane);
+		stage_tile(T0, sp, 0, ld);
 		cp_async_commit();
 		double s = 0.0;
 		for (int t = 0; t < ntiles; t++) {
 			double *cur = (t & 1) ? T1 : T0;
 			if (t + 1 < ntiles)
-				stage_tile((t & 1) ? T0 : T1, Rold, j, cnt, (t + 1) * KT, ld, lane);
+				stage_tile((t & 1) ? T0 : T1, sp, (t + 1) * KT, ld);
 			cp_async_commit();
 			cp_async_wait<1>();       /* everything but the tile just issued has landed */
 			__syncwarp();
@@ -319,20 +415,22 @@ k_update_L(const LoopArgs p, const double *__restrict__ Lold, double *__restrict
 }
 
 /*
- * By-item pass.  One warp per (stored column c, group of 32 features), lane = feature.
+ * By-item pass over the stored columns [c_begin, c_end).  One warp per (column, group of
+ * 32 features), lane = feature.  B = rows per register block of the pipeline (32 for the
+ * launch of the few longest columns, 8 for the bulk).
  * single-GPU: Rout = R_new, starts from R_old[j][k]        (matFact.c:50-51)
  * N shards:   Rout = G (rows by item_slot), starts from 0  (matFact-mpi.c:187-205)
  */
-template <int WARPS>
+template <int WARPS, int B>
 __global__ void __launch_bounds__(WARPS * 32)
-k_update_R(const LoopArgs p, const double *__restrict__ Lold, const double *__restrict__ Rold,
-           double *__restrict__ Rout)
+k_update_R(const LoopArgs p, int c_begin, int c_end, const double *__restrict__ Lold,
+           const double *__restrict__ Rold, double *__restrict__ Rout)
 {
 	const int lane = threadIdx.x & 31;
 	const int NG = (p.F + 31) >> 5;
 	const long gw = (long)blockIdx.x * WARPS + (threadIdx.x >> 5);
-	const int c = (int)(gw / NG), g = (int)(gw % NG);
-	if (c >= p.n_cols)
+	const int c = c_begin + (int)(gw / NG), g = (int)(gw % NG);
+	if (c >= c_end)
 		return;
 	const int k = g * 32 + lane;
 	const bool active = k < p.F;
@@ -341,7 +439,10 @@ k_update_R(const LoopArgs p, const double *__restrict__ Lold, const double *__re
 	const int b = p.col_ptr[c], m = p.col_ptr[c + 1] - b;
 	const double *Lk = Lold + (active ? k : 0) - (size_t)p.user_lo * ld;
 	double acc = (p.item_slot || !active) ? 0.0 : Rold[(size_t)j * ld + k];
-	acc = chain_regs(acc, lane, p.row_idx + b, p.e_csc + b, m, Lk, ld);
+	if (B == 32)
+		acc = chain_regs(acc, lane, p.row_idx + b, p.e_csc + b, m, Lk, ld);
+	else
+		acc = chain_regs_small<(B == 32 ? 8 : B)>(acc, lane, p.row_idx + b, p.e_csc + b, m, Lk, ld);
 	if (active) {
 		const size_t orow = p.item_slot ? (size_t)p.item_slot[j] : (size_t)j;
 		Rout[orow * ld + k] = acc;

@@ -61,6 +61,14 @@ int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
 		       s->pat.row_ptr[n_long + 1] - s->pat.row_ptr[n_long] > thresh)
 			n_long++;
 
+	/* columns whose sequential chain alone would outlast the launch get the deep pipeline */
+	const int col_thresh = pl->opt_long_col > 0 ? pl->opt_long_col
+	                                            : std::max(64, (int)std::min<long>(1 << 30, (long)s->pat.nnz / (4L * std::max(1, n_sm))));
+	int n_long_cols = 0;
+	while (n_long_cols < s->pat.n_cols &&
+	       s->pat.col_ptr[n_long_cols + 1] - s->pat.col_ptr[n_long_cols] > col_thresh)
+		n_long_cols++;
+
 	mf::LoopArgs &a = s->la;
 	a.F = F;
 	a.ld = pl->ld;
@@ -69,6 +77,7 @@ int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
 	a.n_rows = s->pat.n_rows;
 	a.n_long = n_long;
 	a.n_cols = s->pat.n_cols;
+	a.n_long_cols = n_long_cols;
 	a.user_lo = s->user_lo;
 	a.alpha2 = pl->alpha * 2;     /* matFact.c:45: alpha * 2 * (...) associates left, exact */
 	a.row_id = s->d_row_id;
@@ -83,8 +92,9 @@ int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
 	a.e_csc = s->d_e_csc;
 	a.e_csr = s->d_e_csr;
 	s->k1_blocks = (a.n_rows - n_long + warps - 1) / warps;      /* short-row launch; n_long CTAs more for the long rows */
-	const long k2_warps = (long)a.n_cols * ((F + 31) / 32);
-	s->k2_blocks = (int)((k2_warps + 7) / 8);
+	const long ng = (F + 31) / 32;
+	s->k2_blocks = (int)(((long)(a.n_cols - n_long_cols) * ng + 7) / 8);
+	s->k2_long_blocks = (int)(((long)n_long_cols * ng + 7) / 8);
 	for (int g = 0; g < 2; g++)
 		if (s->gexec[g]) {
 			cudaGraphExecDestroy(s->gexec[g]);
@@ -415,6 +425,7 @@ extern "C" int mfgpu_plan_set_option(mfgpu_plan *pl, const char *name, int value
 	else if (!strcmp(name, "graph_iters")) pl->opt_graph_iters = std::max(2, value & ~1);
 	else if (!strcmp(name, "long_row")) pl->opt_long_row = value;
 	else if (!strcmp(name, "chunk")) pl->opt_ch = value;
+	else if (!strcmp(name, "long_col")) pl->opt_long_col = value;
 	else
 		return mf_fail(MFGPU_EINVAL, "unknown option '%s'", name);
 	for (int g = 0; g < local_shards(pl); g++) {

@@ -15,6 +15,7 @@ struct LoopArgs {
 	int n_rows;       /* stored user rows (users with >= 1 nonzero)       */
 	int n_long;       /* the first n_long stored rows get a whole CTA     */
 	int n_cols;       /* stored item columns                              */
+	int n_long_cols;  /* the first n_long_cols get the deep (32-row) pipeline */
 	int user_lo;      /* first user of this shard; L holds rows user_lo.. */
 	double alpha2;    /* alpha * 2, exact                                 */
 	const int *row_id, *row_ptr, *col_idx, *epos;
