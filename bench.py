@@ -301,7 +301,7 @@ def main():
     k_ms = plan.profile_kernels(20)
     lo, hi = plan.user_range(0)
     e = inst.entries
-    mine = e[(e["row"] >= lo) & (e["row"] < hi)] if (comm or args.gpus == 1) else e
+    mine = e[(e["row"] >= lo) & (e["row"] < hi)]      # shard 0 (= this rank): the kernels timed above
     U_t, I_t = len(np.unique(mine["row"])), len(np.unique(mine["col"]))
     b1, b2, b_it = kernel_bytes(F, U_t, I_t, len(mine))
     peak, peak_src = peaks()
@@ -341,8 +341,9 @@ def main():
     barrier()
     e2e_s = max_over_ranks(time.perf_counter() - t0)
     e2e_value = inst.nnz * T * e2e_steps / e2e_s
-    nu = hi - lo if (comm or args.gpus == 1) else U
-    nloc = len(mine)
+    single_process_multi = (not comm) and args.gpus > 1
+    nu = U if single_process_multi else hi - lo
+    nloc = inst.nnz if single_process_multi else len(mine)
     h2d = nloc * (4 + 8 + 4 + 4) + nloc * 4 + 4 * (2 * U + 2 + U_t + I_t) * 2 + 8 * F * (nu + I)
     d2h = 8 * F * (nu + I) + 4 * nu
     if not np.array_equal(best[lo:hi] if comm else best, best2[lo:hi] if comm else best2):

@@ -1,0 +1,49 @@
+"""Worker of tests/test_gpu_parity.py::test_rank_mode_*: one process per GPU
+(launched with torch.distributed.run), users sharded by rank, R gradient
+all-reduced by NCCL inside the C-ABI library.  Rank 0 writes the result."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from recommender_system_b200 import api, synth  # noqa: E402
+
+
+def main():
+    out_path = sys.argv[1]
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    local = int(os.environ["LOCAL_RANK"])
+    dist.init_process_group("gloo")
+    uid = [api.Comm.unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(uid, src=0)
+    comm = api.Comm(world, rank, uid[0], local)
+    inst = synth.random_instance(300, 200, 20, 0.1, 25, 0.002, seed=33)
+    L, R = api.random_fill_LR(inst.users, inst.items, inst.features)
+    plan = api.Plan(inst.users, inst.items, inst.features, inst.entries, inst.alpha, comm=comm)
+    plan.set_factors(L, R)
+    plan.iterate(17)           # graph path (16) + one direct iteration
+    plan.iterate(8)
+    lo, hi = plan.user_range(0)
+    plan.get_factors(L, R)
+    best = plan.recommend()
+    plan.close()
+    comm.close()
+    parts = [None] * world
+    dist.all_gather_object(parts, (lo, hi, L[lo:hi].copy(), best[lo:hi].copy(), R.copy()))
+    if rank == 0:
+        best_all = np.full(inst.users, -2, dtype=np.int32)
+        for (a, b, rows, bb, _) in parts:
+            L[a:b] = rows
+            best_all[a:b] = bb
+        replicas_equal = all(np.array_equal(parts[0][4].view(np.uint64), p[4].view(np.uint64)) for p in parts)
+        np.savez(out_path, L=L, R=R, best=best_all, replicas_equal=replicas_equal,
+                 cut=np.array([p[0] for p in parts] + [inst.users]))
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -219,3 +219,38 @@ def test_multi_gpu_matches_sharded_oracle(gpu, oracle, nshards):
     assert bits_equal(L0, L1) and bits_equal(R0, R1)
     assert np.array_equal(best, oracle.recommend(inst.users, inst.items, inst.features,
                                                  inst.entries, L0, R0))
+
+
+@pytest.mark.parametrize("nranks", [2, 4, 8])
+def test_rank_mode_nccl_allreduce(gpu, oracle, tmp_path, nranks):
+    """One process per GPU (what bench.py does under torchrun): NCCL all-reduce of the
+    R gradient.  Replicas of R bit-identical to each other; against the oracle's N-shard
+    ordering bit-identical for 2 ranks (a+b is commutative) and within 1e-9 of max|x|
+    otherwise (NCCL's reduction order is its own)."""
+    import sys
+    import socket
+    if gpu.device_count() < nranks:
+        pytest.skip("needs %d GPUs" % nranks)
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    out = tmp_path / "rank_mode.npz"
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(nranks),
+           "--master-addr", "127.0.0.1", "--master-port", str(port),
+           os.path.join(ROOT, "tests", "rank_mode_worker.py"), str(out)]
+    p = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert p.returncode == 0, p.stderr[-3000:]
+    got = np.load(out)
+    inst = synth.random_instance(300, 200, 20, 0.1, 25, 0.002, seed=33)
+    cut = gpu.split_users(inst.users, inst.entries, nranks)
+    assert np.array_equal(got["cut"], cut)
+    L0, R0 = oracle.init_LR(inst.users, inst.items, inst.features)
+    oracle.factorize_sharded(inst.users, inst.items, inst.features, inst.entries, 25, inst.alpha, L0, R0, cut)
+    assert bool(got["replicas_equal"])
+    if nranks == 2:
+        assert bits_equal(L0, got["L"]) and bits_equal(R0, got["R"])
+    else:
+        for a, b in ((L0, got["L"]), (R0, got["R"])):
+            assert np.max(np.abs(a - b)) <= 1e-9 * np.max(np.abs(a))
+    assert np.array_equal(got["best"], oracle.recommend(inst.users, inst.items, inst.features,
+                                                        inst.entries, L0, R0))
