@@ -156,16 +156,12 @@ def time_reference(inst, kind, budget_s, threads):
 
 
 def kernel_bytes(F, U_t, I_t, nnz):
-    """Algorithmic (compulsory) HBM bytes of ONE launch of each loop kernel, DESIGN.md section 4:
-    by-user pass : L row read + written once, every touched R row read once, per nonzero
-                   item index + rating + by-item position read and e written (4+8+4+8);
-    by-item pass : R row read + written once, every touched L row read once, per nonzero
-                   user index + e read (4+8).
-    iteration    : SURVEY.md 8(d) figure 16*F*(U_t+I_t) + 12*nnz (one fused pass; stricter)."""
-    k1 = 16 * F * U_t + 8 * F * I_t + 24 * nnz
-    k2 = 16 * F * I_t + 8 * F * U_t + 12 * nnz
+    """Algorithmic (compulsory) HBM bytes of one ITERATION, SURVEY.md 8(d): every touched
+    factor element read once and written once, A read once: 16*F*(U_t+I_t) + 12*nnz.  (The
+    per-launch figures of the individual kernels come from the library,
+    mfgpu_plan_kernel_bytes)"""
     it = 16 * F * (U_t + I_t) + 12 * nnz
-    return k1, k2, it
+    return None, None, it
 
 
 def ncu_traffic(workload, kernel):
@@ -299,21 +295,22 @@ def main():
 
     # per-kernel device times for the roofline (all ranks: the exchange is collective)
     k_ms = plan.profile_kernels(20)
+    k_bytes = plan.kernel_bytes()
     lo, hi = plan.user_range(0)
     e = inst.entries
     mine = e[(e["row"] >= lo) & (e["row"] < hi)]      # shard 0 (= this rank): the kernels timed above
     U_t, I_t = len(np.unique(mine["row"])), len(np.unique(mine["col"]))
-    b1, b2, b_it = kernel_bytes(F, U_t, I_t, len(mine))
+    _, _, b_it = kernel_bytes(F, U_t, I_t, len(mine))
     peak, peak_src = peaks()
-    dom = 0 if k_ms[0] >= k_ms[1] else 1
-    dom_name = ["k_update_L", "k_update_R"][dom]
-    dom_bytes = [b1, b2][dom]
-    ach = dom_bytes / (k_ms[dom] * 1e-3) / 1e9 if k_ms[dom] > 0 else 0.0
+    loop_kernels = ["k_update_L", "k_dot", "k_chain_bulk", "k_chain_deep"]
+    dom_name = max(loop_kernels, key=lambda k: k_ms[k])
+    dom_bytes = k_bytes[dom_name]
+    ach = dom_bytes / (k_ms[dom_name] * 1e-3) / 1e9 if k_ms[dom_name] > 0 else 0.0
     it_ms = region_ms / (args.steps * T)
     roofline = {"bound": "hbm", "kernel": dom_name, "achieved": ach, "peak": peak, "unit": "GB/s",
                 "frac": ach / peak, "traffic": ncu_traffic(args.workload, dom_name),
                 "peak_source": peak_src, "algorithmic_bytes_per_launch": dom_bytes,
-                "kernel_ms": {"k_update_L": k_ms[0], "k_update_R": k_ms[1], "exchange_apply": k_ms[2]},
+                "kernel_ms": k_ms, "kernel_algorithmic_bytes": k_bytes,
                 "iteration": {"algorithmic_bytes": b_it, "ms": it_ms,
                               "achieved": b_it / (it_ms * 1e-3) / 1e9,
                               "frac": b_it / (it_ms * 1e-3) / 1e9 / peak}}

@@ -123,9 +123,12 @@ int mfgpu_plan_save_factors(mfgpu_plan *plan);
 int mfgpu_plan_restore_factors(mfgpu_plan *plan);
 /* Average device time (CUDA events on the plan's stream, shard 0) of `reps`
  * back-to-back launches of each loop kernel on the current factors; the factors
- * are left unchanged.  ms[0] = by-user pass (k_update_L), ms[1] = by-item pass
- * (k_update_R), ms[2] = exchange + apply (N shards, else 0). */
-int mfgpu_plan_profile_kernels(mfgpu_plan *plan, int reps, float ms[3]);
+ * are left unchanged.  ms[0] = by-user pass of the short rows (k_update_L),
+ * ms[1] = dots of the long rows (k_dot), ms[2] / ms[3] = sequential accumulations
+ * (k_chain, bulk / deep launch), ms[4] = exchange + apply (rank mode, else 0). */
+int mfgpu_plan_profile_kernels(mfgpu_plan *plan, int reps, float ms[5]);
+/* Algorithmic (compulsory) bytes of one launch of each of those kernels on shard 0. */
+int mfgpu_plan_kernel_bytes(mfgpu_plan *plan, long long bytes[5]);
 /* Device stopwatch on the plan's stream(s): start records an event, stop records
  * another, waits for it and returns the elapsed device time (max over the
  * plan's devices).  Everything enqueued on the plan in between is covered. */

@@ -30,12 +30,13 @@ EXPORTS = [
     "mfgpu_plan_last_loop_ms", "mfgpu_plan_recommend", "mfgpu_plan_last_recommend_ms",
     "mfgpu_plan_user_range", "mfgpu_plan_launch_count", "mfgpu_plan_bytes_per_iter",
     "mfgpu_plan_set_option", "mfgpu_plan_save_factors", "mfgpu_plan_restore_factors",
-    "mfgpu_plan_profile_kernels", "mfgpu_plan_timer_start", "mfgpu_plan_timer_stop",
+    "mfgpu_plan_profile_kernels", "mfgpu_plan_kernel_bytes", "mfgpu_plan_timer_start", "mfgpu_plan_timer_stop",
     "mfgpu_comm_unique_id", "mfgpu_comm_create", "mfgpu_comm_destroy",
     "mfgpu_split_users", "mfgpu_random_fill_LR", "mfgpu_mask_stats",
 ]
 
 UID_BYTES = 128
+KERNELS = ["k_update_L", "k_dot", "k_chain_bulk", "k_chain_deep", "exchange_apply"]
 
 
 class MatFactError(RuntimeError):
@@ -83,6 +84,7 @@ def lib():
     L.mfgpu_plan_save_factors.argtypes = [vp]
     L.mfgpu_plan_restore_factors.argtypes = [vp]
     L.mfgpu_plan_profile_kernels.argtypes = [vp, i, ctypes.POINTER(ctypes.c_float)]
+    L.mfgpu_plan_kernel_bytes.argtypes = [vp, ctypes.POINTER(ctypes.c_longlong)]
     L.mfgpu_plan_timer_start.argtypes = [vp]
     L.mfgpu_plan_timer_stop.argtypes = [vp, ctypes.POINTER(ctypes.c_float)]
     L.mfgpu_comm_unique_id.argtypes = [vp]
@@ -284,9 +286,14 @@ class Plan:
         _check(lib().mfgpu_plan_restore_factors(self._h))
 
     def profile_kernels(self, reps=20):
-        ms = (ctypes.c_float * 3)()
+        ms = (ctypes.c_float * 5)()
         _check(lib().mfgpu_plan_profile_kernels(self._h, reps, ms))
-        return [ms[0], ms[1], ms[2]]
+        return dict(zip(KERNELS, [float(x) for x in ms]))
+
+    def kernel_bytes(self):
+        b = (ctypes.c_longlong * 5)()
+        _check(lib().mfgpu_plan_kernel_bytes(self._h, b))
+        return dict(zip(KERNELS, [int(x) for x in b]))
 
     def close(self):
         if self._h:

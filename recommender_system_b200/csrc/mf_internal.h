@@ -41,16 +41,18 @@ struct mf_shard {
 	double *d_val, *d_e_csc, *d_e_csr;
 	int *d_mask_ptr, *d_mask_col, *d_first_free;
 	int *d_item_slot, *d_touched_item;       /* N-shard only */
+	int *d_chunk_row, *d_chunk_pos;          /* chunks of the long rows (k_dot) */
 	/* factors, double buffered; L holds the shard's users only */
 	double *L[2], *R[2];
 	double *G[2];                            /* N-shard only: partial R gradient */
 	double *L_keep, *R_keep;                 /* mfgpu_plan_save_factors           */
 	mf::LoopArgs la;
 	int warps;                               /* 8 or 1: k_update_L template      */
-	int k1_blocks, k2_blocks, k2_long_blocks;
+	int k1_blocks, dot_blocks;
+	long long kbytes[5];                     /* algorithmic bytes per launch of each kernel */
 	size_t k1_smem;
 	cudaGraphExec_t gexec[2];                /* by starting parity                */
-	cudaEvent_t ev0, ev1, ev_g[2], ev_t0, ev_t1, ev_fork, ev_join;
+	cudaEvent_t ev0, ev1, ev_g[2], ev_t0, ev_t1, ev_fork, ev_join, ev_a, ev_b;
 	/* arg-max scratch */
 	double *part_v;
 	int *part_j, *nan_first, *d_best;
@@ -70,7 +72,7 @@ struct mfgpu_plan {
 	long long launches;
 	float loop_ms, rec_ms;
 	/* options */
-	int opt_graph, opt_graph_iters, opt_long_row, opt_long_col, opt_ch;
+	int opt_graph, opt_graph_iters, opt_long_row, opt_long_col, opt_ch, opt_chain_ring;
 };
 
 /* ---- shared helpers (defined in mf_capi.cu) ----------------------------------- */

@@ -55,10 +55,14 @@ int mf_kernels_prepare(int warps, size_t k1_smem)
 {
 	const auto attr = cudaFuncAttributeMaxDynamicSharedMemorySize;
 	if (warps == 8) {
-		CK(cudaFuncSetAttribute(mf::k_update_L<8, false>, attr, (int)k1_smem));
-		CK(cudaFuncSetAttribute(mf::k_update_L<8, true>, attr, (int)k1_smem));
+		CK(cudaFuncSetAttribute(mf::k_update_L<8>, attr, (int)k1_smem));
+		CK(cudaFuncSetAttribute(mf::k_dot<8>, attr, (int)k1_smem));
+		CK(cudaFuncSetAttribute(mf::k_chain<8, mf::CHAIN_DEEP_RING>, attr,
+		                        8 * mf::RING_DEEP_ROWS * mf::RING_DEEP_STAGES * 32 * (int)sizeof(double)));
+		CK(cudaFuncSetAttribute(mf::k_chain<8, mf::CHAIN_BULK_RING>, attr,
+		                        8 * mf::RING_BULK_ROWS * mf::RING_BULK_STAGES * 32 * (int)sizeof(double)));
 	} else {
-		CK(cudaFuncSetAttribute(mf::k_update_L<1, false>, attr, (int)k1_smem));
+		CK(cudaFuncSetAttribute(mf::k_update_L<1>, attr, (int)k1_smem));
 	}
 	return MFGPU_OK;
 }
@@ -67,63 +71,118 @@ static int local_shards(const mfgpu_plan *pl) { return pl->comm ? 1 : pl->nshard
 
 /* ---- launches ------------------------------------------------------------------ */
 
-static int launch_update_L(mfgpu_plan *pl, mf_shard *s, int c)
+static mf::ChainSide side_L(const mfgpu_plan *, const mf_shard *s, int c, int begin, int end)
 {
-	const int n_long = s->la.n_long;
-	if (n_long > 0) {
-		/* the few whole-CTA rows run on a second stream beside the short-row launch */
-		CK(cudaEventRecord(s->ev_fork, s->st));
-		CK(cudaStreamWaitEvent(s->st2, s->ev_fork, 0));
-		mf::k_update_L<8, true><<<n_long, 256, s->k1_smem, s->st2>>>(s->la, s->L[c], s->L[1 - c], s->R[c]);
-		CK(cudaGetLastError());
-		CK(cudaEventRecord(s->ev_join, s->st2));
-		pl->launches++;
-	}
-	if (s->k1_blocks > 0) {
-		if (s->warps == 8)
-			mf::k_update_L<8, false><<<s->k1_blocks, 256, s->k1_smem, s->st>>>(s->la, s->L[c], s->L[1 - c],
-			                                                                  s->R[c]);
-		else
-			mf::k_update_L<1, false><<<s->k1_blocks, 32, s->k1_smem, s->st>>>(s->la, s->L[c], s->L[1 - c],
-			                                                                 s->R[c]);
-		CK(cudaGetLastError());
-		pl->launches++;
-	}
-	if (n_long > 0)
-		CK(cudaStreamWaitEvent(s->st, s->ev_join, 0));
+	mf::ChainSide d;
+	d.begin = begin; d.end = end;
+	d.ptr = s->d_row_ptr; d.idx = s->d_col_idx; d.id = s->d_row_id;
+	d.e = s->d_e_csr;
+	d.init = s->L[c]; d.src = s->R[c]; d.out = s->L[1 - c];
+	d.own_off = s->user_lo; d.src_off = 0;
+	d.out_slot = nullptr;
+	return d;
+}
+
+static mf::ChainSide side_R(const mfgpu_plan *pl, const mf_shard *s, int c, int begin, int end, double *rout)
+{
+	mf::ChainSide d;
+	d.begin = begin; d.end = end;
+	d.ptr = s->d_col_ptr; d.idx = s->d_row_idx; d.id = s->d_col_id;
+	d.e = s->d_e_csc;
+	d.init = pl->nshards > 1 ? nullptr : s->R[c];    /* N shards: the gradient G starts from 0.0 */
+	d.src = s->L[c]; d.out = rout;
+	d.own_off = 0; d.src_off = s->user_lo;
+	d.out_slot = pl->nshards > 1 ? s->d_item_slot : nullptr;
+	return d;
+}
+
+enum { K_FUSED = 1, K_DOT = 2, K_BULK = 4, K_DEEP = 8, K_ALL = 15 };
+
+static int launch_fused(mfgpu_plan *pl, mf_shard *s, int c, cudaStream_t st)
+{
+	if (s->k1_blocks <= 0)
+		return MFGPU_OK;
+	if (s->warps == 8)
+		mf::k_update_L<8><<<s->k1_blocks, 256, s->k1_smem, st>>>(s->la, s->L[c], s->L[1 - c], s->R[c]);
+	else
+		mf::k_update_L<1><<<s->k1_blocks, 32, s->k1_smem, st>>>(s->la, s->L[c], s->L[1 - c], s->R[c]);
+	CK(cudaGetLastError());
+	pl->launches++;
 	return MFGPU_OK;
 }
 
-static int launch_update_R(mfgpu_plan *pl, mf_shard *s, int c, double *out)
+static int launch_dot(mfgpu_plan *pl, mf_shard *s, int c, cudaStream_t st)
 {
-	const int n_long = s->la.n_long_cols;
-	if (s->k2_long_blocks > 0) {
-		/* the few longest columns: deep register pipeline, beside the bulk on the second stream */
-		CK(cudaEventRecord(s->ev_fork, s->st));
-		CK(cudaStreamWaitEvent(s->st2, s->ev_fork, 0));
-		mf::k_update_R<8, 32><<<s->k2_long_blocks, 256, 0, s->st2>>>(s->la, 0, n_long, s->L[c], s->R[c], out);
-		CK(cudaGetLastError());
-		CK(cudaEventRecord(s->ev_join, s->st2));
-		pl->launches++;
+	if (s->dot_blocks <= 0)
+		return MFGPU_OK;
+	mf::k_dot<8><<<s->dot_blocks, 256, s->k1_smem, st>>>(s->la, s->L[c], s->R[c]);
+	CK(cudaGetLastError());
+	pl->launches++;
+	return MFGPU_OK;
+}
+
+static int launch_chain(mfgpu_plan *pl, mf_shard *s, int c, double *rout, bool deep, cudaStream_t st)
+{
+	const mf::LoopArgs &a = s->la;
+	const mf::ChainSide A = deep ? side_L(pl, s, c, 0, a.n_deep_rows) : side_L(pl, s, c, a.n_deep_rows, a.n_long);
+	const mf::ChainSide B = deep ? side_R(pl, s, c, 0, a.n_deep_cols, rout)
+	                             : side_R(pl, s, c, a.n_deep_cols, a.n_cols, rout);
+	const long ng = (a.F + 31) / 32;
+	const long wa = (long)(A.end - A.begin) * ng, wb = (long)(B.end - B.begin) * ng;
+	const long blocks = (wa + wb + 7) / 8;
+	if (blocks <= 0)
+		return MFGPU_OK;
+	const size_t ring_deep = (size_t)8 * mf::RING_DEEP_ROWS * mf::RING_DEEP_STAGES * 32 * sizeof(double);
+	const size_t ring_bulk = (size_t)8 * mf::RING_BULK_ROWS * mf::RING_BULK_STAGES * 32 * sizeof(double);
+	const bool ring = pl->opt_chain_ring != 0;
+	if (deep && ring)
+		mf::k_chain<8, mf::CHAIN_DEEP_RING><<<(unsigned)blocks, 256, ring_deep, st>>>(A, B, wa, a.F, a.ld);
+	else if (deep)
+		mf::k_chain<8, mf::CHAIN_DEEP_REGS><<<(unsigned)blocks, 256, 0, st>>>(A, B, wa, a.F, a.ld);
+	else if (ring)
+		mf::k_chain<8, mf::CHAIN_BULK_RING><<<(unsigned)blocks, 256, ring_bulk, st>>>(A, B, wa, a.F, a.ld);
+	else
+		mf::k_chain<8, mf::CHAIN_BULK_REGS><<<(unsigned)blocks, 256, 0, st>>>(A, B, wa, a.F, a.ld);
+	CK(cudaGetLastError());
+	pl->launches++;
+	return MFGPU_OK;
+}
+
+static bool has_deep(const mf_shard *s) { return s->la.n_deep_rows > 0 || s->la.n_deep_cols > 0; }
+
+/* The kernels of one iteration on one shard; R-side results go to rout.
+ *   st : k_update_L(short rows) ------------\                /-> k_chain<bulk> --\
+ *   st2: k_dot(long rows) ------------------- both done ----+--> k_chain<deep> ---+-> st
+ * (k_chain needs every e_n: the short rows' from k_update_L, the long rows' from k_dot) */
+static int enqueue_loop_kernels(mfgpu_plan *pl, mf_shard *s, int c, double *rout)
+{
+	const bool second = s->dot_blocks > 0 || has_deep(s);
+	if (!second) {
+		TRY(launch_fused(pl, s, c, s->st));
+		return launch_chain(pl, s, c, rout, false, s->st);
 	}
-	if (s->k2_blocks > 0) {
-		mf::k_update_R<8, 8><<<s->k2_blocks, 256, 0, s->st>>>(s->la, n_long, s->la.n_cols, s->L[c], s->R[c], out);
-		CK(cudaGetLastError());
-		pl->launches++;
-	}
-	if (s->k2_long_blocks > 0)
-		CK(cudaStreamWaitEvent(s->st, s->ev_join, 0));
+	CK(cudaEventRecord(s->ev_fork, s->st));
+	CK(cudaStreamWaitEvent(s->st2, s->ev_fork, 0));
+	TRY(launch_fused(pl, s, c, s->st));
+	CK(cudaEventRecord(s->ev_a, s->st));
+	TRY(launch_dot(pl, s, c, s->st2));
+	CK(cudaEventRecord(s->ev_b, s->st2));
+	CK(cudaStreamWaitEvent(s->st, s->ev_b, 0));
+	TRY(launch_chain(pl, s, c, rout, false, s->st));
+	CK(cudaStreamWaitEvent(s->st2, s->ev_a, 0));
+	TRY(launch_chain(pl, s, c, rout, true, s->st2));
+	CK(cudaEventRecord(s->ev_join, s->st2));
+	CK(cudaStreamWaitEvent(s->st, s->ev_join, 0));
 	return MFGPU_OK;
 }
 
 /* one iteration of a 1-shard plan, or of one rank in rank mode */
 static int enqueue_iteration(mfgpu_plan *pl, mf_shard *s, int c)
 {
-	TRY(launch_update_L(pl, s, c));
 	if (pl->nshards == 1)
-		return launch_update_R(pl, s, c, s->R[1 - c]);
+		return enqueue_loop_kernels(pl, s, c, s->R[1 - c]);
 	/* rank mode */
-	TRY(launch_update_R(pl, s, c, s->G[0]));
+	TRY(enqueue_loop_kernels(pl, s, c, s->G[0]));
 	const size_t count = (size_t)pl->n_touched * pl->ld;
 	if (count == 0)
 		return MFGPU_OK;
@@ -145,8 +204,7 @@ static int enqueue_iteration_peer(mfgpu_plan *pl, int c, int t)
 	for (int g = 0; g < pl->nshards; g++) {
 		mf_shard *s = &pl->sh[g];
 		CK(cudaSetDevice(s->dev));
-		TRY(launch_update_L(pl, s, c));
-		TRY(launch_update_R(pl, s, c, s->G[gb]));
+		TRY(enqueue_loop_kernels(pl, s, c, s->G[gb]));
 		CK(cudaEventRecord(s->ev_g[gb], s->st));
 	}
 	const long total = (long)pl->n_touched * pl->F;
@@ -196,7 +254,10 @@ static int build_graph(mfgpu_plan *pl, mf_shard *s, int c, int n)
 
 static long long launches_per_iteration(const mfgpu_plan *pl, const mf_shard *s)
 {
-	long long n = (s->la.n_long > 0) + (s->k1_blocks > 0) + (s->k2_long_blocks > 0) + (s->k2_blocks > 0);
+	const mf::LoopArgs &a = s->la;
+	long long n = (s->k1_blocks > 0) + (s->dot_blocks > 0);
+	n += (a.n_long - a.n_deep_rows > 0 || a.n_cols - a.n_deep_cols > 0);
+	n += (a.n_deep_rows > 0 || a.n_deep_cols > 0);
 	if (pl->nshards > 1 && (long)pl->n_touched * pl->F > 0)
 		n += 1;
 	return n;
@@ -261,14 +322,17 @@ extern "C" int mfgpu_plan_last_loop_ms(mfgpu_plan *pl, float *ms)
 	return MFGPU_OK;
 }
 
-/* Per-kernel device times for the roofline report of bench.py. */
-extern "C" int mfgpu_plan_profile_kernels(mfgpu_plan *pl, int reps, float ms[3])
+/* Per-kernel device times for the roofline report of bench.py: each kernel `reps` times back
+ * to back on the plan's stream.  ms[0] k_update_L (short rows), [1] k_dot (long rows),
+ * [2] k_chain<bulk>, [3] k_chain<deep>, [4] exchange + apply (rank mode). */
+extern "C" int mfgpu_plan_profile_kernels(mfgpu_plan *pl, int reps, float ms[5])
 {
 	if (!pl || !ms || reps < 1)
 		return mf_fail(MFGPU_EINVAL, "bad argument");
 	if (!pl->have_factors)
 		return mf_fail(MFGPU_EINVAL, "mfgpu_plan_set_factors has not been called");
-	ms[0] = ms[1] = ms[2] = 0.f;
+	for (int k = 0; k < 5; k++)
+		ms[k] = 0.f;
 	if (pl->F == 0 || pl->nnz == 0)
 		return MFGPU_OK;
 	mf_shard *s = &pl->sh[0];
@@ -276,15 +340,19 @@ extern "C" int mfgpu_plan_profile_kernels(mfgpu_plan *pl, int reps, float ms[3])
 	const long long before = pl->launches;
 	CK(cudaSetDevice(s->dev));
 	double *rout = pl->nshards == 1 ? s->R[1 - c] : s->G[0];
-	for (int phase = 0; phase < 3; phase++) {
-		if (phase == 2 && !(pl->comm && (size_t)pl->n_touched * pl->ld > 0))
+	for (int phase = 0; phase < 5; phase++) {
+		if (phase == 4 && !(pl->comm && (size_t)pl->n_touched * pl->ld > 0))
 			break;
 		CK(cudaEventRecord(s->ev0, s->st));
 		for (int r = 0; r < reps; r++) {
 			if (phase == 0)
-				TRY(launch_update_L(pl, s, c));
+				TRY(launch_fused(pl, s, c, s->st));
 			else if (phase == 1)
-				TRY(launch_update_R(pl, s, c, rout));
+				TRY(launch_dot(pl, s, c, s->st));
+			else if (phase == 2)
+				TRY(launch_chain(pl, s, c, rout, false, s->st));
+			else if (phase == 3)
+				TRY(launch_chain(pl, s, c, rout, true, s->st));
 			else {
 				NCK(g_nccl.AllReduce(s->G[0], s->G[1], (size_t)pl->n_touched * pl->ld, 8, 0,
 				                     pl->comm->nccl, s->st));

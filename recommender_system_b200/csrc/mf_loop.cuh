@@ -11,18 +11,17 @@
  * in file order of that column's nonzeros.  The kernels keep exactly that
  * order, so one GPU reproduces the reference's doubles bit for bit:
  *
- *   k_update_L  by-user pass.  A warp owns a user row: the R rows of up to CH of
- *               its nonzeros are staged in shared memory with 16-byte cp.async,
- *               e_n is computed with one lane per nonzero walking k
- *               sequentially (the dot of mat2d.c:133-137), then L_new[i][k] is
- *               accumulated with lanes over features walking the nonzeros
- *               sequentially.  Rows longer than a threshold get a whole CTA:
- *               all warps compute dots, then every warp runs the sequential
- *               accumulation of 32 features with the register pipeline below.
- *               Writes e_n at its by-item position.
- *   k_update_R  by-item pass.  A warp owns (item, 32 features) and walks the
- *               item's nonzeros in file order; the gathered L values run two
- *               blocks of 32 rows ahead of the accumulation in registers.
+ *   k_update_L  short user rows, one warp per row: the R rows of up to CH of its nonzeros
+ *               stream through shared-memory tiles (16-byte cp.async) while e_n is computed
+ *               with one lane per nonzero walking k sequentially (the dot of
+ *               mat2d.c:133-137); then L_new[i][k] is accumulated with lanes over features
+ *               walking the nonzeros in order.  Writes e_n at its by-item position.
+ *   k_dot       the same dot phase for the long rows, one warp per chunk of <= 32 nonzeros,
+ *               so a row of thousands of nonzeros is spread over many warps.
+ *   k_chain     the sequential accumulations that remain: L rows of the long users and all
+ *               R rows.  One warp per (row or column, 32 features) walks the nonzeros in
+ *               file order with the gathered operands running ahead in registers (a deep
+ *               variant for the few longest chains, a light one for the bulk).
  *   k_apply_R   N shards only: R_new = R_old + G (G = sum of the partial
  *               gradients, the MPI_Iallreduce of matFact-mpi.c:208).
  *
@@ -45,21 +44,6 @@ constexpr unsigned FULL = 0xffffffffu;
 __device__ __forceinline__ double2 ld2(const double *p)
 {
 	return *reinterpret_cast<const double2 *>(p);
-}
-
-/* e for the nonzero of this lane: sequential-k dot, mat2d.c:133-137. */
-__device__ __forceinline__ double seq_dot_smem(const double *Ls, const double *Rr, int F)
-{
-	double s = 0.0;
-	int k = 0;
-	for (; k + 1 < F; k += 2) {
-		const double2 l = ld2(Ls + k), r = ld2(Rr + k);
-		s = __dadd_rn(s, __dmul_rn(l.x, r.x));
-		s = __dadd_rn(s, __dmul_rn(l.y, r.y));
-	}
-	if (k < F)
-		s = __dadd_rn(s, __dmul_rn(Ls[k], Rr[k]));
-	return s;
 }
 
 constexpr int KT = 16;        /* features per staged tile of the dot phase          */
@@ -161,84 +145,22 @@ __device__ __forceinline__ void row_update(const double *init, double *Lout,
 			Lout[off[g]] = acc[g];
 }
 
-/* ---- register pipeline of the sequential accumulations ----------------------------------
+/* ---- register pipelines of the sequential accumulations ------------------------------------
  *
  * acc = ((acc + ev[0]*x[0]) + ev[1]*x[1]) + ...  with x[n] = srck[idx[n]*ld], n < m, in order.
- * One warp, lane = feature.  The additions form one dependent chain per lane, so the
- * only way to go fast is to keep the operands ready: lane l holds (idx, ev) of nonzero
- * 32q + l of block q and broadcasts them by shuffle, and the gathered x of the next block
- * of 32 nonzeros are loaded into registers while the current block is being added.
+ * One warp, lane = feature.  The additions form one dependent chain per lane, so the only
+ * way to go fast is to have the operands ready: lane l holds (idx, ev) of nonzero 32q + l of
+ * index block q and broadcasts them by shuffle, and the gathered x run ahead of the chain in
+ * registers.  Past the end of the list the last nonzero is loaded again (never added), so
+ * no load is predicated: a predicated load is followed by a select that waits for it.
+ *
+ * chain_deep: sub-blocks of 16 rows, four register buffers -> 48 rows in flight ahead of
+ * the chain and the index blocks two blocks (64 rows) ahead; ~170 registers, 8 warps/SM.
+ * For the few chains so long that they alone decide how long a launch lasts.
  */
-__device__ __forceinline__ void gather_block(double (&X)[32], int bi, const double *__restrict__ srck,
-                                             int ld)
-{
-	/* unconditional loads (every lane's bi is a valid row, see chain_regs): a predicated
-	 * load would be followed by a select that waits for it and serialise the gather */
-#pragma unroll
-	for (int r = 0; r < 32; r++)
-		X[r] = srck[(size_t)__shfl_sync(FULL, bi, r) * ld];
-}
-
-__device__ __forceinline__ double chain_block(double acc, const double (&X)[32], double be, int rows)
-{
-	if (rows == 32) {
-#pragma unroll
-		for (int r = 0; r < 32; r++)
-			acc = __dadd_rn(acc, __dmul_rn(__shfl_sync(FULL, be, r), X[r]));
-	} else {
-#pragma unroll
-		for (int r = 0; r < 32; r++) {
-			const double e = __shfl_sync(FULL, be, r);
-			if (r < rows)
-				acc = __dadd_rn(acc, __dmul_rn(e, X[r]));
-		}
-	}
-	return acc;
-}
-
-__device__ __forceinline__ double chain_regs(double acc, int lane,
-                                             const int *__restrict__ idx, const double *__restrict__ ev,
-                                             int m, const double *__restrict__ srck, int ld)
-{
-	const int nblk = (m + 31) >> 5;
-	int iA = 0, iB = 0, iC = 0;
-	double eA = 0.0, eB = 0.0, eC = 0.0;
-	auto load_blk = [&](int q, int &bi, double &be) {
-		const int n = min(q * 32 + lane, m - 1);   /* past the end: repeat the last row (never added) */
-		bi = idx[n];
-		be = ev[n];
-	};
-	auto rows_of = [&](int q) { return min(32, m - q * 32); };
-	double XA[32], XB[32];
-	load_blk(0, iA, eA);
-	load_blk(1, iB, eB);
-	gather_block(XA, iA, srck, ld);
-	for (int q = 0; q < nblk; q += 2) {
-		if (q + 1 < nblk)
-			gather_block(XB, iB, srck, ld);
-		load_blk(q + 2, iC, eC);
-		acc = chain_block(acc, XA, eA, rows_of(q));
-		if (q + 2 < nblk)
-			gather_block(XA, iC, srck, ld);
-		iA = iC;
-		eA = eC;
-		load_blk(q + 3, iC, eC);
-		if (q + 1 < nblk)
-			acc = chain_block(acc, XB, eB, rows_of(q + 1));
-		iB = iC;
-		eB = eC;
-	}
-	return acc;
-}
-
-/* Same accumulation with blocks of B = 8 or 16 nonzeros and two small register buffers:
- * ~64 registers instead of ~170, so four times as many warps are resident.  This is the
- * variant for launches with many more (item, feature group) chains than warp slots, where
- * the other warps hide the gather latency; the 32-row variant above is for the few chains
- * that are so long that they alone decide how long the launch lasts. */
 template <int B>
-__device__ __forceinline__ void gather_small(double (&X)[B], int bi, int lane0,
-                                             const double *__restrict__ srck, int ld)
+__device__ __forceinline__ void gather_rows(double (&X)[B], int bi, int lane0,
+                                            const double *__restrict__ srck, int ld)
 {
 #pragma unroll
 	for (int r = 0; r < B; r++)
@@ -246,7 +168,7 @@ __device__ __forceinline__ void gather_small(double (&X)[B], int bi, int lane0,
 }
 
 template <int B>
-__device__ __forceinline__ double chain_small(double acc, const double (&X)[B], double be, int lane0, int rows)
+__device__ __forceinline__ double chain_rows(double acc, const double (&X)[B], double be, int lane0, int rows)
 {
 	if (rows >= B) {
 #pragma unroll
@@ -263,8 +185,53 @@ __device__ __forceinline__ double chain_small(double acc, const double (&X)[B], 
 	return acc;
 }
 
+__device__ __forceinline__ double chain_deep(double acc, int lane, const int *__restrict__ idx,
+                                             const double *__restrict__ ev, int m,
+                                             const double *__restrict__ srck, int ld)
+{
+	auto load_blk = [&](int q, int &bi, double &be) {
+		const int n = min(q * 32 + lane, m - 1);
+		bi = idx[n];
+		be = ev[n];
+	};
+	int i0, i1, i2, i3;
+	double e0, e1, e2, e3;
+	load_blk(0, i0, e0);
+	load_blk(1, i1, e1);
+	load_blk(2, i2, e2);
+	load_blk(3, i3, e3);
+	double X0[16], X1[16], X2[16], X3[16];
+	gather_rows<16>(X0, i0, 0, srck, ld);
+	gather_rows<16>(X1, i0, 16, srck, ld);
+	gather_rows<16>(X2, i1, 0, srck, ld);
+	/* per trip: index blocks q, q+1 = four sub-blocks; each sub-block is gathered three
+	 * sub-blocks before it is added */
+	for (int q = 0; q * 32 < m; q += 2) {
+		const int left = m - q * 32;
+		gather_rows<16>(X3, i1, 16, srck, ld);
+		acc = chain_rows<16>(acc, X0, e0, 0, left);
+		gather_rows<16>(X0, i2, 0, srck, ld);
+		if (left > 16)
+			acc = chain_rows<16>(acc, X1, e0, 16, left - 16);
+		gather_rows<16>(X1, i2, 16, srck, ld);
+		if (left > 32)
+			acc = chain_rows<16>(acc, X2, e1, 0, left - 32);
+		gather_rows<16>(X2, i3, 0, srck, ld);
+		if (left > 48)
+			acc = chain_rows<16>(acc, X3, e1, 16, left - 48);
+		i0 = i2; e0 = e2;
+		i1 = i3; e1 = e3;
+		load_blk(q + 4, i2, e2);
+		load_blk(q + 5, i3, e3);
+	}
+	return acc;
+}
+
+/* chain_bulk: sub-blocks of B = 8 rows and two register buffers: ~74 registers, so three
+ * times as many warps are resident.  For launches with many more chains than warp slots,
+ * where the other warps hide the gather latency. */
 template <int B>
-__device__ __forceinline__ double chain_regs_small(double acc, int lane, const int *__restrict__ idx,
+__device__ __forceinline__ double chain_bulk(double acc, int lane, const int *__restrict__ idx,
                                                    const double *__restrict__ ev, int m,
                                                    const double *__restrict__ srck, int ld)
 {
@@ -280,22 +247,22 @@ __device__ __forceinline__ double chain_regs_small(double acc, int lane, const i
 	load_blk(0, iCur, eCur);
 	load_blk(1, iNxt, eNxt);
 	double X0[B], X1[B];
-	gather_small<B>(X0, iCur, 0, srck, ld);
+	gather_rows<B>(X0, iCur, 0, srck, ld);
 	for (int ib = 0; ib < nib; ib++) {
 		const int rows_ib = min(32, m - ib * 32);
 #pragma unroll
 		for (int sb = 0; sb < NSB; sb++) {
 			/* next sub-block in flight while this one is added */
 			if (sb + 1 < NSB) {
-				if (sb & 1) gather_small<B>(X0, iCur, (sb + 1) * B, srck, ld);
-				else        gather_small<B>(X1, iCur, (sb + 1) * B, srck, ld);
+				if (sb & 1) gather_rows<B>(X0, iCur, (sb + 1) * B, srck, ld);
+				else        gather_rows<B>(X1, iCur, (sb + 1) * B, srck, ld);
 			} else {
-				gather_small<B>(X0, iNxt, 0, srck, ld);     /* NSB even: sub-block 0 lives in X0 */
+				gather_rows<B>(X0, iNxt, 0, srck, ld);     /* NSB even: sub-block 0 lives in X0 */
 			}
 			const int rows = rows_ib - sb * B;
 			if (rows > 0)
-				acc = (sb & 1) ? chain_small<B>(acc, X1, eCur, sb * B, rows)
-				               : chain_small<B>(acc, X0, eCur, sb * B, rows);
+				acc = (sb & 1) ? chain_rows<B>(acc, X1, eCur, sb * B, rows)
+				               : chain_rows<B>(acc, X0, eCur, sb * B, rows);
 		}
 		iCur = iNxt;
 		eCur = eNxt;
@@ -304,14 +271,122 @@ __device__ __forceinline__ double chain_regs_small(double acc, int lane, const i
 	return acc;
 }
 
+/* chain_ring: the same accumulation with the gathered rows landing in a per-warp ring in
+ * shared memory instead of registers: RS rows per stage, NST stages, stage s+NST-1 issued
+ * (16-byte cp.async, a half-warp per row, so one instruction moves two rows) before stage
+ * s is added.  cp.async groups complete in order and wait_group<N> leaves the N newest
+ * pending, which register loads cannot express: the six scoreboard slots of a warp are
+ * shared by all loads in flight, so waiting for an old block also waits for the newest one.
+ * src_g = first of the group's 32 features in row 0 of the gathered factor; gw = number of
+ * valid doubles of the group in a row (even, <= 32). */
+template <int RS, int NST>
+__device__ __forceinline__ double chain_ring(double acc, int lane, const int *__restrict__ idx,
+                                             const double *__restrict__ ev, int m,
+                                             const double *__restrict__ src_g, int ld, int gw, double *ring)
+{
+	constexpr int D = NST - 1;            /* stages in flight ahead of the one being added */
+	constexpr int SPB = 32 / RS;          /* stages per index block of 32 nonzeros        */
+	constexpr int NB = (SPB - 1 + D) / SPB + 2;   /* index blocks held in registers       */
+	int bi[NB];
+	double be[NB];
+	auto load_blk = [&](int q, int &i_, double &e_) {
+		const int n = min(q * 32 + lane, m - 1);
+		i_ = idx[n];
+		e_ = ev[n];
+	};
+#pragma unroll
+	for (int b = 0; b < NB; b++)
+		load_blk(b, bi[b], be[b]);
+	const int half = lane >> 4, piece = lane & 15;
+	const bool piece_ok = 2 * piece < gw;
+	auto issue = [&](int slot, int blk_i, int lane0) {
+		/* rows lane0 .. lane0+RS-1 of the index block whose indices are in blk_i */
+#pragma unroll
+		for (int u = 0; u < RS / 2; u++) {
+			const int i = __shfl_sync(FULL, blk_i, lane0 + 2 * u + half);
+			if (piece_ok)
+				cp_async16(ring + (size_t)(slot * RS + 2 * u + half) * 32 + 2 * piece,
+				           src_g + (size_t)i * ld + 2 * piece);
+		}
+	};
+	/* prologue: stages 0 .. D-1 */
+#pragma unroll
+	for (int t = 0; t < D; t++) {
+		if (t * RS < m)
+			issue(t % NST, bi[t / SPB], (t % SPB) * RS);
+		cp_async_commit();
+	}
+	int slot = 0;                          /* ring slot of the stage being added */
+	for (int q = 0; q * 32 < m; q++) {
+#pragma unroll
+		for (int j = 0; j < SPB; j++) {
+			const int s = q * SPB + j;
+			if ((s + D) * RS < m)
+				issue(slot == 0 ? NST - 1 : slot - 1, bi[(j + D) / SPB], ((j + D) % SPB) * RS);
+			cp_async_commit();
+			cp_async_wait<D>();            /* stage s has landed */
+			__syncwarp();
+			const int rows = m - s * RS;
+			const double *x = ring + (size_t)slot * RS * 32 + lane;
+			if (rows >= RS) {
+#pragma unroll
+				for (int r = 0; r < RS; r++)
+					acc = __dadd_rn(acc, __dmul_rn(__shfl_sync(FULL, be[0], j * RS + r), x[r * 32]));
+			} else if (rows > 0) {
+#pragma unroll
+				for (int r = 0; r < RS; r++) {
+					const double e = __shfl_sync(FULL, be[0], j * RS + r);
+					if (r < rows)
+						acc = __dadd_rn(acc, __dmul_rn(e, x[r * 32]));
+				}
+			}
+			__syncwarp();                  /* the slot is refilled by the next issue */
+			slot = (slot + 1 == NST) ? 0 : slot + 1;
+		}
+#pragma unroll
+		for (int b = 0; b + 1 < NB; b++) {
+			bi[b] = bi[b + 1];
+			be[b] = be[b + 1];
+		}
+		load_blk(q + NB, bi[NB - 1], be[NB - 1]);
+	}
+	cp_async_wait<0>();
+	return acc;
+}
+
+/* e_n = alpha2 * (a_n - L_i . R_j) for the chunk's nonzero of this lane (lane < cnt): one
+ * lane per nonzero walks k sequentially (mat2d.c:133-137) while the R rows stream through the
+ * two tiles T0/T1, the next tile in flight while the current one is added.  Ls must be the
+ * warp's copy of L_i; copies issued by the caller before this call join the first group. */
+__device__ __forceinline__ double chunk_error(double *T0, double *T1, const double *Ls,
+                                              const double *__restrict__ Rold, int j, double a, int cnt,
+                                              int F, int ld, double alpha2, int lane)
+{
+	const int ntiles = (F + KT - 1) / KT;
+	StagePlan sp;
+	stage_plan(sp, Rold, j, cnt, ld, lane);
+	stage_tile(T0, sp, 0, ld);
+	cp_async_commit();
+	double s = 0.0;
+	for (int t = 0; t < ntiles; t++) {
+		double *cur = (t & 1) ? T1 : T0;
+		if (t + 1 < ntiles)
+			stage_tile((t & 1) ? T0 : T1, sp, (t + 1) * KT, ld);
+		cp_async_commit();
+		cp_async_wait<1>();           /* everything but the tile just issued has landed */
+		__syncwarp();
+		if (lane < cnt)
+			s = dot_tile(s, Ls + t * KT, cur + lane * TS, min(KT, F - t * KT));
+		__syncwarp();                 /* tile `cur` may be overwritten by the next issue */
+	}
+	return __dmul_rn(alpha2, __dsub_rn(a, s));
+}
+
 /*
- * By-user pass.  Dynamic shared memory per warp: two dot-phase tiles [CH][TS], the user's
- * L row [ld], es[32].  LONG = true: block b takes stored row b (< n_long) with the whole
- * CTA; LONG = false: every warp takes one of the remaining rows.  The dot of a nonzero streams its R row through the two tiles in
- * pieces of KT features (next tile in flight while the current one is added); the
- * accumulation of L_new then re-reads the R rows coalesced from L2.
+ * By-user pass of the short rows [n_long, n_rows): one warp per row does everything.
+ * Dynamic shared memory per warp: two dot-phase tiles [CH][TS], the user's L row [ld], es[32].
  */
-template <int WARPS, bool LONG>
+template <int WARPS>
 __global__ void __launch_bounds__(WARPS * 32)
 k_update_L(const LoopArgs p, const double *__restrict__ Lold, double *__restrict__ Lnew,
            const double *__restrict__ Rold)
@@ -325,24 +400,18 @@ k_update_L(const LoopArgs p, const double *__restrict__ Lold, double *__restrict
 	double *Ls = T1 + (size_t)CH * TS;
 	double *es = Ls + ld;
 
-	constexpr bool is_long = LONG;    /* two kernels: the register-hungry pipeline of the long rows
-	                                     must not cap the occupancy of the short-row launch */
-	const int r = is_long ? (int)blockIdx.x : p.n_long + (int)blockIdx.x * WARPS + warp;
+	const int r = p.n_long + (int)blockIdx.x * WARPS + warp;
 	if (r >= p.n_rows)
-		return;                       /* whole warp leaves; short-path blocks never use a block barrier */
+		return;
 	const int i = p.row_id[r] - p.user_lo;
 	const int base = p.row_ptr[r];
 	const int m = p.row_ptr[r + 1] - base;
 	const double *Lrow = Lold + (size_t)i * ld;
 	double *Lout = Lnew + (size_t)i * ld;
-	const int ntiles = (F + KT - 1) / KT;
 
-	const int c_first = is_long ? warp * CH : 0;
-	const int c_step = is_long ? WARPS * CH : CH;
-	if (c_first < m)                  /* joins the first tile's copy group */
-		for (int q = lane; q < (ld >> 1); q += 32)
-			cp_async16(Ls + 2 * q, Lrow + 2 * q);
-	for (int c0 = c_first; c0 < m; c0 += c_step) {
+	for (int q = lane; q < (ld >> 1); q += 32)      /* joins the first tile's copy group */
+		cp_async16(Ls + 2 * q, Lrow + 2 * q);
+	for (int c0 = 0; c0 < m; c0 += CH) {
 		const int cnt = min(CH, m - c0);
 		const int pos = base + c0 + lane;
 		int j = 0;
@@ -352,100 +421,125 @@ k_update_L(const LoopArgs p, const double *__restrict__ Lold, double *__restrict
 			a = p.val[pos];
 		}
 		j = __shfl_sync(FULL, j, min(lane, cnt - 1));   /* idle lanes mirror a valid item */
-
-		/* e_n = alpha2 * (a - dot): one lane per nonzero, k sequential, tiles double buffered */
-		StagePlan sp;
-		stage_plan(sp, Rold, j, cnt, ld, lane);
-		stage_tile(T0, sp, 0, ld);
-		cp_async_commit();
-		double s = 0.0;
-		for (int t = 0; t < ntiles; t++) {
-			double *cur = (t & 1) ? T1 : T0;
-			if (t + 1 < ntiles)
-				stage_tile((t & 1) ? T0 : T1, sp, (t + 1) * KT, ld);
-			cp_async_commit();
-			cp_async_wait<1>();       /* everything but the tile just issued has landed */
-			__syncwarp();
-			if (lane < cnt)
-				s = dot_tile(s, Ls + t * KT, cur + lane * TS, min(KT, F - t * KT));
-			__syncwarp();             /* tile `cur` may be overwritten by the next issue */
-		}
+		const double e = chunk_error(T0, T1, Ls, Rold, j, a, cnt, F, ld, p.alpha2, lane);
 		if (lane < cnt) {
-			const double e = __dmul_rn(p.alpha2, __dsub_rn(a, s));
 			p.e_csc[p.epos[pos]] = e;
-			if (is_long)
-				p.e_csr[pos] = e;
-			else
-				es[lane] = e;
+			es[lane] = e;
 		}
 		__syncwarp();
-		if (!is_long) {
-			/* L_new[i][k] chain over this chunk's nonzeros; the feature groups of a lane
-			 * are independent chains and run interleaved */
-			for (int kb = 0; kb < F; kb += 256) {
-				const double *init = (c0 == 0) ? Ls : Lout;
-				switch (min(8, (F - kb + 31) >> 5)) {
-				case 1: row_update<1>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
-				case 2: row_update<2>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
-				case 3: row_update<3>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
-				case 4: row_update<4>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
-				case 5: row_update<5>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
-				case 6: row_update<6>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
-				case 7: row_update<7>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
-				default: row_update<8>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
-				}
+		/* L_new[i][k] chain over this chunk's nonzeros; the feature groups of a lane are
+		 * independent chains and run interleaved */
+		for (int kb = 0; kb < F; kb += 256) {
+			const double *init = (c0 == 0) ? Ls : Lout;
+			switch (min(8, (F - kb + 31) >> 5)) {
+			case 1: row_update<1>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
+			case 2: row_update<2>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
+			case 3: row_update<3>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
+			case 4: row_update<4>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
+			case 5: row_update<5>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
+			case 6: row_update<6>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
+			case 7: row_update<7>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
+			default: row_update<8>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
 			}
-			__syncwarp();             /* es is rewritten by the next chunk */
 		}
-	}
-	if (!is_long)
-		return;
-
-	/* whole-CTA row: every e_n is in e_csr (written above by this CTA); each warp now owns
-	 * 32 features and walks the row's nonzeros in order with the register pipeline */
-	__syncthreads();
-	for (int kb = warp * 32; kb < F; kb += WARPS * 32) {
-		const int k = kb + lane;
-		const bool active = k < F;
-		double acc = active ? Lrow[k] : 0.0;
-		acc = chain_regs(acc, lane, p.col_idx + base, p.e_csr + base, m, Rold + (active ? k : 0), ld);
-		if (active)
-			Lout[k] = acc;
+		__syncwarp();                 /* es is rewritten by the next chunk */
 	}
 }
 
 /*
- * By-item pass over the stored columns [c_begin, c_end).  One warp per (column, group of
- * 32 features), lane = feature.  B = rows per register block of the pipeline (32 for the
- * launch of the few longest columns, 8 for the bulk).
- * single-GPU: Rout = R_new, starts from R_old[j][k]        (matFact.c:50-51)
- * N shards:   Rout = G (rows by item_slot), starts from 0  (matFact-mpi.c:187-205)
+ * Dots of the long rows [0, n_long): one warp per chunk of <= CH nonzeros of one row, so a
+ * row of thousands of nonzeros spreads over as many warps as it has chunks.  Writes e_n at
+ * its by-user and by-item positions; k_chain does the accumulations.
+ * Dynamic shared memory per warp: as k_update_L.
  */
-template <int WARPS, int B>
+template <int WARPS>
 __global__ void __launch_bounds__(WARPS * 32)
-k_update_R(const LoopArgs p, int c_begin, int c_end, const double *__restrict__ Lold,
-           const double *__restrict__ Rold, double *__restrict__ Rout)
+k_dot(const LoopArgs p, const double *__restrict__ Lold, const double *__restrict__ Rold)
 {
-	const int lane = threadIdx.x & 31;
-	const int NG = (p.F + 31) >> 5;
-	const long gw = (long)blockIdx.x * WARPS + (threadIdx.x >> 5);
-	const int c = c_begin + (int)(gw / NG), g = (int)(gw % NG);
-	if (c >= c_end)
+	extern __shared__ __align__(16) double smem[];
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	const int F = p.F, ld = p.ld, CH = p.CH;
+	const size_t per_warp = (size_t)2 * CH * TS + ld + 32;
+	double *T0 = smem + per_warp * warp;
+	double *T1 = T0 + (size_t)CH * TS;
+	double *Ls = T1 + (size_t)CH * TS;
+
+	const int c = (int)blockIdx.x * WARPS + warp;
+	if (c >= p.n_chunks)
+		return;
+	const int r = p.chunk_row[c];
+	const int first = p.chunk_pos[c];
+	const int cnt = min(CH, p.row_ptr[r + 1] - first);
+	const double *Lrow = Lold + (size_t)(p.row_id[r] - p.user_lo) * ld;
+	for (int q = lane; q < (ld >> 1); q += 32)
+		cp_async16(Ls + 2 * q, Lrow + 2 * q);
+	const int pos = first + lane;
+	int j = 0;
+	double a = 0.0;
+	if (lane < cnt) {
+		j = p.col_idx[pos];
+		a = p.val[pos];
+	}
+	j = __shfl_sync(FULL, j, min(lane, cnt - 1));
+	const double e = chunk_error(T0, T1, Ls, Rold, j, a, cnt, F, ld, p.alpha2, lane);
+	if (lane < cnt) {
+		p.e_csr[pos] = e;
+		p.e_csc[p.epos[pos]] = e;
+	}
+}
+
+/*
+ * Sequential accumulations: one warp per (stored row or column r, group of 32 features),
+ * lane = feature; side A takes the first warps_a warps of the launch, side B the rest.
+ *   L side (matFact.c:48-49): out = L_new, init = L_old, src = R_old, idx = items of the row
+ *   R side (matFact.c:50-51): out = R_new (or G from 0.0 for N shards, matFact-mpi.c:187-205),
+ *                             init = R_old, src = L_old, idx = users of the column
+ */
+constexpr int CHAIN_BULK_REGS = 0, CHAIN_DEEP_REGS = 1, CHAIN_BULK_RING = 2, CHAIN_DEEP_RING = 3;
+constexpr int RING_BULK_ROWS = 8, RING_BULK_STAGES = 3;     /* 6 KB per warp  */
+constexpr int RING_DEEP_ROWS = 16, RING_DEEP_STAGES = 6;    /* 24 KB per warp */
+
+template <int WARPS, int MODE>
+__global__ void __launch_bounds__(WARPS * 32)
+k_chain(const ChainSide A, const ChainSide B, long warps_a, int F, int ld)
+{
+	extern __shared__ __align__(16) double smem[];
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	const int NG = (F + 31) >> 5;
+	long w = (long)blockIdx.x * WARPS + warp;
+	const bool is_a = w < warps_a;
+	const ChainSide &sd = is_a ? A : B;
+	if (!is_a)
+		w -= warps_a;
+	const int r = sd.begin + (int)(w / NG), g = (int)(w % NG);
+	if (r >= sd.end)
 		return;
 	const int k = g * 32 + lane;
-	const bool active = k < p.F;
-	const int ld = p.ld;
-	const int j = p.col_id[c];
-	const int b = p.col_ptr[c], m = p.col_ptr[c + 1] - b;
-	const double *Lk = Lold + (active ? k : 0) - (size_t)p.user_lo * ld;
-	double acc = (p.item_slot || !active) ? 0.0 : Rold[(size_t)j * ld + k];
-	if (B == 32)
-		acc = chain_regs(acc, lane, p.row_idx + b, p.e_csc + b, m, Lk, ld);
-	else
-		acc = chain_regs_small<(B == 32 ? 8 : B)>(acc, lane, p.row_idx + b, p.e_csc + b, m, Lk, ld);
+	const bool active = k < F;
+	const int own = sd.id[r];
+	const int b = sd.ptr[r], m = sd.ptr[r + 1] - b;
+	double acc = (sd.init && active) ? sd.init[(size_t)(own - sd.own_off) * ld + k] : 0.0;
+	if (MODE == CHAIN_BULK_RING || MODE == CHAIN_DEEP_RING) {
+		const double *src_g = sd.src + g * 32 - (size_t)sd.src_off * ld;
+		const int gw = min(32, ld - g * 32);
+		if (MODE == CHAIN_DEEP_RING)
+			acc = chain_ring<RING_DEEP_ROWS, RING_DEEP_STAGES>(
+			    acc, lane, sd.idx + b, sd.e + b, m, src_g, ld, gw,
+			    smem + (size_t)warp * RING_DEEP_ROWS * RING_DEEP_STAGES * 32);
+		else
+			acc = chain_ring<RING_BULK_ROWS, RING_BULK_STAGES>(
+			    acc, lane, sd.idx + b, sd.e + b, m, src_g, ld, gw,
+			    smem + (size_t)warp * RING_BULK_ROWS * RING_BULK_STAGES * 32);
+	} else {
+		const double *srck = sd.src + (active ? k : 0) - (size_t)sd.src_off * ld;   /* idle lanes: a valid column */
+		if (MODE == CHAIN_DEEP_REGS)
+			acc = chain_deep(acc, lane, sd.idx + b, sd.e + b, m, srck, ld);
+		else
+			acc = chain_bulk<8>(acc, lane, sd.idx + b, sd.e + b, m, srck, ld);
+	}
 	if (active) {
-		const size_t orow = p.item_slot ? (size_t)p.item_slot[j] : (size_t)j;
-		Rout[orow * ld + k] = acc;
+		const size_t orow = sd.out_slot ? (size_t)sd.out_slot[own] : (size_t)(own - sd.own_off);
+		sd.out[orow * ld + k] = acc;
 	}
 }
 

@@ -18,6 +18,7 @@
 
 #include <algorithm>
 #include <new>
+#include <vector>
 
 template <typename T>
 static int upload(T **dst, const T *src, size_t n, cudaStream_t st)
@@ -48,36 +49,51 @@ int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
 	s->warps = warps;
 	s->k1_smem = warps * warp_doubles(CH) * sizeof(double);
 	TRY(mf_kernels_prepare(warps, s->k1_smem));
-
-	/* a warp spends ~100 cycles per nonzero, so a row much longer than the per-warp share of
-	 * the shard (nnz / (8 warps x SMs)) would outlast the rest of the launch on the warp path */
+	/* Row classes.  A warp of k_update_L spends ~100 cycles per nonzero, so a row much longer
+	 * than the per-warp share of the shard (nnz / (8 warps x SMs)) would outlast the rest of
+	 * the launch: such rows have their dots spread over warps by k_dot.  Chains longer than
+	 * ~nnz / (4 x SMs) get the deep register pipeline of k_chain, the rest the light one. */
 	int n_sm = 148;
 	CK(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, s->dev));
-	const int share = (int)std::min<long>(1 << 30, (long)s->pat.nnz / (2L * 8 * std::max(1, n_sm)));
-	const int thresh = pl->opt_long_row > 0 ? pl->opt_long_row : std::max(2 * CH, share);
-	int n_long = 0;
+	n_sm = std::max(1, n_sm);
+	const mf_pattern &pt = s->pat;
+	const int share = (int)std::min<long>(1 << 30, (long)pt.nnz / (16L * n_sm));
+	const int long_thresh = pl->opt_long_row > 0 ? pl->opt_long_row : std::max(2 * CH, share);
+	const int deep_thresh = pl->opt_long_col > 0 ? pl->opt_long_col
+	                                             : std::max(64, (int)std::min<long>(1 << 30, (long)pt.nnz / (4L * n_sm)));
+	int n_long = 0, n_deep_rows = 0, n_deep_cols = 0;
 	if (warps > 1)
-		while (n_long < s->pat.n_rows &&
-		       s->pat.row_ptr[n_long + 1] - s->pat.row_ptr[n_long] > thresh)
+		while (n_long < pt.n_rows && pt.row_ptr[n_long + 1] - pt.row_ptr[n_long] > long_thresh)
 			n_long++;
+	while (n_deep_rows < n_long && pt.row_ptr[n_deep_rows + 1] - pt.row_ptr[n_deep_rows] > deep_thresh)
+		n_deep_rows++;
+	while (n_deep_cols < pt.n_cols && pt.col_ptr[n_deep_cols + 1] - pt.col_ptr[n_deep_cols] > deep_thresh)
+		n_deep_cols++;
 
-	/* columns whose sequential chain alone would outlast the launch get the deep pipeline */
-	const int col_thresh = pl->opt_long_col > 0 ? pl->opt_long_col
-	                                            : std::max(64, (int)std::min<long>(1 << 30, (long)s->pat.nnz / (4L * std::max(1, n_sm))));
-	int n_long_cols = 0;
-	while (n_long_cols < s->pat.n_cols &&
-	       s->pat.col_ptr[n_long_cols + 1] - s->pat.col_ptr[n_long_cols] > col_thresh)
-		n_long_cols++;
+	/* chunks of the long rows for k_dot */
+	std::vector<int> chunk_row, chunk_pos;
+	for (int r = 0; r < n_long; r++)
+		for (int pos = pt.row_ptr[r]; pos < pt.row_ptr[r + 1]; pos += CH) {
+			chunk_row.push_back(r);
+			chunk_pos.push_back(pos);
+		}
+	cudaFree(s->d_chunk_row);
+	cudaFree(s->d_chunk_pos);
+	s->d_chunk_row = s->d_chunk_pos = nullptr;
+	TRY(upload(&s->d_chunk_row, chunk_row.data(), chunk_row.size(), s->st));
+	TRY(upload(&s->d_chunk_pos, chunk_pos.data(), chunk_pos.size(), s->st));
+	CK(cudaStreamSynchronize(s->st));     /* the vectors die with this scope */
 
 	mf::LoopArgs &a = s->la;
 	a.F = F;
 	a.ld = pl->ld;
-	a.S = TS;
 	a.CH = CH;
-	a.n_rows = s->pat.n_rows;
+	a.n_rows = pt.n_rows;
 	a.n_long = n_long;
-	a.n_cols = s->pat.n_cols;
-	a.n_long_cols = n_long_cols;
+	a.n_deep_rows = n_deep_rows;
+	a.n_cols = pt.n_cols;
+	a.n_deep_cols = n_deep_cols;
+	a.n_chunks = (int)chunk_row.size();
 	a.user_lo = s->user_lo;
 	a.alpha2 = pl->alpha * 2;     /* matFact.c:45: alpha * 2 * (...) associates left, exact */
 	a.row_id = s->d_row_id;
@@ -88,13 +104,31 @@ int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
 	a.col_id = s->d_col_id;
 	a.col_ptr = s->d_col_ptr;
 	a.row_idx = s->d_row_idx;
+	a.chunk_row = s->d_chunk_row;
+	a.chunk_pos = s->d_chunk_pos;
 	a.item_slot = pl->nshards > 1 ? s->d_item_slot : nullptr;
 	a.e_csc = s->d_e_csc;
 	a.e_csr = s->d_e_csr;
-	s->k1_blocks = (a.n_rows - n_long + warps - 1) / warps;      /* short-row launch; n_long CTAs more for the long rows */
-	const long ng = (F + 31) / 32;
-	s->k2_blocks = (int)(((long)(a.n_cols - n_long_cols) * ng + 7) / 8);
-	s->k2_long_blocks = (int)(((long)n_long_cols * ng + 7) / 8);
+	s->k1_blocks = (a.n_rows - n_long + warps - 1) / warps;
+	s->dot_blocks = (a.n_chunks + 7) / 8;
+
+	/* algorithmic (compulsory) bytes of one launch of each kernel, DESIGN.md section 4 */
+	{
+		const long long Fb = 8LL * F;
+		const long long nnz_long = n_long ? pt.row_ptr[n_long] : 0, nnz_short = pt.nnz - nnz_long;
+		const long long nnz_deep_r = n_deep_rows ? pt.row_ptr[n_deep_rows] : 0;
+		const long long nnz_deep_c = n_deep_cols ? pt.col_ptr[n_deep_cols] : 0;
+		auto touched = [&](long long nnz_part, long long other_total) { return std::min(nnz_part, other_total); };
+		s->kbytes[0] = 2 * Fb * (pt.n_rows - n_long) + Fb * touched(nnz_short, pt.n_cols) + 24 * nnz_short;
+		s->kbytes[1] = Fb * n_long + Fb * touched(nnz_long, pt.n_cols) + 32 * nnz_long;
+		s->kbytes[2] = 2 * Fb * (n_long - n_deep_rows) + Fb * touched(nnz_long - nnz_deep_r, pt.n_cols) +
+		               12 * (nnz_long - nnz_deep_r) +
+		               2 * Fb * (pt.n_cols - n_deep_cols) + Fb * touched(pt.nnz - nnz_deep_c, pt.n_rows) +
+		               12 * (pt.nnz - nnz_deep_c);
+		s->kbytes[3] = 2 * Fb * n_deep_rows + Fb * touched(nnz_deep_r, pt.n_cols) + 12 * nnz_deep_r +
+		               2 * Fb * n_deep_cols + Fb * touched(nnz_deep_c, pt.n_rows) + 12 * nnz_deep_c;
+		s->kbytes[4] = pl->nshards > 1 ? 3 * Fb * pl->n_touched : 0;
+	}
 	for (int g = 0; g < 2; g++)
 		if (s->gexec[g]) {
 			cudaGraphExecDestroy(s->gexec[g]);
@@ -112,6 +146,8 @@ static int shard_create(mfgpu_plan *pl, mf_shard *s, int dev, const mfgpu_entry 
 	CK(cudaStreamCreateWithFlags(&s->st2, cudaStreamNonBlocking));
 	CK(cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming));
 	CK(cudaEventCreateWithFlags(&s->ev_join, cudaEventDisableTiming));
+	CK(cudaEventCreateWithFlags(&s->ev_a, cudaEventDisableTiming));
+	CK(cudaEventCreateWithFlags(&s->ev_b, cudaEventDisableTiming));
 	CK(cudaEventCreate(&s->ev0));
 	CK(cudaEventCreate(&s->ev1));
 	CK(cudaEventCreate(&s->ev_t0));
@@ -185,7 +221,7 @@ static void shard_destroy(mf_shard *s)
 	void *ptrs[] = {s->d_row_id, s->d_row_ptr, s->d_col_idx, s->d_epos, s->d_col_id, s->d_col_ptr,
 	                s->d_row_idx, s->d_val, s->d_e_csc, s->d_e_csr, s->d_mask_ptr, s->d_mask_col,
 	                s->d_first_free, s->d_item_slot, s->d_touched_item, s->part_v, s->part_j,
-	                s->nan_first, s->d_best, s->L_keep, s->R_keep};
+	                s->nan_first, s->d_best, s->L_keep, s->R_keep, s->d_chunk_row, s->d_chunk_pos};
 	for (void *q : ptrs)
 		cudaFree(q);
 	if (s->ev0) cudaEventDestroy(s->ev0);
@@ -194,6 +230,8 @@ static void shard_destroy(mf_shard *s)
 	if (s->ev_t1) cudaEventDestroy(s->ev_t1);
 	if (s->ev_fork) cudaEventDestroy(s->ev_fork);
 	if (s->ev_join) cudaEventDestroy(s->ev_join);
+	if (s->ev_a) cudaEventDestroy(s->ev_a);
+	if (s->ev_b) cudaEventDestroy(s->ev_b);
 	if (s->st2) cudaStreamDestroy(s->st2);
 	if (s->st) cudaStreamDestroy(s->st);
 	mf_pattern_free(&s->pat);
@@ -236,6 +274,7 @@ static int plan_create(mfgpu_plan **out, int users, int items, int features, int
 	pl->comm = comm;
 	pl->opt_graph = 1;
 	pl->opt_graph_iters = 16;
+	pl->opt_chain_ring = 1;
 
 	int rc = mf_split_users(users, nnz, entries, nshards, pl->cut);
 	int *item_slot = nullptr, *touched = nullptr;
@@ -417,6 +456,15 @@ extern "C" long long mfgpu_plan_bytes_per_iter(mfgpu_plan *pl)
 	return b;
 }
 
+extern "C" int mfgpu_plan_kernel_bytes(mfgpu_plan *pl, long long bytes[5])
+{
+	if (!pl || !bytes)
+		return mf_fail(MFGPU_EINVAL, "null argument");
+	for (int k = 0; k < 5; k++)
+		bytes[k] = pl->sh[0].kbytes[k];
+	return MFGPU_OK;
+}
+
 extern "C" int mfgpu_plan_set_option(mfgpu_plan *pl, const char *name, int value)
 {
 	if (!pl || !name)
@@ -426,6 +474,7 @@ extern "C" int mfgpu_plan_set_option(mfgpu_plan *pl, const char *name, int value
 	else if (!strcmp(name, "long_row")) pl->opt_long_row = value;
 	else if (!strcmp(name, "chunk")) pl->opt_ch = value;
 	else if (!strcmp(name, "long_col")) pl->opt_long_col = value;
+	else if (!strcmp(name, "chain_ring")) pl->opt_chain_ring = value;
 	else
 		return mf_fail(MFGPU_EINVAL, "unknown option '%s'", name);
 	for (int g = 0; g < local_shards(pl); g++) {

@@ -7,23 +7,41 @@
 
 namespace mf {
 
+/* Rows (users with >= 1 nonzero) are stored longest first and fall in three classes:
+ *   [0, n_deep_rows)        dots by k_dot, accumulation by k_chain<deep>
+ *   [n_deep_rows, n_long)   dots by k_dot, accumulation by k_chain<bulk>
+ *   [n_long, n_rows)        everything by k_update_L (one warp per row)
+ * Columns (items with >= 1 nonzero), longest first: [0, n_deep_cols) k_chain<deep>, rest bulk. */
 struct LoopArgs {
 	int F;            /* features                                         */
 	int ld;           /* row stride of L and R in doubles (even, >= F)    */
-	int S;            /* row stride of the staged R rows in shared memory */
-	int CH;           /* nonzeros staged per chunk (<= 32)                */
-	int n_rows;       /* stored user rows (users with >= 1 nonzero)       */
-	int n_long;       /* the first n_long stored rows get a whole CTA     */
-	int n_cols;       /* stored item columns                              */
-	int n_long_cols;  /* the first n_long_cols get the deep (32-row) pipeline */
+	int CH;           /* nonzeros per chunk of the dot phase (<= 32)      */
+	int n_rows, n_long, n_deep_rows;
+	int n_cols, n_deep_cols;
+	int n_chunks;     /* chunks of the rows [0, n_long) for k_dot         */
 	int user_lo;      /* first user of this shard; L holds rows user_lo.. */
 	double alpha2;    /* alpha * 2, exact                                 */
 	const int *row_id, *row_ptr, *col_idx, *epos;
 	const double *val;
 	const int *col_id, *col_ptr, *row_idx;
-	const int *item_slot;   /* N-GPU: item -> row of G, else nullptr      */
+	const int *chunk_row, *chunk_pos;   /* stored row and first by-user position of a chunk */
+	const int *item_slot;   /* N shards: item -> row of G, else nullptr   */
 	double *e_csc;    /* e_n at by-item positions                         */
-	double *e_csr;    /* e_n at by-user positions (long rows only)        */
+	double *e_csr;    /* e_n at by-user positions (rows [0, n_long) only) */
+};
+
+/* One side of a k_chain launch: for every stored row/column r in [begin, end) and every
+ * group of 32 features,  out[own(r)][k] = init[own(r)][k] + sum_n e[n] * src[idx[n]][k]
+ * over n in [ptr[r], ptr[r+1]), added strictly in that order. */
+struct ChainSide {
+	int begin, end;
+	const int *ptr, *idx, *id;
+	const double *e;
+	const double *init;       /* own matrix (old values); nullptr: start from 0.0      */
+	const double *src;        /* the other factor (old values), gathered by idx         */
+	double *out;
+	int own_off, src_off;     /* first row held by init/out and by src                  */
+	const int *out_slot;      /* nullptr, or out row = out_slot[id[r]] (N shards: G)   */
 };
 
 constexpr int AM_TI = 64;      /* users per CTA           */
