@@ -25,6 +25,16 @@ __device__ __forceinline__ void cp_async16(void *dst, const void *src)
 	asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
 }
 
+/* the same with the destination as a shared-window address and a predicate (no branch) */
+__device__ __forceinline__ void cp_async16_if(uint32_t dst, const void *src, bool pred)
+{
+	asm volatile(
+	    "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %2, 0;\n\t"
+	    "@p cp.async.cg.shared.global [%0], [%1], 16;\n\t}"
+	    ::"r"(dst), "l"(src), "r"((int)pred)
+	    : "memory");
+}
+
 __device__ __forceinline__ void cp_async_commit()
 {
 	asm volatile("cp.async.commit_group;" ::: "memory");

@@ -49,6 +49,8 @@ struct mf_shard {
 	mf::LoopArgs la;
 	int warps;                               /* 8 or 1: k_update_L template      */
 	int k1_blocks, dot_blocks;
+	int res_ng;                              /* > 0: k_update_L_res<res_ng> does the short rows */
+	size_t res_smem;
 	long long kbytes[5];                     /* algorithmic bytes per launch of each kernel */
 	size_t k1_smem;
 	cudaGraphExec_t gexec[2];                /* by starting parity                */
@@ -72,7 +74,7 @@ struct mfgpu_plan {
 	long long launches;
 	float loop_ms, rec_ms;
 	/* options */
-	int opt_graph, opt_graph_iters, opt_long_row, opt_long_col, opt_ch, opt_chain_ring;
+	int opt_graph, opt_graph_iters, opt_long_row, opt_long_col, opt_ch, opt_chain_ring, opt_resident, opt_res_rows;
 };
 
 /* ---- shared helpers (defined in mf_capi.cu) ----------------------------------- */
@@ -80,7 +82,7 @@ int mf_fail(int code, const char *fmt, ...);
 int mf_load_nccl(void);
 int mf_usable_devices(int *ids, int cap);
 int mf_configure_shard(mfgpu_plan *pl, mf_shard *s);      /* mf_plan.cu */
-int mf_kernels_prepare(int warps, size_t k1_smem);   /* mf_iter.cu: kernels live in that TU only */
+int mf_kernels_prepare(int warps, size_t k1_smem, int res_ng, size_t res_smem);   /* mf_iter.cu: kernels live in that TU only */
 extern mf_nccl_api g_nccl;
 
 #define CK(call)                                                                        \

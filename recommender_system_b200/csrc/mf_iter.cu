@@ -51,9 +51,30 @@ k_apply_R_peer(int n_touched, int F, int ld, const int *__restrict__ touched_ite
 
 } // namespace mf
 
-int mf_kernels_prepare(int warps, size_t k1_smem)
+template <int NG>
+static int prepare_res(size_t smem)
+{
+	CK(cudaFuncSetAttribute(mf::k_update_L_res<NG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+	/* the resident rows decide how many warps an SM holds: take all the shared memory there is */
+	CK(cudaFuncSetAttribute(mf::k_update_L_res<NG>, cudaFuncAttributePreferredSharedMemoryCarveout,
+	                        (int)cudaSharedmemCarveoutMaxShared));
+	return MFGPU_OK;
+}
+
+int mf_kernels_prepare(int warps, size_t k1_smem, int res_ng, size_t res_smem)
 {
 	const auto attr = cudaFuncAttributeMaxDynamicSharedMemorySize;
+	switch (res_ng) {
+	case 1: TRY(prepare_res<1>(res_smem)); break;
+	case 2: TRY(prepare_res<2>(res_smem)); break;
+	case 3: TRY(prepare_res<3>(res_smem)); break;
+	case 4: TRY(prepare_res<4>(res_smem)); break;
+	case 5: TRY(prepare_res<5>(res_smem)); break;
+	case 6: TRY(prepare_res<6>(res_smem)); break;
+	case 7: TRY(prepare_res<7>(res_smem)); break;
+	case 8: TRY(prepare_res<8>(res_smem)); break;
+	default: break;
+	}
 	if (warps == 8) {
 		CK(cudaFuncSetAttribute(mf::k_update_L<8>, attr, (int)k1_smem));
 		CK(cudaFuncSetAttribute(mf::k_dot<8>, attr, (int)k1_smem));
@@ -102,10 +123,19 @@ static int launch_fused(mfgpu_plan *pl, mf_shard *s, int c, cudaStream_t st)
 {
 	if (s->k1_blocks <= 0)
 		return MFGPU_OK;
-	if (s->warps == 8)
+#define MF_RES(NG) \
+	case NG: mf::k_update_L_res<NG><<<s->k1_blocks, 32 * mf::RES_WARPS, s->res_smem, st>>>( \
+		s->la, s->L[c], s->L[1 - c], s->R[c]); break;
+	if (s->res_ng) {
+		switch (s->res_ng) {
+			MF_RES(1) MF_RES(2) MF_RES(3) MF_RES(4) MF_RES(5) MF_RES(6) MF_RES(7) MF_RES(8)
+		default: return mf_fail(MFGPU_EINVAL, "resident kernel: bad group count %d", s->res_ng);
+		}
+	} else if (s->warps == 8)
 		mf::k_update_L<8><<<s->k1_blocks, 256, s->k1_smem, st>>>(s->la, s->L[c], s->L[1 - c], s->R[c]);
 	else
 		mf::k_update_L<1><<<s->k1_blocks, 32, s->k1_smem, st>>>(s->la, s->L[c], s->L[1 - c], s->R[c]);
+#undef MF_RES
 	CK(cudaGetLastError());
 	pl->launches++;
 	return MFGPU_OK;

@@ -446,6 +446,280 @@ k_update_L(const LoopArgs p, const double *__restrict__ Lold, double *__restrict
 	}
 }
 
+/* wait until at most n of this thread's copy groups are pending (n is not a constant here) */
+__device__ __forceinline__ void cp_async_wait_dyn(int n)
+{
+	switch (n) {
+	case 0: cp_async_wait<0>(); break;
+	case 1: cp_async_wait<1>(); break;
+	case 2: cp_async_wait<2>(); break;
+	case 3: cp_async_wait<3>(); break;
+	case 4: cp_async_wait<4>(); break;
+	case 5: cp_async_wait<5>(); break;
+	case 6: cp_async_wait<6>(); break;
+	default: cp_async_wait<7>(); break;
+	}
+}
+
+/*
+ * By-user pass of the short rows with the gathered R rows resident in shared memory: each
+ * R row of a nonzero is read from L2 ONCE and serves both the dot (lane = nonzero, k
+ * sequential) and the accumulation of L_new (lane = feature, nonzeros in file order); the
+ * gathers are what bounds the loop (L2 -> SM bytes), so this halves the cost of the pass
+ * against the tiled k_update_L, which streams the rows for the dot and reads them again for
+ * the accumulation.  One warp per row, chunks of CR nonzeros; rows RST doubles apart with
+ * RST/2 odd, so that the 16-byte reads of the dot (8 lanes = 8 rows per wavefront) are
+ * conflict free.  The copies are issued as groups of 64 features (one 16-byte piece per
+ * lane and row) and the dot starts as soon as the first group has landed.  The L_new
+ * accumulators of the NG feature groups of a lane stay in registers over the whole row.
+ * Dynamic shared memory per warp: R rows [CR][RST], the user's L row [ld], es[32].
+ * Used for F <= 256 (NG <= 8).
+ */
+constexpr int RES_WARPS = 2;
+
+/* s += x[0]*y[0], + x[1]*y[1], ... in order over 8 features held as four double2 pairs */
+__device__ __forceinline__ double dot8(double s, const double2 (&x)[4], const double2 (&y)[4])
+{
+#pragma unroll
+	for (int u = 0; u < 4; u++) {
+		s = __dadd_rn(s, __dmul_rn(x[u].x, y[u].x));
+		s = __dadd_rn(s, __dmul_rn(x[u].y, y[u].y));
+	}
+	return s;
+}
+
+__device__ __forceinline__ void load8(double2 (&x)[4], double2 (&y)[4], const double *l, const double *r)
+{
+#pragma unroll
+	for (int u = 0; u < 4; u++) {
+		x[u] = ld2(l + 2 * u);
+		y[u] = ld2(r + 2 * u);
+	}
+}
+
+/* s continued over features [k0, k1) of l . r (k0 even, 16-byte aligned operands): blocks of
+ * 8 features alternate between two register sets, the next block being read from shared
+ * memory while the current one is added */
+__device__ __forceinline__ double dot_range(double s, const double *l, const double *r, int k0, int k1)
+{
+	const int nblk = (k1 - k0) >> 3;
+	if (nblk > 0) {
+		double2 xa[4], ya[4], xb[4], yb[4];
+		load8(xa, ya, l + k0, r + k0);
+		int b = 0;
+		for (; b + 2 < nblk; b += 2) {
+			load8(xb, yb, l + k0 + 8 * (b + 1), r + k0 + 8 * (b + 1));
+			s = dot8(s, xa, ya);
+			load8(xa, ya, l + k0 + 8 * (b + 2), r + k0 + 8 * (b + 2));
+			s = dot8(s, xb, yb);
+		}
+		if (b + 1 < nblk) {
+			load8(xb, yb, l + k0 + 8 * (b + 1), r + k0 + 8 * (b + 1));
+			s = dot8(s, xa, ya);
+			s = dot8(s, xb, yb);
+		} else {
+			s = dot8(s, xa, ya);
+		}
+	}
+	for (int k = k0 + 8 * nblk; k < k1; k++)
+		s = __dadd_rn(s, __dmul_rn(l[k], r[k]));
+	return s;
+}
+
+/* x[g] = row[g*32 + lane] for the NG feature groups of a lane (klast: the last group's index) */
+template <int NG>
+__device__ __forceinline__ void load_groups(double (&x)[NG], const double *row, int lane, int klast)
+{
+	const double *rl = row + lane;
+#pragma unroll
+	for (int g = 0; g < NG - 1; g++)
+		x[g] = rl[g * 32];
+	x[NG - 1] = row[klast];
+}
+
+/* Gather of the R rows of a chunk into shared memory (k_update_L_res): row n
+ * goes to rs_addr + n*rstb (rs_addr, sbase already include this lane's 16-byte piece); the
+ * 16-byte pieces of a lane in a row are features 64t + 2*lane, t < NT_MAX.  The first NT_A
+ * k-ranges form copy group A, the rest group B, so that the dot can start after A. */
+template <int NG>
+__device__ __forceinline__ void res_stage(uint32_t rs_addr, const char *sbase, unsigned ldb, unsigned rstb,
+                                          int j, int cnt, const bool (&piece_ok)[(NG + 1) / 2])
+{
+	constexpr int NT_MAX = (NG + 1) / 2, NT_A = (NT_MAX + 1) / 2;
+#pragma unroll
+	for (int half = 0; half < 2; half++) {
+		const int t0 = half ? NT_A : 0, t1 = half ? NT_MAX : NT_A;
+		uint32_t drow = rs_addr;
+		int n = 0;
+		for (; n + 4 <= cnt; n += 4) {       /* four rows per trip, no guards */
+			unsigned jn[4];
+#pragma unroll
+			for (int u = 0; u < 4; u++)
+				jn[u] = (unsigned)__shfl_sync(FULL, j, n + u);
+#pragma unroll
+			for (int u = 0; u < 4; u++) {
+				const char *srow = sbase + (unsigned long long)jn[u] * ldb;
+#pragma unroll
+				for (int t = 0; t < NT_MAX; t++)
+					if (t >= t0 && t < t1)
+						cp_async16_if(drow + u * rstb + 512 * t, srow + 512 * t, piece_ok[t]);
+			}
+			drow += 4 * rstb;
+		}
+		for (; n < cnt; n++) {
+			const unsigned j1 = (unsigned)__shfl_sync(FULL, j, n);
+			const char *srow = sbase + (unsigned long long)j1 * ldb;
+#pragma unroll
+			for (int t = 0; t < NT_MAX; t++)
+				if (t >= t0 && t < t1)
+					cp_async16_if(drow + 512 * t, srow + 512 * t, piece_ok[t]);
+			drow += rstb;
+		}
+		cp_async_commit();
+	}
+}
+
+template <int NG>
+__global__ void __launch_bounds__(RES_WARPS * 32)
+k_update_L_res(const LoopArgs p, const double *__restrict__ Lold, double *__restrict__ Lnew,
+               const double *__restrict__ Rold)
+{
+	extern __shared__ __align__(16) double smem[];
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	const int F = p.F, ld = p.ld, CR = p.CR, RST = p.RST;
+	const size_t per_warp = (size_t)CR * RST + ld + 32;
+	double *Rs = smem + per_warp * warp;
+	double *Ls = Rs + (size_t)CR * RST;
+	double *es = Ls + ld;
+
+	/* the 16-byte pieces of this lane in a row: features 64t + 2*lane, t < NT; the first
+	 * NT_A k-ranges form copy group A, the rest group B, and the dot starts after A */
+	constexpr int NT_MAX = (NG + 1) / 2, NT_A = (NT_MAX + 1) / 2;
+	const int kA = min(F, 64 * NT_A);              /* features covered by group A */
+	const char *sbase = (const char *)(Rold + 2 * lane);
+	const unsigned ldb = (unsigned)ld * 8u, rstb = (unsigned)RST * 8u;
+	const uint32_t rs_addr = smem_u32(Rs + 2 * lane);
+	bool piece_ok[NT_MAX];
+#pragma unroll
+	for (int t = 0; t < NT_MAX; t++)
+		piece_ok[t] = 64 * t + 2 * lane < ld;
+	/* only the last feature group can be partial; its idle lanes read a valid address */
+	const bool ok_last = (NG - 1) * 32 + lane < F;
+	const int klast = ok_last ? (NG - 1) * 32 + lane : 0;
+
+	/* rows r, r + stride, ...: the row's (user, first position, length) and the (item, value,
+	 * by-item position) of its first chunk are fetched one row ahead */
+	const int stride = (int)gridDim.x * RES_WARPS;
+	int r = p.n_long + (int)blockIdx.x * RES_WARPS + warp;
+	if (r >= p.n_rows)
+		return;
+	int i = p.row_id[r] - p.user_lo, base = p.row_ptr[r], m = p.row_ptr[r + 1] - base;
+	int j = 0, ep = 0;
+	double a = 0.0;
+	if (lane < min(CR, m)) {
+		j = p.col_idx[base + lane];
+		a = p.val[base + lane];
+		ep = p.epos[base + lane];
+	}
+	while (r < p.n_rows) {
+		const int rn = r + stride;
+		int i2 = 0, base2 = 0, m2 = 0;
+		if (rn < p.n_rows) {
+			i2 = p.row_id[rn] - p.user_lo;
+			base2 = p.row_ptr[rn];
+			m2 = p.row_ptr[rn + 1] - base2;
+		}
+		const double *Lrow = Lold + (size_t)i * ld;
+		double *Lout = Lnew + (size_t)i * ld;
+		double acc[NG];
+		for (int q = lane; q < (ld >> 1); q += 32)      /* joins the first copy group */
+			cp_async16(Ls + 2 * q, Lrow + 2 * q);
+		for (int c0 = 0; c0 < m; c0 += CR) {
+			const int cnt = min(CR, m - c0);
+			res_stage<NG>(rs_addr, sbase, ldb, rstb, j, cnt, piece_ok);
+			/* the next chunk's nonzeros (of this row, or the first of the next row) */
+			const double a_cur = a;
+			const int ep_cur = ep;
+			int jx = 0, epx = 0;
+			double ax = 0.0;
+			{
+				const bool same = c0 + CR < m;
+				const int posx = same ? base + c0 + CR + lane : base2 + lane;
+				const int cntx = same ? min(CR, m - c0 - CR) : min(CR, m2);
+				if (lane < cntx) {
+					jx = p.col_idx[posx];
+					ax = p.val[posx];
+					epx = p.epos[posx];
+				}
+			}
+			/* e_n (mat2d.c:133-137, matFact.c:45): idle lanes walk a valid row, unused */
+			/* (lanes without a nonzero stay out: their quarter-warp costs no shared-memory
+			 * wavefront, and that pipe is what this kernel runs against) */
+			const double *rrow = Rs + lane * RST;
+			cp_async_wait<1>();
+			__syncwarp();
+			double s = 0.0;
+			if (lane < cnt)
+				s = dot_range(s, Ls, rrow, 0, kA);
+			cp_async_wait<0>();
+			__syncwarp();
+			if (lane < cnt)
+				s = dot_range(s, Ls, rrow, kA, F);
+			const double e = __dmul_rn(p.alpha2, __dsub_rn(a_cur, s));
+			if (lane < cnt) {
+				p.e_csc[ep_cur] = e;
+				es[lane] = e;
+			}
+			__syncwarp();
+			if (c0 == 0) {
+#pragma unroll
+				for (int g = 0; g < NG; g++)
+					acc[g] = Ls[g < NG - 1 ? g * 32 + lane : klast];
+			}
+			/* matFact.c:48-49 in file order; the NG chains of a lane are independent; two
+			 * register sets alternate so that the operands of n+1 are read while n is added */
+			{
+				double x0[NG], x1[NG], e0 = es[0], e1;
+				load_groups<NG>(x0, Rs, lane, klast);
+				int n = 0;
+				for (; n + 1 < cnt; n += 2) {
+					e1 = es[n + 1];
+					load_groups<NG>(x1, Rs + (n + 1) * RST, lane, klast);
+#pragma unroll
+					for (int g = 0; g < NG; g++)
+						acc[g] = __dadd_rn(acc[g], __dmul_rn(e0, x0[g]));
+					const int n2 = min(n + 2, cnt - 1);
+					e0 = es[n2];
+					load_groups<NG>(x0, Rs + n2 * RST, lane, klast);
+#pragma unroll
+					for (int g = 0; g < NG; g++)
+						acc[g] = __dadd_rn(acc[g], __dmul_rn(e1, x1[g]));
+				}
+				if (n < cnt) {
+#pragma unroll
+					for (int g = 0; g < NG; g++)
+						acc[g] = __dadd_rn(acc[g], __dmul_rn(e0, x0[g]));
+				}
+			}
+			__syncwarp();                 /* Rs, Ls and es are rewritten by the next copies */
+			j = jx;
+			a = ax;
+			ep = epx;
+		}
+		if (m > 0) {
+#pragma unroll
+			for (int g = 0; g < NG - 1; g++)
+				Lout[g * 32 + lane] = acc[g];
+			if (ok_last)
+				Lout[klast] = acc[NG - 1];
+		}
+		r = rn;
+		i = i2;
+		base = base2;
+		m = m2;
+	}
+}
+
 /*
  * Dots of the long rows [0, n_long): one warp per chunk of <= CH nonzeros of one row, so a
  * row of thousands of nonzeros spreads over as many warps as it has chunks.  Writes e_n at

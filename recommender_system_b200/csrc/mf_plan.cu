@@ -48,7 +48,6 @@ int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
 		return mf_fail(MFGPU_EINVAL, "features=%d does not fit shared memory (%d bytes)", F, max_smem);
 	s->warps = warps;
 	s->k1_smem = warps * warp_doubles(CH) * sizeof(double);
-	TRY(mf_kernels_prepare(warps, s->k1_smem));
 	/* Row classes.  A warp of k_update_L spends ~100 cycles per nonzero, so a row much longer
 	 * than the per-warp share of the shard (nnz / (8 warps x SMs)) would outlast the rest of
 	 * the launch: such rows have their dots spread over warps by k_dot.  Chains longer than
@@ -70,6 +69,29 @@ int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
 	while (n_deep_cols < pt.n_cols && pt.col_ptr[n_deep_cols + 1] - pt.col_ptr[n_deep_cols] > deep_thresh)
 		n_deep_cols++;
 
+	/* Short rows with their gathered R rows resident in shared memory (k_update_L_res): rows
+	 * RST doubles apart (RST/2 odd), CR rows per chunk = the longest short row (at most 32).
+	 * It reads every R row once instead of twice, but a warp then owns CR x RST x 8 bytes of
+	 * shared memory: measured on B200 it wins while eight or more warps fit an SM (F = 100:
+	 * 107 us against 140 us on the MovieLens-1M shape) and loses to the tiled kernel when
+	 * fewer do (F = 200: 311 us against 276 us on inst60000).  resident=2 forces it. */
+	int CR = 0, RST = pl->ld + (((pl->ld / 2) & 1) ? 0 : 2);
+	s->res_ng = 0;
+	s->res_smem = 0;
+	if (warps > 1 && pl->opt_resident && F <= 256 && n_long < pt.n_rows) {
+		const int longest = pt.row_ptr[n_long + 1] - pt.row_ptr[n_long];
+		CR = std::min(32, longest);
+		if (pl->opt_res_rows > 0)
+			CR = std::min(32, pl->opt_res_rows);
+		const size_t per_warp = ((size_t)CR * RST + pl->ld + 32) * sizeof(double);
+		const bool eight_fit = 8 * per_warp <= (size_t)max_smem;
+		if ((eight_fit || pl->opt_resident > 1) && 2 * per_warp <= (size_t)max_smem) {
+			s->res_ng = (F + 31) / 32;
+			s->res_smem = 2 * per_warp;          /* mf::RES_WARPS warps per CTA */
+		}
+	}
+	TRY(mf_kernels_prepare(warps, s->k1_smem, s->res_ng, s->res_smem));
+
 	/* chunks of the long rows for k_dot */
 	std::vector<int> chunk_row, chunk_pos;
 	for (int r = 0; r < n_long; r++)
@@ -88,6 +110,8 @@ int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
 	a.F = F;
 	a.ld = pl->ld;
 	a.CH = CH;
+	a.CR = CR;
+	a.RST = RST;
 	a.n_rows = pt.n_rows;
 	a.n_long = n_long;
 	a.n_deep_rows = n_deep_rows;
@@ -110,6 +134,13 @@ int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
 	a.e_csc = s->d_e_csc;
 	a.e_csr = s->d_e_csr;
 	s->k1_blocks = (a.n_rows - n_long + warps - 1) / warps;
+	if (s->res_ng) {
+		/* persistent warps: as many CTAs as are resident at once, rows dealt round robin */
+		int smem_sm = 228 * 1024;
+		CK(cudaDeviceGetAttribute(&smem_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, s->dev));
+		const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(32, smem_sm / (s->res_smem + 1024)));
+		s->k1_blocks = std::min((a.n_rows - n_long + 1) / 2, n_sm * per_sm);
+	}
 	s->dot_blocks = (a.n_chunks + 7) / 8;
 
 	/* algorithmic (compulsory) bytes of one launch of each kernel, DESIGN.md section 4 */
@@ -275,6 +306,8 @@ static int plan_create(mfgpu_plan **out, int users, int items, int features, int
 	pl->opt_graph = 1;
 	pl->opt_graph_iters = 16;
 	pl->opt_chain_ring = 1;
+	pl->opt_resident = 1;
+	pl->opt_res_rows = 0;
 
 	int rc = mf_split_users(users, nnz, entries, nshards, pl->cut);
 	int *item_slot = nullptr, *touched = nullptr;
@@ -475,6 +508,8 @@ extern "C" int mfgpu_plan_set_option(mfgpu_plan *pl, const char *name, int value
 	else if (!strcmp(name, "chunk")) pl->opt_ch = value;
 	else if (!strcmp(name, "long_col")) pl->opt_long_col = value;
 	else if (!strcmp(name, "chain_ring")) pl->opt_chain_ring = value;
+	else if (!strcmp(name, "resident")) pl->opt_resident = value;
+	else if (!strcmp(name, "res_rows")) pl->opt_res_rows = value;
 	else
 		return mf_fail(MFGPU_EINVAL, "unknown option '%s'", name);
 	for (int g = 0; g < local_shards(pl); g++) {

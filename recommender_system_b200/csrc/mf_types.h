@@ -16,6 +16,7 @@ struct LoopArgs {
 	int F;            /* features                                         */
 	int ld;           /* row stride of L and R in doubles (even, >= F)    */
 	int CH;           /* nonzeros per chunk of the dot phase (<= 32)      */
+	int CR, RST;      /* k_update_L_res: resident rows per chunk, their stride in doubles */
 	int n_rows, n_long, n_deep_rows;
 	int n_cols, n_deep_cols;
 	int n_chunks;     /* chunks of the rows [0, n_long) for k_dot         */
