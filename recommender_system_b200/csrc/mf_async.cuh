@@ -46,4 +46,40 @@ __device__ __forceinline__ void cp_async_wait()
 	asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
+/* ---- mbarriers in shared memory (CTA scope): producer / consumer hand-over of ring stages ---- */
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, int count)
+{
+	asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+
+/* release: everything this thread read or wrote before is ordered before the arrival */
+__device__ __forceinline__ void mbar_arrive(uint32_t bar)
+{
+	asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity)
+{
+	uint32_t ok;
+	asm volatile(
+	    "{\n\t.reg .pred p;\n\t"
+	    "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+	    "selp.u32 %0, 1, 0, p;\n\t}"
+	    : "=r"(ok)
+	    : "r"(bar), "r"(parity)
+	    : "memory");
+	return ok != 0;
+}
+
+/* wait for the phase with the given parity to complete; a wait that cannot end (a protocol
+ * error) traps after ~10^8 polls instead of hanging the device */
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
+{
+	unsigned spins = 0;
+	while (!mbar_try_wait(bar, parity))
+		if (++spins > (1u << 27))
+			__trap();
+}
+
 } // namespace mf

@@ -74,7 +74,7 @@ struct mfgpu_plan {
 	long long launches;
 	float loop_ms, rec_ms;
 	/* options */
-	int opt_graph, opt_graph_iters, opt_long_row, opt_long_col, opt_ch, opt_chain_ring, opt_resident, opt_res_rows;
+	int opt_graph, opt_graph_iters, opt_long_row, opt_long_col, opt_ch, opt_chain_ring, opt_resident, opt_res_rows, opt_chain_ws;
 };
 
 /* ---- shared helpers (defined in mf_capi.cu) ----------------------------------- */

@@ -165,7 +165,9 @@ static int launch_chain(mfgpu_plan *pl, mf_shard *s, int c, double *rout, bool d
 	const size_t ring_deep = (size_t)8 * mf::RING_DEEP_ROWS * mf::RING_DEEP_STAGES * 32 * sizeof(double);
 	const size_t ring_bulk = (size_t)8 * mf::RING_BULK_ROWS * mf::RING_BULK_STAGES * 32 * sizeof(double);
 	const bool ring = pl->opt_chain_ring != 0;
-	if (deep && ring)
+	if (deep && pl->opt_chain_ws)
+		mf::k_chain_ws<<<(unsigned)(wa + wb), mf::WS_THREADS, mf::WS_SMEM, st>>>(A, B, wa, a.F, a.ld);
+	else if (deep && ring)
 		mf::k_chain<8, mf::CHAIN_DEEP_RING><<<(unsigned)blocks, 256, ring_deep, st>>>(A, B, wa, a.F, a.ld);
 	else if (deep)
 		mf::k_chain<8, mf::CHAIN_DEEP_REGS><<<(unsigned)blocks, 256, 0, st>>>(A, B, wa, a.F, a.ld);

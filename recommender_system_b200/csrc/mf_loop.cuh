@@ -817,6 +817,141 @@ k_chain(const ChainSide A, const ChainSide B, long warps_a, int F, int ld)
 	}
 }
 
+/*
+ * k_chain_ws: the same sequential accumulation for the longest chains, one CTA per (row or
+ * column, group of 32 features) with the work split over specialised warps.  What bounds a
+ * long chain is the latency of one warp: ~13 instructions per nonzero in k_chain, although
+ * only the addition has to be serial (8 cycles, profiles/r01_ubench_fp64.txt).  Here
+ *   warps 1..WS_PRODUCERS  take stages of WS_ROWS nonzeros round robin: gather x[n] = src[idx[n]]
+ *       (one coalesced 256-byte read per nonzero, two stages in flight per warp), form
+ *       the products e[n]*x[n] -- they do not depend on the chain -- and store them in a
+ *       ring of WS_STAGES stages in shared memory;
+ *   warp 0  reads the products of a stage into registers, hands the stage back, and adds
+ *       them to the accumulator in file order while the next stage is being read:
+ *       one LDS and one DADD per nonzero.
+ * Stages are handed over through mbarriers (full[slot]: one producer arrival; empty[slot]:
+ * one consumer arrival).
+ */
+constexpr int WS_PRODUCERS = 4, WS_ROWS = 16, WS_STAGES = 8;
+constexpr int WS_THREADS = 32 * (1 + WS_PRODUCERS);
+constexpr int WS_SMEM = WS_STAGES * WS_ROWS * 32 * (int)sizeof(double) + 2 * WS_STAGES * 8;
+
+__global__ void __launch_bounds__(WS_THREADS)
+k_chain_ws(const ChainSide A, const ChainSide B, long units_a, int F, int ld)
+{
+	extern __shared__ __align__(16) double smem[];
+	double *ring = smem;                                    /* [WS_STAGES][WS_ROWS][32] */
+	const uint32_t bars = smem_u32(smem + WS_STAGES * WS_ROWS * 32);
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	const int NG = (F + 31) >> 5;
+	long w = blockIdx.x;
+	const bool is_a = w < units_a;
+	const ChainSide &sd = is_a ? A : B;
+	if (!is_a)
+		w -= units_a;
+	const int r = sd.begin + (int)(w / NG), g = (int)(w % NG);
+	const int k = g * 32 + lane;
+	const bool active = k < F;
+	const int b = sd.ptr[r], m = sd.ptr[r + 1] - b;
+	const int nst = (m + WS_ROWS - 1) / WS_ROWS;
+	auto full = [&](int slot) { return bars + 8u * slot; };
+	auto empty = [&](int slot) { return bars + 8u * (WS_STAGES + slot); };
+
+	if (threadIdx.x == 0)
+		for (int q = 0; q < 2 * WS_STAGES; q++)
+			mbar_init(bars + 8u * q, 1);
+	__syncthreads();
+
+	if (warp == 0) {
+		/* ---- consumer ---- */
+		const int own = sd.id[r];
+		double acc = (sd.init && active) ? sd.init[(size_t)(own - sd.own_off) * ld + k] : 0.0;
+		double va[WS_ROWS], vb[WS_ROWS];
+		auto take = [&](double (&v)[WS_ROWS], int s) {    /* stage s into registers, slot back */
+			const int slot = s % WS_STAGES;
+			mbar_wait(full(slot), (s / WS_STAGES) & 1);
+			const double *x = ring + (size_t)slot * WS_ROWS * 32 + lane;
+#pragma unroll
+			for (int q = 0; q < WS_ROWS; q++)
+				v[q] = x[q * 32];
+			__syncwarp();
+			if (lane == 0)
+				mbar_arrive(empty(slot));
+		};
+		auto add = [&](const double (&v)[WS_ROWS], int s) {
+			const int rows = m - s * WS_ROWS;
+			if (rows >= WS_ROWS) {
+#pragma unroll
+				for (int q = 0; q < WS_ROWS; q++)
+					acc = __dadd_rn(acc, v[q]);
+			} else {
+#pragma unroll
+				for (int q = 0; q < WS_ROWS; q++)
+					if (q < rows)
+						acc = __dadd_rn(acc, v[q]);
+			}
+		};
+		if (nst > 0)
+			take(va, 0);
+		for (int s = 0; s < nst; s += 2) {
+			if (s + 1 < nst)
+				take(vb, s + 1);
+			add(va, s);
+			if (s + 2 < nst)
+				take(va, s + 2);
+			if (s + 1 < nst)
+				add(vb, s + 1);
+		}
+		if (active) {
+			const size_t orow = sd.out_slot ? (size_t)sd.out_slot[own] : (size_t)(own - sd.own_off);
+			sd.out[orow * ld + k] = acc;
+		}
+		return;
+	}
+
+	/* ---- producers: warp p takes stages p-1, p-1+WS_PRODUCERS, ... ---- */
+	const double *srck = sd.src + (active ? k : 0) - (size_t)sd.src_off * ld;   /* idle lanes: a valid column */
+	const int *idx = sd.idx + b;
+	const double *ev = sd.e + b;
+	int ia, ib;
+	double ea, eb, xa[WS_ROWS], xb[WS_ROWS];
+	auto fetch = [&](int s, int &i_, double &e_, double (&x)[WS_ROWS]) {
+		/* lanes < WS_ROWS carry (idx, e) of the stage's nonzeros; past the end of the chain
+		 * the last nonzero is read again (and never added) */
+		const int n = min(s * WS_ROWS + (lane & (WS_ROWS - 1)), m - 1);
+		i_ = idx[n];
+		e_ = ev[n];
+#pragma unroll
+		for (int q = 0; q < WS_ROWS; q++)
+			x[q] = srck[(size_t)__shfl_sync(FULL, i_, q) * ld];
+	};
+	auto put = [&](int s, double e_, const double (&x)[WS_ROWS]) {
+		const int slot = s % WS_STAGES;
+		if (s >= WS_STAGES)
+			mbar_wait(empty(slot), ((s / WS_STAGES) - 1) & 1);
+		double *dst = ring + (size_t)slot * WS_ROWS * 32 + lane;
+#pragma unroll
+		for (int q = 0; q < WS_ROWS; q++)
+			dst[q * 32] = __dmul_rn(__shfl_sync(FULL, e_, q), x[q]);
+		__syncwarp();
+		if (lane == 0)
+			mbar_arrive(full(slot));
+	};
+	int s = warp - 1;
+	if (s < nst)
+		fetch(s, ia, ea, xa);
+	for (; s < nst; s += 2 * WS_PRODUCERS) {
+		const int s1 = s + WS_PRODUCERS, s2 = s + 2 * WS_PRODUCERS;
+		if (s1 < nst)
+			fetch(s1, ib, eb, xb);
+		put(s, ea, xa);
+		if (s2 < nst)
+			fetch(s2, ia, ea, xa);
+		if (s1 < nst)
+			put(s1, eb, xb);
+	}
+}
+
 /* N shards: R_new[item] = R_old[item] + G[slot] for the touched items. */
 __global__ void __launch_bounds__(256)
 k_apply_R(int n_touched, int F, int ld, const int *__restrict__ touched_item,

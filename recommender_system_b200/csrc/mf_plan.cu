@@ -308,6 +308,7 @@ static int plan_create(mfgpu_plan **out, int users, int items, int features, int
 	pl->opt_chain_ring = 1;
 	pl->opt_resident = 1;
 	pl->opt_res_rows = 0;
+	pl->opt_chain_ws = 1;
 
 	int rc = mf_split_users(users, nnz, entries, nshards, pl->cut);
 	int *item_slot = nullptr, *touched = nullptr;
@@ -510,6 +511,7 @@ extern "C" int mfgpu_plan_set_option(mfgpu_plan *pl, const char *name, int value
 	else if (!strcmp(name, "chain_ring")) pl->opt_chain_ring = value;
 	else if (!strcmp(name, "resident")) pl->opt_resident = value;
 	else if (!strcmp(name, "res_rows")) pl->opt_res_rows = value;
+	else if (!strcmp(name, "chain_ws")) pl->opt_chain_ws = value;
 	else
 		return mf_fail(MFGPU_EINVAL, "unknown option '%s'", name);
 	for (int g = 0; g < local_shards(pl); g++) {
