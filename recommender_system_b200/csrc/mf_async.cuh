@@ -46,6 +46,17 @@ __device__ __forceinline__ void cp_async_wait()
 	asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
+/* 8-byte asynchronous copy (for operands that are only 8-byte aligned) */
+__device__ __forceinline__ void cp_async8(void *dst, const void *src)
+{
+	asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
+
+__device__ __forceinline__ void cp_async4(void *dst, const void *src)
+{
+	asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
+
 /* ---- mbarriers in shared memory (CTA scope): producer / consumer hand-over of ring stages ---- */
 
 __device__ __forceinline__ void mbar_init(uint32_t bar, int count)
@@ -57,6 +68,13 @@ __device__ __forceinline__ void mbar_init(uint32_t bar, int count)
 __device__ __forceinline__ void mbar_arrive(uint32_t bar)
 {
 	asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+
+/* one (pre-counted) arrival that happens when every cp.async this thread has issued so far has
+ * landed: the copies of a stage signal their own completion, nobody waits for them */
+__device__ __forceinline__ void mbar_arrive_on_copies(uint32_t bar)
+{
+	asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
 }
 
 __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity)

@@ -64,6 +64,7 @@ static int prepare_res(size_t smem)
 int mf_kernels_prepare(int warps, size_t k1_smem, int res_ng, size_t res_smem)
 {
 	const auto attr = cudaFuncAttributeMaxDynamicSharedMemorySize;
+	CK(cudaFuncSetAttribute(mf::k_chain_ws, attr, mf::WS_SMEM));
 	switch (res_ng) {
 	case 1: TRY(prepare_res<1>(res_smem)); break;
 	case 2: TRY(prepare_res<2>(res_smem)); break;

@@ -34,6 +34,9 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#ifdef MF_WS_DEBUG
+#include <cstdio>
+#endif
 #include "mf_types.h"
 #include "mf_async.cuh"
 
@@ -820,28 +823,34 @@ k_chain(const ChainSide A, const ChainSide B, long warps_a, int F, int ld)
 /*
  * k_chain_ws: the same sequential accumulation for the longest chains, one CTA per (row or
  * column, group of 32 features) with the work split over specialised warps.  What bounds a
- * long chain is the latency of one warp: ~13 instructions per nonzero in k_chain, although
- * only the addition has to be serial (8 cycles, profiles/r01_ubench_fp64.txt).  Here
- *   warps 1..WS_PRODUCERS  take stages of WS_ROWS nonzeros round robin: gather x[n] = src[idx[n]]
- *       (one coalesced 256-byte read per nonzero, two stages in flight per warp), form
- *       the products e[n]*x[n] -- they do not depend on the chain -- and store them in a
- *       ring of WS_STAGES stages in shared memory;
- *   warp 0  reads the products of a stage into registers, hands the stage back, and adds
- *       them to the accumulator in file order while the next stage is being read:
- *       one LDS and one DADD per nonzero.
- * Stages are handed over through mbarriers (full[slot]: one producer arrival; empty[slot]:
- * one consumer arrival).
+ * long chain is the latency of one warp: in k_chain ~13 instructions per nonzero plus
+ * exposed load latencies (a warp's loads share six scoreboards, so waiting for an old gather
+ * also waits for the newest), although only the addition has to be serial (8 cycles,
+ * profiles/r01_ubench_fp64.txt).  Here
+ *   warps 1, 2 (producers) take the stages of WS_ROWS = 32 nonzeros alternately: 16-byte
+ *       cp.async of x[n] = src[idx[n]] (a half-warp per nonzero) and 8-byte cp.async of e[n]
+ *       into a ring of WS_STAGES stages; the copies signal the stage's `full` mbarrier
+ *       themselves when they land, so a producer never waits for data, only for a free
+ *       slot.  The indices themselves run WS_IDX_AHEAD blocks ahead in a small ring of the
+ *       warp's own (4-byte cp.async): cp.async groups complete in order, so
+ *       wait_group<WS_IDX_AHEAD> means "my next block has landed" without waiting for the
+ *       younger ones, which a register load cannot express;
+ *   warp 0 (consumer) reads a landed stage into registers, adds e[n]*x[n] in file order
+ *       (one LDS, one DMUL, one DADD per nonzero) and hands the slot back (`empty`).
+ * WS_STAGES x WS_ROWS = 192 nonzeros are in flight ahead of the additions.
  */
-constexpr int WS_PRODUCERS = 4, WS_ROWS = 16, WS_STAGES = 8;
+constexpr int WS_PRODUCERS = 2, WS_ROWS = 32, WS_STAGES = 6;
 constexpr int WS_THREADS = 32 * (1 + WS_PRODUCERS);
-constexpr int WS_SMEM = WS_STAGES * WS_ROWS * 32 * (int)sizeof(double) + 2 * WS_STAGES * 8;
+constexpr int WS_STAGE_DOUBLES = WS_ROWS * 32 + WS_ROWS;          /* x[32][32] | e[32] */
+constexpr int WS_IDX_AHEAD = 4, WS_IDX_BLOCKS = 8;                 /* blocks of 32 indices, per producer */
+constexpr int WS_SMEM = (WS_STAGES * WS_STAGE_DOUBLES + 2 * WS_STAGES) * (int)sizeof(double) +
+                        WS_PRODUCERS * WS_IDX_BLOCKS * 32 * (int)sizeof(int);
 
 __global__ void __launch_bounds__(WS_THREADS)
 k_chain_ws(const ChainSide A, const ChainSide B, long units_a, int F, int ld)
 {
 	extern __shared__ __align__(16) double smem[];
-	double *ring = smem;                                    /* [WS_STAGES][WS_ROWS][32] */
-	const uint32_t bars = smem_u32(smem + WS_STAGES * WS_ROWS * 32);
+	const uint32_t bars = smem_u32(smem + WS_STAGES * WS_STAGE_DOUBLES);
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 	const int NG = (F + 31) >> 5;
 	long w = blockIdx.x;
@@ -850,57 +859,55 @@ k_chain_ws(const ChainSide A, const ChainSide B, long units_a, int F, int ld)
 	if (!is_a)
 		w -= units_a;
 	const int r = sd.begin + (int)(w / NG), g = (int)(w % NG);
-	const int k = g * 32 + lane;
-	const bool active = k < F;
 	const int b = sd.ptr[r], m = sd.ptr[r + 1] - b;
 	const int nst = (m + WS_ROWS - 1) / WS_ROWS;
 	auto full = [&](int slot) { return bars + 8u * slot; };
 	auto empty = [&](int slot) { return bars + 8u * (WS_STAGES + slot); };
 
 	if (threadIdx.x == 0)
-		for (int q = 0; q < 2 * WS_STAGES; q++)
-			mbar_init(bars + 8u * q, 1);
+		for (int q = 0; q < WS_STAGES; q++) {
+			mbar_init(full(q), 32);       /* the 32 lanes of the stage's producer */
+			mbar_init(empty(q), 1);       /* lane 0 of the consumer                 */
+		}
 	__syncthreads();
 
 	if (warp == 0) {
 		/* ---- consumer ---- */
+		const int k = g * 32 + lane;
+		const bool active = k < F;
 		const int own = sd.id[r];
 		double acc = (sd.init && active) ? sd.init[(size_t)(own - sd.own_off) * ld + k] : 0.0;
-		double va[WS_ROWS], vb[WS_ROWS];
-		auto take = [&](double (&v)[WS_ROWS], int s) {    /* stage s into registers, slot back */
+		for (int s = 0; s < nst; s++) {
 			const int slot = s % WS_STAGES;
+			const double *st = smem + (size_t)slot * WS_STAGE_DOUBLES;
+			double x[WS_ROWS];
+			double2 e[WS_ROWS / 2];
 			mbar_wait(full(slot), (s / WS_STAGES) & 1);
-			const double *x = ring + (size_t)slot * WS_ROWS * 32 + lane;
 #pragma unroll
 			for (int q = 0; q < WS_ROWS; q++)
-				v[q] = x[q * 32];
-			__syncwarp();
-			if (lane == 0)
-				mbar_arrive(empty(slot));
-		};
-		auto add = [&](const double (&v)[WS_ROWS], int s) {
+				x[q] = st[q * 32 + lane];
+#pragma unroll
+			for (int q = 0; q < WS_ROWS / 2; q++)
+				e[q] = ld2(st + WS_ROWS * 32 + 2 * q);
 			const int rows = m - s * WS_ROWS;
 			if (rows >= WS_ROWS) {
 #pragma unroll
-				for (int q = 0; q < WS_ROWS; q++)
-					acc = __dadd_rn(acc, v[q]);
+				for (int q = 0; q < WS_ROWS / 2; q++) {
+					acc = __dadd_rn(acc, __dmul_rn(e[q].x, x[2 * q]));
+					acc = __dadd_rn(acc, __dmul_rn(e[q].y, x[2 * q + 1]));
+				}
 			} else {
 #pragma unroll
-				for (int q = 0; q < WS_ROWS; q++)
-					if (q < rows)
-						acc = __dadd_rn(acc, v[q]);
+				for (int q = 0; q < WS_ROWS / 2; q++) {
+					if (2 * q < rows)
+						acc = __dadd_rn(acc, __dmul_rn(e[q].x, x[2 * q]));
+					if (2 * q + 1 < rows)
+						acc = __dadd_rn(acc, __dmul_rn(e[q].y, x[2 * q + 1]));
+				}
 			}
-		};
-		if (nst > 0)
-			take(va, 0);
-		for (int s = 0; s < nst; s += 2) {
-			if (s + 1 < nst)
-				take(vb, s + 1);
-			add(va, s);
-			if (s + 2 < nst)
-				take(va, s + 2);
-			if (s + 1 < nst)
-				add(vb, s + 1);
+			__syncwarp();
+			if (lane == 0)
+				mbar_arrive(empty(slot));
 		}
 		if (active) {
 			const size_t orow = sd.out_slot ? (size_t)sd.out_slot[own] : (size_t)(own - sd.own_off);
@@ -909,47 +916,48 @@ k_chain_ws(const ChainSide A, const ChainSide B, long units_a, int F, int ld)
 		return;
 	}
 
-	/* ---- producers: warp p takes stages p-1, p-1+WS_PRODUCERS, ... ---- */
-	const double *srck = sd.src + (active ? k : 0) - (size_t)sd.src_off * ld;   /* idle lanes: a valid column */
+	/* ---- producer p: stages p, p + 2, ... (stage s = nonzeros 32s .. 32s+31) ---- */
+	const int p = warp - 1;
+	const int half = lane >> 4, piece = lane & 15;
+	const int gw = min(32, ld - g * 32);                 /* doubles of this group in a row (even) */
+	const bool piece_ok = 2 * piece < gw;
+	const double *src_g = sd.src + g * 32 + 2 * piece - (size_t)sd.src_off * ld;
 	const int *idx = sd.idx + b;
 	const double *ev = sd.e + b;
-	int ia, ib;
-	double ea, eb, xa[WS_ROWS], xb[WS_ROWS];
-	auto fetch = [&](int s, int &i_, double &e_, double (&x)[WS_ROWS]) {
-		/* lanes < WS_ROWS carry (idx, e) of the stage's nonzeros; past the end of the chain
-		 * the last nonzero is read again (and never added) */
-		const int n = min(s * WS_ROWS + (lane & (WS_ROWS - 1)), m - 1);
-		i_ = idx[n];
-		e_ = ev[n];
-#pragma unroll
-		for (int q = 0; q < WS_ROWS; q++)
-			x[q] = srck[(size_t)__shfl_sync(FULL, i_, q) * ld];
+	int *iring = (int *)(smem + WS_STAGES * WS_STAGE_DOUBLES + 2 * WS_STAGES) + p * WS_IDX_BLOCKS * 32;
+	auto request = [&](int t) {          /* indices of this producer's t-th stage */
+		const int s = 2 * t + p;
+		if (s < nst)
+			cp_async4(iring + (t % WS_IDX_BLOCKS) * 32 + lane, idx + min(s * 32 + lane, m - 1));
+		cp_async_commit();
 	};
-	auto put = [&](int s, double e_, const double (&x)[WS_ROWS]) {
-		const int slot = s % WS_STAGES;
+#pragma unroll
+	for (int t = 0; t < WS_IDX_AHEAD; t++)
+		request(t);
+	for (int t = 0; 2 * t + p < nst; t++) {
+		const int s = 2 * t + p, slot = s % WS_STAGES;
+		request(t + WS_IDX_AHEAD);
+		cp_async_wait<WS_IDX_AHEAD>();
+		__syncwarp();
+		const int *bi = iring + (t % WS_IDX_BLOCKS) * 32 + half;
+		int iu[WS_ROWS / 2];             /* all indices first: the copies are compiler barriers */
+#pragma unroll
+		for (int u = 0; u < WS_ROWS / 2; u++)
+			iu[u] = bi[2 * u];
 		if (s >= WS_STAGES)
 			mbar_wait(empty(slot), ((s / WS_STAGES) - 1) & 1);
-		double *dst = ring + (size_t)slot * WS_ROWS * 32 + lane;
+		double *st = smem + (size_t)slot * WS_STAGE_DOUBLES;
+		const uint32_t st_addr = smem_u32(st) + (uint32_t)(half * 32 + 2 * piece) * 8u;
 #pragma unroll
-		for (int q = 0; q < WS_ROWS; q++)
-			dst[q * 32] = __dmul_rn(__shfl_sync(FULL, e_, q), x[q]);
-		__syncwarp();
-		if (lane == 0)
-			mbar_arrive(full(slot));
-	};
-	int s = warp - 1;
-	if (s < nst)
-		fetch(s, ia, ea, xa);
-	for (; s < nst; s += 2 * WS_PRODUCERS) {
-		const int s1 = s + WS_PRODUCERS, s2 = s + 2 * WS_PRODUCERS;
-		if (s1 < nst)
-			fetch(s1, ib, eb, xb);
-		put(s, ea, xa);
-		if (s2 < nst)
-			fetch(s2, ia, ea, xa);
-		if (s1 < nst)
-			put(s1, eb, xb);
+		for (int u = 0; u < WS_ROWS / 2; u++)
+			cp_async16_if(st_addr + u * 512u, src_g + (size_t)iu[u] * ld, piece_ok);
+		const int n = s * WS_ROWS + lane;
+		if (n < m)
+			cp_async8(st + WS_ROWS * 32 + lane, ev + n);
+		mbar_arrive_on_copies(full(slot));
+		__syncwarp();                 /* ring entry t + WS_IDX_BLOCKS overwrites this block */
 	}
+	cp_async_wait<0>();
 }
 
 /* N shards: R_new[item] = R_old[item] + G[slot] for the touched items. */

@@ -51,7 +51,9 @@ int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
 	/* Row classes.  A warp of k_update_L spends ~100 cycles per nonzero, so a row much longer
 	 * than the per-warp share of the shard (nnz / (8 warps x SMs)) would outlast the rest of
 	 * the launch: such rows have their dots spread over warps by k_dot.  Chains longer than
-	 * ~nnz / (4 x SMs) get the deep register pipeline of k_chain, the rest the light one. */
+	 * ~nnz / (8 x SMs) go to k_chain_ws (one CTA of specialised warps per chain and feature
+	 * group: ~20 cycles per nonzero against ~70 for a warp of k_chain, but three warps and
+	 * 52 KB of shared memory per chain), the rest to k_chain. */
 	int n_sm = 148;
 	CK(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, s->dev));
 	n_sm = std::max(1, n_sm);
@@ -59,7 +61,7 @@ int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
 	const int share = (int)std::min<long>(1 << 30, (long)pt.nnz / (16L * n_sm));
 	const int long_thresh = pl->opt_long_row > 0 ? pl->opt_long_row : std::max(2 * CH, share);
 	const int deep_thresh = pl->opt_long_col > 0 ? pl->opt_long_col
-	                                             : std::max(64, (int)std::min<long>(1 << 30, (long)pt.nnz / (4L * n_sm)));
+	                                             : std::max(64, (int)std::min<long>(1 << 30, (long)pt.nnz / (8L * n_sm)));
 	int n_long = 0, n_deep_rows = 0, n_deep_cols = 0;
 	if (warps > 1)
 		while (n_long < pt.n_rows && pt.row_ptr[n_long + 1] - pt.row_ptr[n_long] > long_thresh)
