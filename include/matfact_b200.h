@@ -125,7 +125,8 @@ int mfgpu_plan_restore_factors(mfgpu_plan *plan);
  * back-to-back launches of each loop kernel on the current factors; the factors
  * are left unchanged.  ms[0] = by-user pass of the short rows (k_update_L),
  * ms[1] = dots of the long rows (k_dot), ms[2] / ms[3] = sequential accumulations
- * (k_chain, bulk / deep launch), ms[4] = exchange + apply (rank mode, else 0). */
+ * (k_chain for the bulk of the chains / k_chain_ws for the longest ones), ms[4] =
+ * exchange + apply (rank mode, else 0). */
 int mfgpu_plan_profile_kernels(mfgpu_plan *plan, int reps, float ms[5]);
 /* Algorithmic (compulsory) bytes of one launch of each of those kernels on shard 0. */
 int mfgpu_plan_kernel_bytes(mfgpu_plan *plan, long long bytes[5]);
@@ -134,7 +135,20 @@ int mfgpu_plan_kernel_bytes(mfgpu_plan *plan, long long bytes[5]);
  * plan's devices).  Everything enqueued on the plan in between is covered. */
 int mfgpu_plan_timer_start(mfgpu_plan *plan);
 int mfgpu_plan_timer_stop(mfgpu_plan *plan, float *ms);
-/* Tuning knob for experiments: name = "l_warps", "r_warps", "graph" ... */
+/* Launch-configuration knobs (tests and experiments; none of them changes a bit
+ * of the result).  value 0 restores the default where one is derived from the input.
+ *   "graph"        1/0   iterations replayed from CUDA graphs (default 1)
+ *   "graph_iters"  n     iterations captured per graph (default 16)
+ *   "long_row"     n     rows longer than n nonzeros have their dots done by k_dot
+ *   "long_col"     n     chains longer than n nonzeros go to the long-chain kernel
+ *   "chunk"        n     nonzeros per chunk of the tiled dot phase (1..32)
+ *   "resident"     0/1/2 short rows with their gathered R rows resident in shared
+ *                        memory: never / when eight warps fit an SM (default) / always
+ *   "res_rows"     n     resident rows per chunk (1..32)
+ *   "chain_ws"     1/0   warp-specialised kernel for the longest chains (default 1)
+ *   "chain_ring"   1/0   k_chain gathers through a shared-memory ring / registers
+ * May be set between iterate calls (the plan is reconfigured); unknown names return
+ * MFGPU_EINVAL. */
 int mfgpu_plan_set_option(mfgpu_plan *plan, const char *name, int value);
 
 /* ---- multi-process groups (one process per GPU, e.g. under torchrun) -------- */
