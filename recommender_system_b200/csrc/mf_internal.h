@@ -51,6 +51,8 @@ struct mf_shard {
 	int k1_blocks, dot_blocks;
 	int res_ng;                              /* > 0: k_update_L_res<res_ng> does the short rows */
 	size_t res_smem;
+	void *host_ws;                           /* page-locked workspace of `pat`, from the arena cache */
+	size_t host_ws_bytes;
 	long long kbytes[5];                     /* algorithmic bytes per launch of each kernel */
 	size_t k1_smem;
 	cudaGraphExec_t gexec[2];                /* by starting parity                */

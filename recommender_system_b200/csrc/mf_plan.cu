@@ -20,10 +20,124 @@
 #include <new>
 #include <vector>
 
+/* MFGPU_TRACE=1: wall-clock of the phases of plan creation / destruction on stderr */
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+static bool trace_on()
+{
+	static const bool on = getenv("MFGPU_TRACE") != nullptr;
+	return on;
+}
+struct TraceClock {
+	std::chrono::steady_clock::time_point t = std::chrono::steady_clock::now();
+	void lap(const char *what)
+	{
+		if (!trace_on())
+			return;
+		const auto n = std::chrono::steady_clock::now();
+		fprintf(stderr, "[mfgpu] %-28s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(n - t).count());
+		t = n;
+	}
+};
+
+/* Device buffers come from the device's default memory pool in stream order, and the pool keeps
+ * what is freed (release threshold = everything): a process that factorizes one matrix after
+ * another pays cudaMalloc/cudaFree (milliseconds per 100 MB) once, not per plan.  Buffers that
+ * peers or NCCL touch (G) stay plain cudaMalloc. */
+static int pool_prepare(int dev)
+{
+	static bool done[64];
+	if (dev < 0 || dev >= 64 || done[dev])
+		return MFGPU_OK;
+	cudaMemPool_t pool;
+	CK(cudaDeviceGetDefaultMemPool(&pool, dev));
+	unsigned long long keep = ~0ull;
+	CK(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+	done[dev] = true;
+	return MFGPU_OK;
+}
+
+static int dev_alloc(void **p, size_t bytes, cudaStream_t st)
+{
+	CK(cudaMallocAsync(p, bytes ? bytes : 1, st));
+	return MFGPU_OK;
+}
+
+static void dev_free(void *p, cudaStream_t st)
+{
+	if (p)
+		cudaFreeAsync(p, st);
+}
+
+/* Page-locked host workspaces for the patterns, kept from one plan to the next (a handful,
+ * at most 1 GB in total): cudaHostAlloc costs milliseconds, first-touch page faults of a
+ * fresh 20 MB pattern cost more than building it, and uploads from pageable memory are not
+ * DMA.  A workspace that cannot be had is not an error: the pattern then uses malloc. */
+#include <mutex>
+namespace {
+struct HostWs { void *p; size_t bytes; };
+std::mutex g_ws_mutex;
+std::vector<HostWs> g_ws_free;
+
+void *ws_acquire(size_t need, size_t *got)
+{
+	{
+		std::lock_guard<std::mutex> lk(g_ws_mutex);
+		int best = -1;
+		for (int i = 0; i < (int)g_ws_free.size(); i++)
+			if (g_ws_free[i].bytes >= need && (best < 0 || g_ws_free[i].bytes < g_ws_free[best].bytes))
+				best = i;
+		if (best >= 0) {
+			HostWs w = g_ws_free[best];
+			g_ws_free.erase(g_ws_free.begin() + best);
+			*got = w.bytes;
+			return w.p;
+		}
+	}
+	void *p = nullptr;
+	const size_t bytes = need + need / 8 + 4096;
+	if (cudaHostAlloc(&p, bytes, cudaHostAllocPortable) != cudaSuccess) {
+		cudaGetLastError();
+		return nullptr;
+	}
+	*got = bytes;
+	return p;
+}
+
+void ws_release(void *p, size_t bytes)
+{
+	if (!p)
+		return;
+	{
+		std::lock_guard<std::mutex> lk(g_ws_mutex);
+		size_t total = bytes;
+		for (const HostWs &w : g_ws_free)
+			total += w.bytes;
+		if (g_ws_free.size() < 16 && total <= ((size_t)1 << 30)) {
+			g_ws_free.push_back({p, bytes});
+			return;
+		}
+	}
+	cudaFreeHost(p);
+}
+} // namespace
+
+/* rows of `width` doubles between matrices of row strides dld / sld doubles */
+static int copy_rows(double *dst, size_t dld, const double *src, size_t sld, size_t width, size_t rows,
+                     cudaMemcpyKind kind, cudaStream_t st)
+{
+	if (dld == width && sld == width)
+		CK(cudaMemcpyAsync(dst, src, rows * width * sizeof(double), kind, st));
+	else
+		CK(cudaMemcpy2DAsync(dst, dld * 8, src, sld * 8, width * 8, rows, kind, st));
+	return MFGPU_OK;
+}
+
 template <typename T>
 static int upload(T **dst, const T *src, size_t n, cudaStream_t st)
 {
-	CK(cudaMalloc((void **)dst, (n ? n : 1) * sizeof(T)));
+	TRY(dev_alloc((void **)dst, n * sizeof(T), st));
 	if (n)
 		CK(cudaMemcpyAsync(*dst, src, n * sizeof(T), cudaMemcpyHostToDevice, st));
 	return MFGPU_OK;
@@ -101,8 +215,8 @@ int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
 			chunk_row.push_back(r);
 			chunk_pos.push_back(pos);
 		}
-	cudaFree(s->d_chunk_row);
-	cudaFree(s->d_chunk_pos);
+	dev_free(s->d_chunk_row, s->st);
+	dev_free(s->d_chunk_pos, s->st);
 	s->d_chunk_row = s->d_chunk_pos = nullptr;
 	TRY(upload(&s->d_chunk_row, chunk_row.data(), chunk_row.size(), s->st));
 	TRY(upload(&s->d_chunk_pos, chunk_pos.data(), chunk_pos.size(), s->st));
@@ -175,6 +289,7 @@ static int shard_create(mfgpu_plan *pl, mf_shard *s, int dev, const mfgpu_entry 
 {
 	s->dev = dev;
 	CK(cudaSetDevice(dev));
+	TRY(pool_prepare(dev));
 	CK(cudaStreamCreateWithFlags(&s->st, cudaStreamNonBlocking));
 	CK(cudaStreamCreateWithFlags(&s->st2, cudaStreamNonBlocking));
 	CK(cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming));
@@ -187,7 +302,13 @@ static int shard_create(mfgpu_plan *pl, mf_shard *s, int dev, const mfgpu_entry 
 	CK(cudaEventCreate(&s->ev_t1));
 	for (int g = 0; g < 2; g++)
 		CK(cudaEventCreateWithFlags(&s->ev_g[g], cudaEventDisableTiming));
-	int rc = mf_pattern_build(&s->pat, pl->users, pl->items, pl->nnz, entries, s->user_lo, s->user_hi);
+	TraceClock tc;
+	s->host_ws = ws_acquire(mf_pattern_ws_bytes(pl->users, pl->items, pl->nnz, s->user_lo, s->user_hi),
+	                        &s->host_ws_bytes);
+	tc.lap("create: host workspace");
+	int rc = mf_pattern_build_ws(&s->pat, pl->users, pl->items, pl->nnz, entries, s->user_lo, s->user_hi,
+	                             s->host_ws, s->host_ws_bytes);
+	tc.lap("create: pattern build (host)");
 	if (rc != MFGPU_OK)
 		return mf_fail(rc, rc == MFGPU_EINVAL ? "an entry lies outside the users x items matrix"
 		                                      : "out of host memory building the pattern");
@@ -203,15 +324,16 @@ static int shard_create(mfgpu_plan *pl, mf_shard *s, int dev, const mfgpu_entry 
 	TRY(upload(&s->d_mask_ptr, p.mask_ptr, (size_t)pl->users + 1, s->st));
 	TRY(upload(&s->d_mask_col, p.mask_col, (size_t)p.mask_ptr[pl->users], s->st));
 	TRY(upload(&s->d_first_free, p.first_free, (size_t)pl->users, s->st));
-	CK(cudaMalloc((void **)&s->d_e_csc, ((size_t)p.nnz + 1) * sizeof(double)));
-	CK(cudaMalloc((void **)&s->d_e_csr, ((size_t)p.nnz + 1) * sizeof(double)));
+	tc.lap("create: pattern upload");
+	TRY(dev_alloc((void **)&s->d_e_csc, ((size_t)p.nnz + 1) * sizeof(double), s->st));
+	TRY(dev_alloc((void **)&s->d_e_csr, ((size_t)p.nnz + 1) * sizeof(double), s->st));
 
 	const size_t nu = (size_t)(s->user_hi - s->user_lo);
 	const size_t lbytes = (nu * pl->ld + 2) * sizeof(double);
 	const size_t rbytes = ((size_t)pl->items * pl->ld + 2) * sizeof(double);
 	for (int b = 0; b < 2; b++) {
-		CK(cudaMalloc((void **)&s->L[b], lbytes));
-		CK(cudaMalloc((void **)&s->R[b], rbytes));
+		TRY(dev_alloc((void **)&s->L[b], lbytes, s->st));
+		TRY(dev_alloc((void **)&s->R[b], rbytes, s->st));
 		CK(cudaMemsetAsync(s->L[b], 0, lbytes, s->st));
 		CK(cudaMemsetAsync(s->R[b], 0, rbytes, s->st));
 	}
@@ -231,12 +353,15 @@ static int shard_create(mfgpu_plan *pl, mf_shard *s, int dev, const mfgpu_entry 
 	int splits = tiles_y > 0 ? (148 * 4 + tiles_y - 1) / tiles_y : 1;
 	splits = std::max(1, std::min(splits, std::max(1, n_tiles)));
 	s->am_splits = splits;
-	CK(cudaMalloc((void **)&s->part_v, (nu * splits + 1) * sizeof(double)));
-	CK(cudaMalloc((void **)&s->part_j, (nu * splits + 1) * sizeof(int)));
-	CK(cudaMalloc((void **)&s->nan_first, (nu + 1) * sizeof(int)));
-	CK(cudaMalloc((void **)&s->d_best, (nu + 1) * sizeof(int)));
+	TRY(dev_alloc((void **)&s->part_v, (nu * splits + 1) * sizeof(double), s->st));
+	TRY(dev_alloc((void **)&s->part_j, (nu * splits + 1) * sizeof(int), s->st));
+	TRY(dev_alloc((void **)&s->nan_first, (nu + 1) * sizeof(int), s->st));
+	TRY(dev_alloc((void **)&s->d_best, (nu + 1) * sizeof(int), s->st));
+	tc.lap("create: factor buffers");
 	TRY(mf_configure_shard(pl, s));
+	tc.lap("create: configure");
 	CK(cudaStreamSynchronize(s->st));
+	tc.lap("create: sync");
 	return MFGPU_OK;
 }
 
@@ -244,19 +369,26 @@ static void shard_destroy(mf_shard *s)
 {
 	if (s->dev >= 0)
 		cudaSetDevice(s->dev);
-	for (int g = 0; g < 2; g++) {
+	TraceClock tc;
+	if (s->st) cudaStreamSynchronize(s->st);
+	if (s->st2) cudaStreamSynchronize(s->st2);
+	for (int g = 0; g < 2; g++)
 		if (s->gexec[g]) cudaGraphExecDestroy(s->gexec[g]);
+	tc.lap("destroy: graphs");
+	for (int g = 0; g < 2; g++) {
 		if (s->ev_g[g]) cudaEventDestroy(s->ev_g[g]);
-		cudaFree(s->L[g]);
-		cudaFree(s->R[g]);
+		dev_free(s->L[g], s->st);
+		dev_free(s->R[g], s->st);
 		cudaFree(s->G[g]);
 	}
+	tc.lap("destroy: factor buffers");
 	void *ptrs[] = {s->d_row_id, s->d_row_ptr, s->d_col_idx, s->d_epos, s->d_col_id, s->d_col_ptr,
 	                s->d_row_idx, s->d_val, s->d_e_csc, s->d_e_csr, s->d_mask_ptr, s->d_mask_col,
 	                s->d_first_free, s->d_item_slot, s->d_touched_item, s->part_v, s->part_j,
 	                s->nan_first, s->d_best, s->L_keep, s->R_keep, s->d_chunk_row, s->d_chunk_pos};
 	for (void *q : ptrs)
-		cudaFree(q);
+		dev_free(q, s->st);
+	tc.lap("destroy: other buffers");
 	if (s->ev0) cudaEventDestroy(s->ev0);
 	if (s->ev1) cudaEventDestroy(s->ev1);
 	if (s->ev_t0) cudaEventDestroy(s->ev_t0);
@@ -267,7 +399,11 @@ static void shard_destroy(mf_shard *s)
 	if (s->ev_b) cudaEventDestroy(s->ev_b);
 	if (s->st2) cudaStreamDestroy(s->st2);
 	if (s->st) cudaStreamDestroy(s->st);
+	tc.lap("destroy: events, streams");
 	mf_pattern_free(&s->pat);
+	ws_release(s->host_ws, s->host_ws_bytes);
+	s->host_ws = nullptr;
+	tc.lap("destroy: host pattern");
 	cudaGetLastError();
 }
 
@@ -419,11 +555,9 @@ extern "C" int mfgpu_plan_set_factors(mfgpu_plan *pl, const double *L, const dou
 		CK(cudaSetDevice(s->dev));
 		const size_t nu = (size_t)(s->user_hi - s->user_lo);
 		if (F && nu)
-			CK(cudaMemcpy2DAsync(s->L[0], ld * 8, L + (size_t)s->user_lo * F, F * 8, F * 8, nu,
-			                     cudaMemcpyHostToDevice, s->st));
+			TRY(copy_rows(s->L[0], ld, L + (size_t)s->user_lo * F, F, F, nu, cudaMemcpyHostToDevice, s->st));
 		if (F && pl->items)
-			CK(cudaMemcpy2DAsync(s->R[0], ld * 8, R, F * 8, F * 8, (size_t)pl->items,
-			                     cudaMemcpyHostToDevice, s->st));
+			TRY(copy_rows(s->R[0], ld, R, F, F, (size_t)pl->items, cudaMemcpyHostToDevice, s->st));
 		/* rows without a nonzero are never rewritten, so both buffers start equal */
 		CK(cudaMemcpyAsync(s->L[1], s->L[0], nu * ld * 8, cudaMemcpyDeviceToDevice, s->st));
 		CK(cudaMemcpyAsync(s->R[1], s->R[0], (size_t)pl->items * ld * 8, cudaMemcpyDeviceToDevice, s->st));
@@ -446,11 +580,9 @@ extern "C" int mfgpu_plan_get_factors(mfgpu_plan *pl, double *L, double *R)
 		CK(cudaSetDevice(s->dev));
 		const size_t nu = (size_t)(s->user_hi - s->user_lo);
 		if (L && F && nu)
-			CK(cudaMemcpy2DAsync(L + (size_t)s->user_lo * F, F * 8, s->L[c], ld * 8, F * 8, nu,
-			                     cudaMemcpyDeviceToHost, s->st));
+			TRY(copy_rows(L + (size_t)s->user_lo * F, F, s->L[c], ld, F, nu, cudaMemcpyDeviceToHost, s->st));
 		if (R && g == 0 && F && pl->items)
-			CK(cudaMemcpy2DAsync(R, F * 8, s->R[c], ld * 8, F * 8, (size_t)pl->items,
-			                     cudaMemcpyDeviceToHost, s->st));
+			TRY(copy_rows(R, F, s->R[c], ld, F, (size_t)pl->items, cudaMemcpyDeviceToHost, s->st));
 	}
 	for (int g = 0; g < local_shards(pl); g++)
 		CK(cudaStreamSynchronize(pl->sh[g].st));
@@ -533,8 +665,8 @@ extern "C" int mfgpu_plan_save_factors(mfgpu_plan *pl)
 		CK(cudaSetDevice(s->dev));
 		const size_t lb = ((size_t)(s->user_hi - s->user_lo) * pl->ld + 2) * sizeof(double);
 		const size_t rb = ((size_t)pl->items * pl->ld + 2) * sizeof(double);
-		if (!s->L_keep) CK(cudaMalloc((void **)&s->L_keep, lb));
-		if (!s->R_keep) CK(cudaMalloc((void **)&s->R_keep, rb));
+		if (!s->L_keep) TRY(dev_alloc((void **)&s->L_keep, lb, s->st));
+		if (!s->R_keep) TRY(dev_alloc((void **)&s->R_keep, rb, s->st));
 		CK(cudaMemcpyAsync(s->L_keep, s->L[pl->cur], lb, cudaMemcpyDeviceToDevice, s->st));
 		CK(cudaMemcpyAsync(s->R_keep, s->R[pl->cur], rb, cudaMemcpyDeviceToDevice, s->st));
 	}

@@ -3,12 +3,39 @@
  */
 #include "mf_prep.h"
 
+#include <pthread.h>
 #include <stdlib.h>
 #include <string.h>
+#include <unistd.h>
+
+#define MF_PREP_MAX_THREADS 8
 
 static void *xcalloc(size_t n, size_t sz)
 {
 	return calloc(n ? n : 1, sz);
+}
+
+/* an array of the pattern: from the workspace when there is one; `zero` = start from zeros
+ * like calloc (the big per-nonzero arrays are written in full and skip that) */
+static void *palloc(mf_pattern *p, size_t n, size_t sz, int zero)
+{
+	if (!p->ws)
+		return xcalloc(n, sz);
+	size_t bytes = ((n ? n : 1) * sz + 63) & ~(size_t)63;
+	if (p->ws_used + bytes > p->ws_bytes)
+		return NULL;   /* reported as MFGPU_ENOMEM by the caller */
+	void *q = p->ws + p->ws_used;
+	p->ws_used += bytes;
+	if (zero)
+		memset(q, 0, bytes);
+	return q;
+}
+
+size_t mf_pattern_ws_bytes(int users, int items, int nnz, int user_lo, int user_hi)
+{
+	size_t nu = (size_t)(user_hi - user_lo), n = (size_t)nnz, u = (size_t)users, it = (size_t)items;
+	size_t ints = nu + it + (nu + 1) + (it + 1) + 4 * n + (u + 1) + u;   /* ids, ptrs, col/row idx, epos, mask */
+	return ints * sizeof(int) + n * sizeof(double) + 16 * 64;
 }
 
 /* Order `n_ids` ids by key[id] descending, ties by ascending id (counting sort). */
@@ -52,10 +79,110 @@ int mf_mask_prefix(int users, int items, int nnz, const mfgpu_entry *entries)
 	return n;
 }
 
+/* ---- the two passes over the entries, split over a few threads ------------------------------
+ * Thread t owns the contiguous slice [n0, n1) of the file.  Pass 1 counts the slice's nonzeros
+ * per row and per column; a prefix over the threads turns the counts into each thread's
+ * first write position in every row and column, so that pass 2 can scatter the slices
+ * concurrently and still leave every row and column in file order. */
+typedef struct {
+	const mfgpu_entry *entries;
+	int n0, n1, users, items, user_lo, user_hi;
+	int *row_cur, *col_cur;     /* [users], [items]: counts after pass 1, cursors in pass 2 */
+	int local, bad;
+	int first_unsorted;         /* pass 1: first n in the slice that does not grow strictly in (row, col) */
+	int matched, mask_at;       /* pass 2: entries n < matched go to mask_col from position mask_at */
+	mf_pattern *p;
+} prep_slice;
+
+static void *prep_count(void *arg)
+{
+	prep_slice *s = arg;
+	int local = 0;
+	long prev_r = -1, prev_c = -1;
+	if (s->n0 > 0) {
+		prev_r = s->entries[s->n0 - 1].row;
+		prev_c = s->entries[s->n0 - 1].col;
+	}
+	s->first_unsorted = s->n1;
+	for (int n = s->n0; n < s->n1; n++) {
+		int r = s->entries[n].row, c = s->entries[n].col;
+		if (r < 0 || r >= s->users || c < 0 || c >= s->items) {
+			s->bad = 1;
+			return NULL;
+		}
+		if (!(r > prev_r || (r == prev_r && c > prev_c)) && s->first_unsorted == s->n1)
+			s->first_unsorted = n;
+		prev_r = r;
+		prev_c = c;
+		if (r >= s->user_lo && r < s->user_hi) {
+			s->row_cur[r]++;
+			s->col_cur[c]++;
+			local++;
+		}
+	}
+	s->local = local;
+	return NULL;
+}
+
+static void *prep_scatter(void *arg)
+{
+	prep_slice *s = arg;
+	mf_pattern *p = s->p;
+	for (int n = s->n0; n < s->n1; n++) {
+		int r = s->entries[n].row, c = s->entries[n].col;
+		if (r < s->user_lo || r >= s->user_hi)
+			continue;
+		int pr = s->row_cur[r]++, pc = s->col_cur[c]++;
+		p->col_idx[pr] = c;
+		p->val[pr] = s->entries[n].value;
+		p->epos[pr] = pc;
+		p->row_idx[pc] = r;
+		if (n < s->matched)            /* the matched prefix is (row, col)-sorted: a linear fill */
+			p->mask_col[s->mask_at++] = c;
+	}
+	return NULL;
+}
+
+static void run_slices(prep_slice *sl, int T, void *(*fn)(void *))
+{
+	pthread_t th[MF_PREP_MAX_THREADS];
+	int started[MF_PREP_MAX_THREADS] = {0};
+	for (int t = 1; t < T; t++)
+		started[t] = pthread_create(&th[t], NULL, fn, &sl[t]) == 0;
+	fn(&sl[0]);
+	for (int t = 1; t < T; t++) {
+		if (started[t])
+			pthread_join(th[t], NULL);
+		else
+			fn(&sl[t]);       /* no thread to be had: do the slice here */
+	}
+}
+
+static int prep_threads(int nnz)
+{
+	long cpus = sysconf(_SC_NPROCESSORS_ONLN);
+	int T = nnz / 131072;                 /* a slice is worth a thread from ~10^5 entries */
+	if (T > MF_PREP_MAX_THREADS) T = MF_PREP_MAX_THREADS;
+	if (cpus > 0 && T > cpus) T = (int)cpus;
+	const char *env = getenv("MFGPU_PREP_THREADS");
+	if (env && atoi(env) > 0)
+		T = atoi(env) > MF_PREP_MAX_THREADS ? MF_PREP_MAX_THREADS : atoi(env);
+	return T < 1 ? 1 : T;
+}
+
 int mf_pattern_build(mf_pattern *p, int users, int items, int nnz,
                      const mfgpu_entry *entries, int user_lo, int user_hi)
 {
+	return mf_pattern_build_ws(p, users, items, nnz, entries, user_lo, user_hi, NULL, 0);
+}
+
+int mf_pattern_build_ws(mf_pattern *p, int users, int items, int nnz,
+                        const mfgpu_entry *entries, int user_lo, int user_hi,
+                        void *ws, size_t ws_bytes)
+{
 	memset(p, 0, sizeof *p);
+	p->ws = (char *)ws;
+	p->ws_bytes = ws ? ws_bytes : 0;
 	if (users < 0 || items < 0 || nnz < 0 || user_lo < 0 || user_hi > users || user_lo > user_hi)
 		return MFGPU_EINVAL;
 	if (nnz > 0 && !entries)
@@ -65,6 +192,9 @@ int mf_pattern_build(mf_pattern *p, int users, int items, int nnz,
 	p->user_lo = user_lo;
 	p->user_hi = user_hi;
 
+	const int T = prep_threads(nnz);
+	prep_slice sl[MF_PREP_MAX_THREADS];
+	int *cur = NULL;            /* threads 1..T-1: their per-row / per-column arrays */
 	int *row_count = xcalloc((size_t)users, sizeof *row_count);
 	int *col_count = xcalloc((size_t)items, sizeof *col_count);
 	int *row_slot = xcalloc((size_t)users, sizeof *row_slot);
@@ -72,19 +202,51 @@ int mf_pattern_build(mf_pattern *p, int users, int items, int nnz,
 	int rc = MFGPU_ENOMEM;
 	if (!row_count || !col_count || !row_slot || !col_slot)
 		goto done;
-
+	if (T > 1) {
+		cur = xcalloc((size_t)(T - 1) * ((size_t)users + items), sizeof *cur);
+		if (!cur)
+			goto done;
+	}
+	for (int t = 0; t < T; t++) {
+		sl[t].entries = entries;
+		sl[t].n0 = (int)((long)nnz * t / T);
+		sl[t].n1 = (int)((long)nnz * (t + 1) / T);
+		sl[t].users = users;
+		sl[t].items = items;
+		sl[t].user_lo = user_lo;
+		sl[t].user_hi = user_hi;
+		/* thread 0 counts straight into row_slot / col_slot */
+		sl[t].row_cur = t == 0 ? row_slot : cur + (size_t)(t - 1) * ((size_t)users + items);
+		sl[t].col_cur = t == 0 ? col_slot : sl[t].row_cur + users;
+		sl[t].local = 0;
+		sl[t].bad = 0;
+		sl[t].p = p;
+	}
+	run_slices(sl, T, prep_count);
 	int local = 0;
-	for (int n = 0; n < nnz; n++) {
-		int r = entries[n].row, c = entries[n].col;
-		if (r < 0 || r >= users || c < 0 || c >= items) {
+	for (int t = 0; t < T; t++) {
+		if (sl[t].bad) {
 			rc = MFGPU_EINVAL;
 			goto done;
 		}
-		if (r >= user_lo && r < user_hi) {
-			row_count[r]++;
-			col_count[c]++;
-			local++;
-		}
+		local += sl[t].local;
+	}
+	/* matFact.c:14-22: the entries the cursor of print_output ever matches (mf_mask_prefix) */
+	int matched = nnz;
+	for (int t = T - 1; t >= 0; t--)
+		if (sl[t].first_unsorted < sl[t].n1)
+			matched = sl[t].first_unsorted;
+	for (int i = user_lo; i < user_hi; i++) {
+		int c = 0;
+		for (int t = 0; t < T; t++)
+			c += sl[t].row_cur[i];
+		row_count[i] = c;
+	}
+	for (int j = 0; j < items; j++) {
+		int c = 0;
+		for (int t = 0; t < T; t++)
+			c += sl[t].col_cur[j];
+		col_count[j] = c;
 	}
 	p->nnz = local;
 	for (int i = user_lo; i < user_hi; i++)
@@ -94,8 +256,8 @@ int mf_pattern_build(mf_pattern *p, int users, int items, int nnz,
 		if (col_count[j] > p->max_col_len)
 			p->max_col_len = col_count[j];
 
-	p->row_id = xcalloc((size_t)(user_hi - user_lo), sizeof(int));
-	p->col_id = xcalloc((size_t)items, sizeof(int));
+	p->row_id = palloc(p, (size_t)(user_hi - user_lo), sizeof(int), 0);
+	p->col_id = palloc(p, (size_t)items, sizeof(int), 0);
 	if (!p->row_id || !p->col_id)
 		goto done;
 	p->n_rows = order_by_length_desc(row_count, user_lo, user_hi, p->max_row_len, p->row_id);
@@ -103,58 +265,63 @@ int mf_pattern_build(mf_pattern *p, int users, int items, int nnz,
 	if (p->n_rows < 0 || p->n_cols < 0)
 		goto done;
 
-	p->row_ptr = xcalloc((size_t)p->n_rows + 1, sizeof(int));
-	p->col_ptr = xcalloc((size_t)p->n_cols + 1, sizeof(int));
-	p->col_idx = xcalloc((size_t)local, sizeof(int));
-	p->row_idx = xcalloc((size_t)local, sizeof(int));
-	p->epos = xcalloc((size_t)local, sizeof(int));
-	p->val = xcalloc((size_t)local, sizeof(double));
+	p->row_ptr = palloc(p, (size_t)p->n_rows + 1, sizeof(int), 1);
+	p->col_ptr = palloc(p, (size_t)p->n_cols + 1, sizeof(int), 1);
+	p->col_idx = palloc(p, (size_t)local, sizeof(int), 0);
+	p->row_idx = palloc(p, (size_t)local, sizeof(int), 0);
+	p->epos = palloc(p, (size_t)local, sizeof(int), 0);
+	p->val = palloc(p, (size_t)local, sizeof(double), 0);
 	if (!p->row_ptr || !p->col_ptr || !p->col_idx || !p->row_idx || !p->epos || !p->val)
 		goto done;
+	/* first write position of thread t in row / column x = start of x + what the threads
+	 * before t put there; the scatter then keeps the file order inside every row and column */
 	for (int r = 0; r < p->n_rows; r++) {
-		p->row_ptr[r + 1] = p->row_ptr[r] + row_count[p->row_id[r]];
-		row_slot[p->row_id[r]] = p->row_ptr[r];       /* running write cursor */
+		const int i = p->row_id[r];
+		p->row_ptr[r + 1] = p->row_ptr[r] + row_count[i];
+		int at = p->row_ptr[r];
+		for (int t = 0; t < T; t++) {
+			const int k = sl[t].row_cur[i];
+			sl[t].row_cur[i] = at;
+			at += k;
+		}
 	}
 	for (int c = 0; c < p->n_cols; c++) {
-		p->col_ptr[c + 1] = p->col_ptr[c] + col_count[p->col_id[c]];
-		col_slot[p->col_id[c]] = p->col_ptr[c];
+		const int j = p->col_id[c];
+		p->col_ptr[c + 1] = p->col_ptr[c] + col_count[j];
+		int at = p->col_ptr[c];
+		for (int t = 0; t < T; t++) {
+			const int k = sl[t].col_cur[j];
+			sl[t].col_cur[j] = at;
+			at += k;
+		}
 	}
-	/* one pass in file order keeps the file order inside every row and column */
-	for (int n = 0; n < nnz; n++) {
-		int r = entries[n].row, c = entries[n].col;
-		if (r < user_lo || r >= user_hi)
-			continue;
-		int pr = row_slot[r]++, pc = col_slot[c]++;
-		p->col_idx[pr] = c;
-		p->val[pr] = entries[n].value;
-		p->epos[pr] = pc;
-		p->row_idx[pc] = r;
-	}
-
-	/* rated-item mask, matFact.c:14-22 */
-	p->mask_ptr = xcalloc((size_t)users + 1, sizeof(int));
-	p->first_free = xcalloc((size_t)users, sizeof(int));
+	/* rated-item mask, matFact.c:14-22: per user the items of its matched entries */
+	p->mask_ptr = palloc(p, (size_t)users + 1, sizeof(int), 1);
+	p->first_free = palloc(p, (size_t)users, sizeof(int), 0);
 	if (!p->mask_ptr || !p->first_free)
 		goto done;
-	int matched = mf_mask_prefix(users, items, nnz, entries);
-	for (int n = 0; n < matched; n++) {
-		int r = entries[n].row;
-		if (r >= user_lo && r < user_hi)
-			p->mask_ptr[r + 1]++;
-	}
-	for (int i = 0; i < users; i++)
-		p->mask_ptr[i + 1] += p->mask_ptr[i];
-	p->mask_col = xcalloc((size_t)p->mask_ptr[users], sizeof(int));
-	if (!p->mask_col)
-		goto done;
-	{
-		int w = 0; /* the matched prefix is (row, col)-sorted, so a linear fill is in order */
+	if (matched == nnz) {
+		for (int i = user_lo; i < user_hi; i++)
+			p->mask_ptr[i + 1] = row_count[i];
+	} else {
 		for (int n = 0; n < matched; n++) {
 			int r = entries[n].row;
 			if (r >= user_lo && r < user_hi)
-				p->mask_col[w++] = entries[n].col;
+				p->mask_ptr[r + 1]++;
 		}
 	}
+	for (int i = 0; i < users; i++)
+		p->mask_ptr[i + 1] += p->mask_ptr[i];
+	p->mask_col = palloc(p, (size_t)p->mask_ptr[users], sizeof(int), 0);
+	if (!p->mask_col)
+		goto done;
+	for (int t = 0, at = 0; t < T; t++) {
+		sl[t].matched = matched;
+		sl[t].mask_at = at;             /* local entries before the slice */
+		at += sl[t].local;
+	}
+	run_slices(sl, T, prep_scatter);
+
 	for (int i = 0; i < users; i++) {
 		int f = -1;
 		if (i >= user_lo && i < user_hi) {
@@ -172,6 +339,7 @@ int mf_pattern_build(mf_pattern *p, int users, int items, int nnz,
 	}
 	rc = MFGPU_OK;
 done:
+	free(cur);
 	free(row_count);
 	free(col_count);
 	free(row_slot);
@@ -183,6 +351,10 @@ done:
 
 void mf_pattern_free(mf_pattern *p)
 {
+	if (p->ws) {                 /* the arrays belong to the caller's workspace */
+		memset(p, 0, sizeof *p);
+		return;
+	}
 	free(p->row_id); free(p->row_ptr); free(p->col_idx); free(p->val); free(p->epos);
 	free(p->col_id); free(p->col_ptr); free(p->row_idx);
 	free(p->mask_ptr); free(p->mask_col); free(p->first_free);

@@ -11,6 +11,8 @@
 #ifndef MF_PREP_H
 #define MF_PREP_H
 
+#include <stddef.h>
+
 #include "matfact_b200.h"
 
 #ifdef __cplusplus
@@ -42,6 +44,10 @@ typedef struct {
 	int *first_free;            /* [users]    first item the cursor does not skip, -1 if none */
 
 	int max_row_len, max_col_len;
+
+	/* caller-provided workspace the arrays above live in (mf_pattern_build_ws), else NULL */
+	char *ws;
+	size_t ws_bytes, ws_used;
 } mf_pattern;
 
 /* Build the pattern of the entries whose row lies in [user_lo, user_hi).
@@ -49,6 +55,15 @@ typedef struct {
 int mf_pattern_build(mf_pattern *p, int users, int items, int nnz,
                      const mfgpu_entry *entries, int user_lo, int user_hi);
 void mf_pattern_free(mf_pattern *p);
+
+/* The same with every array of the pattern carved out of the caller's workspace `ws` (e.g.
+ * page-locked memory kept from one plan to the next: no first-touch page faults, and the
+ * upload is a real DMA).  mf_pattern_ws_bytes bounds what a build can need; mf_pattern_free
+ * then leaves the workspace to the caller. */
+size_t mf_pattern_ws_bytes(int users, int items, int nnz, int user_lo, int user_hi);
+int mf_pattern_build_ws(mf_pattern *p, int users, int items, int nnz,
+                        const mfgpu_entry *entries, int user_lo, int user_hi,
+                        void *ws, size_t ws_bytes);
 
 /* Number of leading entries the cursor of print_output (matFact.c:14-22) ever
  * matches: the longest prefix that is strictly increasing in (row, col).  For

@@ -171,3 +171,16 @@ def test_synthetic_shapes():
     key = b.entries["row"].astype(np.int64) * b.items + b.entries["col"]
     assert np.all(np.diff(key) > 0)
     assert set(np.unique(b.entries["value"])) <= {1.0, 2.0, 3.0, 4.0, 5.0}
+
+
+def test_threaded_pattern_build_is_deterministic(tmp_path):
+    """host/mf_prep.c splits its two passes over threads and can build into a caller's workspace:
+    every array must equal the one-thread build, also for unsorted / duplicated entry lists
+    (tests/prep_check.c)."""
+    exe = str(tmp_path / "prep_check")
+    subprocess.run(["gcc", "-O2", "-Wall", "-Wextra", "-I" + os.path.join(ROOT, "include"),
+                    "-I" + os.path.join(ROOT, "recommender_system_b200", "host"), "-o", exe,
+                    os.path.join(ROOT, "tests", "prep_check.c"),
+                    os.path.join(ROOT, "recommender_system_b200", "host", "mf_prep.c"), "-lpthread"], check=True)
+    p = subprocess.run([exe], capture_output=True, text=True)
+    assert p.returncode == 0 and p.stdout.strip().endswith("OK"), p.stdout
