@@ -323,12 +323,17 @@ def main():
     best2 = np.full(U, -2, dtype=np.int32)
 
     def e2e_step():
-        pl = make_plan()
-        pl.set_factors(Lp, Rp)
-        pl.iterate(T)
-        pl.get_factors(Lo, Ro)
-        pl.recommend(best2)
-        pl.close()
+        t = [time.perf_counter()]
+        pl = make_plan(); t.append(time.perf_counter())
+        pl.set_factors(Lp, Rp); t.append(time.perf_counter())
+        pl.iterate(T); t.append(time.perf_counter())
+        pl.get_factors(Lo, Ro); t.append(time.perf_counter())
+        pl.recommend(best2); t.append(time.perf_counter())
+        pl.close(); t.append(time.perf_counter())
+        if os.environ.get("MFGPU_TRACE"):       # host-side view; iterate returns before the device is done
+            names = ["create", "set_factors", "iterate (enqueue)", "get_factors (+wait)", "recommend", "close"]
+            print("[bench rank %d] " % rank + ", ".join("%s %.1f ms" % (n, (b - a) * 1e3)
+                                                        for n, a, b in zip(names, t, t[1:])), file=sys.stderr)
 
     e2e_step()
     barrier()

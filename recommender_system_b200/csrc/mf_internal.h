@@ -84,6 +84,28 @@ int mf_fail(int code, const char *fmt, ...);
 int mf_load_nccl(void);
 int mf_usable_devices(int *ids, int cap);
 int mf_configure_shard(mfgpu_plan *pl, mf_shard *s);      /* mf_plan.cu */
+/* MFGPU_TRACE=1: wall-clock of the host-side phases (plan creation / destruction, graph
+ * builds) on stderr */
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+static inline bool mf_trace_on()
+{
+	static const bool on = getenv("MFGPU_TRACE") != nullptr;
+	return on;
+}
+struct TraceClock {
+	std::chrono::steady_clock::time_point t = std::chrono::steady_clock::now();
+	void lap(const char *what)
+	{
+		if (!mf_trace_on())
+			return;
+		const auto n = std::chrono::steady_clock::now();
+		fprintf(stderr, "[mfgpu] %-28s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(n - t).count());
+		t = n;
+	}
+};
+
 int mf_kernels_prepare(int warps, size_t k1_smem, int res_ng, size_t res_smem);   /* mf_iter.cu: kernels live in that TU only */
 extern mf_nccl_api g_nccl;
 

@@ -319,8 +319,11 @@ extern "C" int mfgpu_plan_iterate(mfgpu_plan *pl, int iters)
 		int left = iters;
 		const int gi = pl->opt_graph_iters;
 		if (pl->opt_graph && left >= gi) {
-			if (!s->gexec[c])
+			if (!s->gexec[c]) {
+				TraceClock tc;
 				TRY(build_graph(pl, s, c, gi));
+				tc.lap("iterate: graph build");
+			}
 			const long long per = launches_per_iteration(pl, s) * gi;
 			for (; left >= gi; left -= gi) {
 				CK(cudaGraphLaunch(s->gexec[c], s->st));

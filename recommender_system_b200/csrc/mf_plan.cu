@@ -20,27 +20,6 @@
 #include <new>
 #include <vector>
 
-/* MFGPU_TRACE=1: wall-clock of the phases of plan creation / destruction on stderr */
-#include <chrono>
-#include <cstdio>
-#include <cstdlib>
-static bool trace_on()
-{
-	static const bool on = getenv("MFGPU_TRACE") != nullptr;
-	return on;
-}
-struct TraceClock {
-	std::chrono::steady_clock::time_point t = std::chrono::steady_clock::now();
-	void lap(const char *what)
-	{
-		if (!trace_on())
-			return;
-		const auto n = std::chrono::steady_clock::now();
-		fprintf(stderr, "[mfgpu] %-28s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(n - t).count());
-		t = n;
-	}
-};
-
 /* Device buffers come from the device's default memory pool in stream order, and the pool keeps
  * what is freed (release threshold = everything): a process that factorizes one matrix after
  * another pays cudaMalloc/cudaFree (milliseconds per 100 MB) once, not per plan.  Buffers that
@@ -448,6 +427,7 @@ static int plan_create(mfgpu_plan **out, int users, int items, int features, int
 	pl->opt_res_rows = 0;
 	pl->opt_chain_ws = 1;
 
+	TraceClock tc;
 	int rc = mf_split_users(users, nnz, entries, nshards, pl->cut);
 	int *item_slot = nullptr, *touched = nullptr;
 	if (rc == MFGPU_OK && nshards > 1) {
@@ -473,6 +453,7 @@ static int plan_create(mfgpu_plan **out, int users, int items, int features, int
 	if (rc != MFGPU_OK)
 		mf_fail(rc, rc == MFGPU_EINVAL ? "an entry lies outside the users x items matrix"
 		                               : "out of host memory");
+	tc.lap("create: user split, items");
 	if (rc == MFGPU_OK) {
 		if (comm) {
 			/* rank mode: this process holds one shard, the users of its rank */
