@@ -282,6 +282,9 @@ __device__ __forceinline__ double chain_bulk(double acc, int lane, const int *__
  * shared by all loads in flight, so waiting for an old block also waits for the newest one.
  * src_g = first of the group's 32 features in row 0 of the gathered factor; gw = number of
  * valid doubles of the group in a row (even, <= 32). */
+/* doubles of one warp's ring: per stage RS gathered rows of 32 features and their RS e_n */
+__host__ __device__ constexpr int ring_doubles(int RS, int NST) { return NST * (RS * 32 + RS); }
+
 template <int RS, int NST>
 __device__ __forceinline__ double chain_ring(double acc, int lane, const int *__restrict__ idx,
                                              const double *__restrict__ ev, int m,
@@ -290,33 +293,33 @@ __device__ __forceinline__ double chain_ring(double acc, int lane, const int *__
 	constexpr int D = NST - 1;            /* stages in flight ahead of the one being added */
 	constexpr int SPB = 32 / RS;          /* stages per index block of 32 nonzeros        */
 	constexpr int NB = (SPB - 1 + D) / SPB + 2;   /* index blocks held in registers       */
+	constexpr int STAGE = RS * 32 + RS;
 	int bi[NB];
-	double be[NB];
-	auto load_blk = [&](int q, int &i_, double &e_) {
-		const int n = min(q * 32 + lane, m - 1);
-		i_ = idx[n];
-		e_ = ev[n];
-	};
+	auto load_blk = [&](int q, int &i_) { i_ = idx[min(q * 32 + lane, m - 1)]; };
 #pragma unroll
 	for (int b = 0; b < NB; b++)
-		load_blk(b, bi[b], be[b]);
+		load_blk(b, bi[b]);
 	const int half = lane >> 4, piece = lane & 15;
 	const bool piece_ok = 2 * piece < gw;
-	auto issue = [&](int slot, int blk_i, int lane0) {
-		/* rows lane0 .. lane0+RS-1 of the index block whose indices are in blk_i */
+	auto issue = [&](int slot, int blk_i, int lane0, int s) {
+		/* stage s = rows lane0 .. lane0+RS-1 of the index block whose indices are in blk_i.
+		 * The e_n travel with the rows (8-byte copies) and are read back as 16-byte
+		 * broadcasts: a shuffle per row costs the shared-memory pipe as much as a row. */
+		double *st = ring + (size_t)slot * STAGE;
 #pragma unroll
 		for (int u = 0; u < RS / 2; u++) {
 			const int i = __shfl_sync(FULL, blk_i, lane0 + 2 * u + half);
 			if (piece_ok)
-				cp_async16(ring + (size_t)(slot * RS + 2 * u + half) * 32 + 2 * piece,
-				           src_g + (size_t)i * ld + 2 * piece);
+				cp_async16(st + (2 * u + half) * 32 + 2 * piece, src_g + (size_t)i * ld + 2 * piece);
 		}
+		if (lane < RS && s * RS + lane < m)
+			cp_async8(st + RS * 32 + lane, ev + s * RS + lane);
 	};
 	/* prologue: stages 0 .. D-1 */
 #pragma unroll
 	for (int t = 0; t < D; t++) {
 		if (t * RS < m)
-			issue(t % NST, bi[t / SPB], (t % SPB) * RS);
+			issue(t % NST, bi[t / SPB], (t % SPB) * RS, t);
 		cp_async_commit();
 	}
 	int slot = 0;                          /* ring slot of the stage being added */
@@ -325,33 +328,33 @@ __device__ __forceinline__ double chain_ring(double acc, int lane, const int *__
 		for (int j = 0; j < SPB; j++) {
 			const int s = q * SPB + j;
 			if ((s + D) * RS < m)
-				issue(slot == 0 ? NST - 1 : slot - 1, bi[(j + D) / SPB], ((j + D) % SPB) * RS);
+				issue(slot == 0 ? NST - 1 : slot - 1, bi[(j + D) / SPB], ((j + D) % SPB) * RS, s + D);
 			cp_async_commit();
 			cp_async_wait<D>();            /* stage s has landed */
 			__syncwarp();
 			const int rows = m - s * RS;
-			const double *x = ring + (size_t)slot * RS * 32 + lane;
+			const double *st = ring + (size_t)slot * STAGE;
+			const double *x = st + lane;
 			if (rows >= RS) {
 #pragma unroll
-				for (int r = 0; r < RS; r++)
-					acc = __dadd_rn(acc, __dmul_rn(__shfl_sync(FULL, be[0], j * RS + r), x[r * 32]));
+				for (int r = 0; r < RS; r += 2) {
+					const double2 e2 = ld2(st + RS * 32 + r);
+					acc = __dadd_rn(acc, __dmul_rn(e2.x, x[r * 32]));
+					acc = __dadd_rn(acc, __dmul_rn(e2.y, x[(r + 1) * 32]));
+				}
 			} else if (rows > 0) {
 #pragma unroll
-				for (int r = 0; r < RS; r++) {
-					const double e = __shfl_sync(FULL, be[0], j * RS + r);
+				for (int r = 0; r < RS; r++)
 					if (r < rows)
-						acc = __dadd_rn(acc, __dmul_rn(e, x[r * 32]));
-				}
+						acc = __dadd_rn(acc, __dmul_rn(st[RS * 32 + r], x[r * 32]));
 			}
 			__syncwarp();                  /* the slot is refilled by the next issue */
 			slot = (slot + 1 == NST) ? 0 : slot + 1;
 		}
 #pragma unroll
-		for (int b = 0; b + 1 < NB; b++) {
+		for (int b = 0; b + 1 < NB; b++)
 			bi[b] = bi[b + 1];
-			be[b] = be[b + 1];
-		}
-		load_blk(q + NB, bi[NB - 1], be[NB - 1]);
+		load_blk(q + NB, bi[NB - 1]);
 	}
 	cp_async_wait<0>();
 	return acc;
@@ -773,7 +776,7 @@ k_dot(const LoopArgs p, const double *__restrict__ Lold, const double *__restric
  *                             init = R_old, src = L_old, idx = users of the column
  */
 constexpr int CHAIN_BULK_REGS = 0, CHAIN_DEEP_REGS = 1, CHAIN_BULK_RING = 2, CHAIN_DEEP_RING = 3;
-constexpr int RING_BULK_ROWS = 8, RING_BULK_STAGES = 3;     /* 6 KB per warp  */
+constexpr int RING_BULK_ROWS = 8, RING_BULK_STAGES = 3;     /* 6.2 KB per warp  */
 constexpr int RING_DEEP_ROWS = 16, RING_DEEP_STAGES = 6;    /* 24 KB per warp */
 
 template <int WARPS, int MODE>
@@ -802,11 +805,11 @@ k_chain(const ChainSide A, const ChainSide B, long warps_a, int F, int ld)
 		if (MODE == CHAIN_DEEP_RING)
 			acc = chain_ring<RING_DEEP_ROWS, RING_DEEP_STAGES>(
 			    acc, lane, sd.idx + b, sd.e + b, m, src_g, ld, gw,
-			    smem + (size_t)warp * RING_DEEP_ROWS * RING_DEEP_STAGES * 32);
+			    smem + (size_t)warp * ring_doubles(RING_DEEP_ROWS, RING_DEEP_STAGES));
 		else
 			acc = chain_ring<RING_BULK_ROWS, RING_BULK_STAGES>(
 			    acc, lane, sd.idx + b, sd.e + b, m, src_g, ld, gw,
-			    smem + (size_t)warp * RING_BULK_ROWS * RING_BULK_STAGES * 32);
+			    smem + (size_t)warp * ring_doubles(RING_BULK_ROWS, RING_BULK_STAGES));
 	} else {
 		const double *srck = sd.src + (active ? k : 0) - (size_t)sd.src_off * ld;   /* idle lanes: a valid column */
 		if (MODE == CHAIN_DEEP_REGS)
