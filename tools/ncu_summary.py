@@ -31,7 +31,7 @@ METRICS = [
     "l1tex__throughput.avg.pct_of_peak_sustained_elapsed",
     "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum.pct_of_peak_sustained_elapsed",
     "lts__throughput.avg.pct_of_peak_sustained_elapsed",
-    "dram__throughput.avg.pct_of_peak_sustained_elapsed",
+    "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
     "dram__bytes_read.sum",
     "dram__bytes_write.sum",
     "lts__t_sectors_srcunit_tex_op_read.sum",
@@ -123,7 +123,7 @@ def main():
             avg(ls, "l1tex__throughput.avg.pct_of_peak_sustained_elapsed"),
             avg(ls, "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum.pct_of_peak_sustained_elapsed"),
             avg(ls, "lts__throughput.avg.pct_of_peak_sustained_elapsed"),
-            avg(ls, "dram__throughput.avg.pct_of_peak_sustained_elapsed"),
+            avg(ls, "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed"),
             dram / 1e6, l2rd / 1e6, avg(ls, "lts__t_sector_hit_rate.pct")))
         st = sorted(((avg(ls, STALLS.format(n)), n) for n in STALL_NAMES if avg(ls, STALLS.format(n)) == avg(ls, STALLS.format(n))),
                     reverse=True)[:4]
