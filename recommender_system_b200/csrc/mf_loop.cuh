@@ -130,9 +130,9 @@ __device__ __forceinline__ void row_update(const double *init, double *Lout,
 		for (int g = 0; g < NG; g++)
 			x[g] = row[off[g]];
 	}
-	for (int n = 0; n < cnt; n++) {
+	for (int n = 0; n + 1 < cnt; n++) {
 		const double e = es[n];
-		const double *row = Rold + (size_t)__shfl_sync(FULL, j, min(n + 1, cnt - 1)) * ld;
+		const double *row = Rold + (size_t)__shfl_sync(FULL, j, n + 1) * ld;
 #pragma unroll
 		for (int g = 0; g < NG; g++)
 			xn[g] = row[off[g]];
@@ -141,6 +141,12 @@ __device__ __forceinline__ void row_update(const double *init, double *Lout,
 			acc[g] = __dadd_rn(acc[g], __dmul_rn(e, x[g]));
 			x[g] = xn[g];
 		}
+	}
+	{
+		const double e = es[cnt - 1];      /* the last nonzero: nothing left to fetch */
+#pragma unroll
+		for (int g = 0; g < NG; g++)
+			acc[g] = __dadd_rn(acc[g], __dmul_rn(e, x[g]));
 	}
 #pragma unroll
 	for (int g = 0; g < NG; g++)

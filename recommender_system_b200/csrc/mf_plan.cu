@@ -329,7 +329,9 @@ static int shard_create(mfgpu_plan *pl, mf_shard *s, int dev, const mfgpu_entry 
 	/* arg-max scratch */
 	const int tiles_y = (int)((nu + mf::AM_TI - 1) / mf::AM_TI);
 	const int n_tiles = (pl->items + mf::AM_TJ - 1) / mf::AM_TJ;
-	int splits = tiles_y > 0 ? (148 * 4 + tiles_y - 1) / tiles_y : 1;
+	/* two CTAs are resident per SM (registers): aim at eight waves of them, so that the last,
+	 * partly filled wave is a small part of the launch (three waves left 20 % of the SMs idle) */
+	int splits = tiles_y > 0 ? (148 * 2 * 8 + tiles_y - 1) / tiles_y : 1;
 	splits = std::max(1, std::min(splits, std::max(1, n_tiles)));
 	s->am_splits = splits;
 	TRY(dev_alloc((void **)&s->part_v, (nu * splits + 1) * sizeof(double), s->st));
