@@ -272,6 +272,7 @@ def main():
 
     # ---- device-resident leg: `value` -------------------------------------------------
     plan = make_plan()
+    xkind = plan.exchange_kind()
     plan.set_factors(Lp, Rp)
     plan.save_factors()
     for _ in range(args.warmup):
@@ -367,8 +368,9 @@ def main():
             "data": "synthetic" if args.workload != "ml100k" else "reference sample file",
             "config": {"workload": desc, "iters": T, "nnz": inst.nnz, "alpha": inst.alpha,
                        "sharding": "users" if n_gpus > 1 else "none",
-                       "exchange": ("nccl allreduce of the R gradient" if comm else
-                                    "peer-memory reduce in shard order") if n_gpus > 1 else "none",
+                       "exchange": {0: "none", 1: "nccl allreduce of the R gradient + apply",
+                                    2: "fused reduce+apply kernel over NVLink peer memory (CUDA IPC), rank order",
+                                    3: "fused reduce+apply kernel over NVLink peer memory, shard order"}[xkind],
                        "l2": "factor buffers %.0f MB vs 126 MB L2; no flush (the loop re-reads "
                              "its own output by construction)" % (32e-6 * F * (U + I))},
             "roofline": roofline, "cpu_baseline": cpu,

@@ -113,6 +113,11 @@ int mfgpu_plan_last_recommend_ms(mfgpu_plan *plan, float *ms);
 int mfgpu_plan_user_range(mfgpu_plan *plan, int shard, int *lo, int *hi);
 /* Kernel launches issued by this plan so far (for bench.py's gpu_launches). */
 long long mfgpu_plan_launch_count(mfgpu_plan *plan);
+/* How the partial R gradients of the shards meet: 0 = one shard, nothing to exchange;
+ * 1 = ncclAllReduce + apply (one process per GPU); 2 = one kernel that reads every rank's
+ * gradient over NVLink peer memory (CUDA IPC) and applies the sum (one process per GPU);
+ * 3 = the same inside one process driving N GPUs. */
+int mfgpu_plan_exchange_kind(mfgpu_plan *plan);
 /* Algorithmic bytes of ONE iteration, SURVEY.md section 8(d):
  * 16*F*(U_t + I_t) + 12*nnz, with U_t / I_t the users / items having >=1 nonzero. */
 long long mfgpu_plan_bytes_per_iter(mfgpu_plan *plan);

@@ -28,7 +28,7 @@ EXPORTS = [
     "mfgpu_plan_create", "mfgpu_plan_create_rank", "mfgpu_plan_destroy",
     "mfgpu_plan_set_factors", "mfgpu_plan_get_factors", "mfgpu_plan_iterate", "mfgpu_plan_sync",
     "mfgpu_plan_last_loop_ms", "mfgpu_plan_recommend", "mfgpu_plan_last_recommend_ms",
-    "mfgpu_plan_user_range", "mfgpu_plan_launch_count", "mfgpu_plan_bytes_per_iter",
+    "mfgpu_plan_user_range", "mfgpu_plan_launch_count", "mfgpu_plan_exchange_kind", "mfgpu_plan_bytes_per_iter",
     "mfgpu_plan_set_option", "mfgpu_plan_save_factors", "mfgpu_plan_restore_factors",
     "mfgpu_plan_profile_kernels", "mfgpu_plan_kernel_bytes", "mfgpu_plan_timer_start", "mfgpu_plan_timer_stop",
     "mfgpu_comm_unique_id", "mfgpu_comm_create", "mfgpu_comm_destroy",
@@ -78,6 +78,8 @@ def lib():
     L.mfgpu_plan_user_range.argtypes = [vp, i, ctypes.POINTER(i), ctypes.POINTER(i)]
     L.mfgpu_plan_launch_count.argtypes = [vp]
     L.mfgpu_plan_launch_count.restype = ctypes.c_longlong
+    L.mfgpu_plan_exchange_kind.argtypes = [vp]
+    L.mfgpu_plan_exchange_kind.restype = ctypes.c_int
     L.mfgpu_plan_bytes_per_iter.argtypes = [vp]
     L.mfgpu_plan_bytes_per_iter.restype = ctypes.c_longlong
     L.mfgpu_plan_set_option.argtypes = [vp, cp, i]
@@ -264,6 +266,10 @@ class Plan:
 
     def launch_count(self) -> int:
         return lib().mfgpu_plan_launch_count(self._h)
+
+    def exchange_kind(self):
+        """0 none, 1 NCCL all-reduce, 2 peer memory across processes, 3 peer memory in one process."""
+        return lib().mfgpu_plan_exchange_kind(self._h)
 
     def bytes_per_iter(self) -> int:
         return lib().mfgpu_plan_bytes_per_iter(self._h)

@@ -75,8 +75,16 @@ struct mfgpu_plan {
 	int have_factors;
 	long long launches;
 	float loop_ms, rec_ms;
+	/* rank mode over peer memory (mf_xchg_setup): every rank maps the G buffers and the flag
+	 * block of every other rank (CUDA IPC) and reduces + applies in one kernel */
+	int xchg_ipc;                                  /* 1: peer-memory exchange, 0: ncclAllReduce */
+	double *peer_G[2][MF_MAX_SHARDS];              /* G[b] of rank h (own rank: the local buffer) */
+	unsigned long long *peer_sync[MF_MAX_SHARDS];  /* sync block of rank h: done[2], consumed[2]  */
+	unsigned long long *d_sync;                    /* own sync block                              */
+	void *ipc_mapped[3 * MF_MAX_SHARDS];
+	int n_ipc_mapped;
 	/* options */
-	int opt_graph, opt_graph_iters, opt_long_row, opt_long_col, opt_ch, opt_chain_ring, opt_resident, opt_res_rows, opt_chain_ws;
+	int opt_graph, opt_graph_iters, opt_long_row, opt_long_col, opt_ch, opt_chain_ring, opt_resident, opt_res_rows, opt_chain_ws, opt_exchange;
 };
 
 /* ---- shared helpers (defined in mf_capi.cu) ----------------------------------- */
@@ -84,6 +92,8 @@ int mf_fail(int code, const char *fmt, ...);
 int mf_load_nccl(void);
 int mf_usable_devices(int *ids, int cap);
 int mf_configure_shard(mfgpu_plan *pl, mf_shard *s);      /* mf_plan.cu */
+int mf_xchg_setup(mfgpu_plan *pl);                          /* mf_plan.cu: collective over the ranks */
+void mf_xchg_teardown(mfgpu_plan *pl);
 /* MFGPU_TRACE=1: wall-clock of the host-side phases (plan creation / destruction, graph
  * builds) on stderr */
 #include <chrono>

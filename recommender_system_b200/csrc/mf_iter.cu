@@ -49,6 +49,69 @@ k_apply_R_peer(int n_touched, int F, int ld, const int *__restrict__ touched_ite
 	Rnew[o] = __dadd_rn(Rold[o], sum);
 }
 
+/* ---- rank mode over peer memory: the same reduce + apply, synchronised by flags ----------
+ * Sync block of a rank (unsigned long long[8], mapped by every other rank):
+ *   done[b]      how many times the rank has finished writing its G[b]
+ *   consumed[b]  how many times the rank has reduced the G[b] of everybody (local use)
+ * k_xchg_signal runs after the kernels that write G[b]; k_apply_R_xchg waits until every
+ * rank's done[b] has reached consumed[b] + 1, then reads all G[b] over NVLink and adds them
+ * in rank order (bit-identical on every rank, and to the oracle's N-shard order); its last
+ * CTA closes the round (consumed[b] += 1).  G[b] is rewritten two iterations later, after this
+ * rank has seen done[1-b] of the next iteration from everybody, which they signal only
+ * after their own reduce of G[b] -- nobody can still be reading it. */
+struct PeerSync {
+	const unsigned long long *sync[MF_MAX_SHARDS];
+	int n;
+};
+
+__global__ void k_xchg_signal(unsigned long long *done)
+{
+	__threadfence_system();              /* G[b], written by the kernels before this one */
+	*(volatile unsigned long long *)done = *done + 1;
+	__threadfence_system();
+}
+
+__global__ void __launch_bounds__(256)
+k_apply_R_xchg(int n_touched, int F, int ld, const int *__restrict__ touched_item,
+               const double *__restrict__ Rold, const PeerG pg, const PeerSync ps, int b,
+               unsigned long long *sync_own, double *__restrict__ Rnew)
+{
+	/* sync_own: done[0..1], consumed[2..3], CTAs finished [4] */
+	__shared__ bool last_cta;
+	if (threadIdx.x < ps.n) {
+		const unsigned long long want = sync_own[2 + b] + 1;
+		const volatile unsigned long long *done = ps.sync[threadIdx.x] + b;
+		unsigned spins = 0;
+		while (*done < want)
+			if (++spins > (1u << 24))    /* a rank that never arrives: fail instead of hanging */
+				__trap();
+		__threadfence_system();
+	}
+	__syncthreads();
+	const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
+	const long total = (long)n_touched * F;
+	if (t < total) {
+		const int s = (int)(t / F), k = (int)(t % F);
+		const size_t gi = (size_t)s * ld + k;
+		double sum = __ldcv(pg.g[0] + gi);
+		for (int h = 1; h < pg.n; h++)
+			sum = __dadd_rn(sum, __ldcv(pg.g[h] + gi));
+		const size_t o = (size_t)touched_item[s] * ld + k;
+		Rnew[o] = __dadd_rn(Rold[o], sum);
+	}
+	/* the last CTA to get here closes the round: every CTA has read consumed[b] by then */
+	__syncthreads();
+	if (threadIdx.x == 0) {
+		__threadfence();
+		last_cta = atomicAdd(sync_own + 4, 1ull) == (unsigned long long)gridDim.x - 1;
+	}
+	__syncthreads();
+	if (last_cta && threadIdx.x == 0) {
+		sync_own[4] = 0;
+		sync_own[2 + b] = sync_own[2 + b] + 1;
+	}
+}
+
 } // namespace mf
 
 template <int NG>
@@ -210,15 +273,37 @@ static int enqueue_loop_kernels(mfgpu_plan *pl, mf_shard *s, int c, double *rout
 }
 
 /* one iteration of a 1-shard plan, or of one rank in rank mode */
+/* rank mode over peer memory: signal G[b], reduce everybody's G[b] and apply, close the round */
+static int enqueue_xchg(mfgpu_plan *pl, mf_shard *s, int c, int b)
+{
+	mf::PeerG pg;
+	mf::PeerSync ps;
+	pg.n = ps.n = pl->comm->nranks;
+	for (int h = 0; h < pg.n; h++) {
+		pg.g[h] = pl->peer_G[b][h];
+		ps.sync[h] = pl->peer_sync[h];
+	}
+	const long total = (long)pl->n_touched * pl->F;
+	mf::k_xchg_signal<<<1, 1, 0, s->st>>>(pl->d_sync + b);
+	mf::k_apply_R_xchg<<<(unsigned)((total + 255) / 256), 256, 0, s->st>>>(
+	    pl->n_touched, pl->F, pl->ld, s->d_touched_item, s->R[c], pg, ps, b, pl->d_sync, s->R[1 - c]);
+	CK(cudaGetLastError());
+	pl->launches += 2;
+	return MFGPU_OK;
+}
+
 static int enqueue_iteration(mfgpu_plan *pl, mf_shard *s, int c)
 {
 	if (pl->nshards == 1)
 		return enqueue_loop_kernels(pl, s, c, s->R[1 - c]);
-	/* rank mode */
-	TRY(enqueue_loop_kernels(pl, s, c, s->G[0]));
+	/* rank mode: the gradient goes to G[c] for the peer-memory exchange (double buffered,
+	 * see k_apply_R_xchg), to G[0] for NCCL */
+	TRY(enqueue_loop_kernels(pl, s, c, pl->xchg_ipc ? s->G[c] : s->G[0]));
 	const size_t count = (size_t)pl->n_touched * pl->ld;
 	if (count == 0)
 		return MFGPU_OK;
+	if (pl->xchg_ipc)
+		return enqueue_xchg(pl, s, c, c);
 	/* out of place: the columns this rank never writes must stay 0.0 in G[0] */
 	NCK(g_nccl.AllReduce(s->G[0], s->G[1], count, /*ncclDouble*/ 8, /*ncclSum*/ 0, pl->comm->nccl, s->st));
 	const long total = (long)pl->n_touched * pl->F;
@@ -292,7 +377,7 @@ static long long launches_per_iteration(const mfgpu_plan *pl, const mf_shard *s)
 	n += (a.n_long - a.n_deep_rows > 0 || a.n_cols - a.n_deep_cols > 0);
 	n += (a.n_deep_rows > 0 || a.n_deep_cols > 0);
 	if (pl->nshards > 1 && (long)pl->n_touched * pl->F > 0)
-		n += 1;
+		n += pl->xchg_ipc ? 2 : 1;
 	return n;
 }
 
@@ -376,6 +461,13 @@ extern "C" int mfgpu_plan_profile_kernels(mfgpu_plan *pl, int reps, float ms[5])
 	const long long before = pl->launches;
 	CK(cudaSetDevice(s->dev));
 	double *rout = pl->nshards == 1 ? s->R[1 - c] : s->G[0];
+	if (pl->xchg_ipc) {
+		/* the launches below write G[0] outside the exchange protocol: wait until no peer
+		 * can still be reducing it (a one-word all-reduce after everybody's last iteration) */
+		CK(cudaStreamSynchronize(s->st));
+		NCK(g_nccl.AllReduce((int *)pl->d_sync + 14, (int *)pl->d_sync + 14, 1, 2, 0, pl->comm->nccl, s->st));
+		CK(cudaStreamSynchronize(s->st));
+	}
 	for (int phase = 0; phase < 5; phase++) {
 		if (phase == 4 && !(pl->comm && (size_t)pl->n_touched * pl->ld > 0))
 			break;
@@ -389,7 +481,9 @@ extern "C" int mfgpu_plan_profile_kernels(mfgpu_plan *pl, int reps, float ms[5])
 				TRY(launch_chain(pl, s, c, rout, false, s->st));
 			else if (phase == 3)
 				TRY(launch_chain(pl, s, c, rout, true, s->st));
-			else {
+			else if (pl->xchg_ipc) {
+				TRY(enqueue_xchg(pl, s, c, 0));
+			} else {
 				NCK(g_nccl.AllReduce(s->G[0], s->G[1], (size_t)pl->n_touched * pl->ld, 8, 0,
 				                     pl->comm->nccl, s->st));
 				const long total = (long)pl->n_touched * pl->F;

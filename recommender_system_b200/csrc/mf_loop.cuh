@@ -11,19 +11,25 @@
  * in file order of that column's nonzeros.  The kernels keep exactly that
  * order, so one GPU reproduces the reference's doubles bit for bit:
  *
- *   k_update_L  short user rows, one warp per row: the R rows of up to CH of its nonzeros
- *               stream through shared-memory tiles (16-byte cp.async) while e_n is computed
- *               with one lane per nonzero walking k sequentially (the dot of
- *               mat2d.c:133-137); then L_new[i][k] is accumulated with lanes over features
- *               walking the nonzeros in order.  Writes e_n at its by-item position.
- *   k_dot       the same dot phase for the long rows, one warp per chunk of <= 32 nonzeros,
- *               so a row of thousands of nonzeros is spread over many warps.
- *   k_chain     the sequential accumulations that remain: L rows of the long users and all
- *               R rows.  One warp per (row or column, 32 features) walks the nonzeros in
- *               file order with the gathered operands running ahead in registers (a deep
- *               variant for the few longest chains, a light one for the bulk).
- *   k_apply_R   N shards only: R_new = R_old + G (G = sum of the partial
- *               gradients, the MPI_Iallreduce of matFact-mpi.c:208).
+ *   k_update_L      short user rows, one warp per row: the R rows of up to CH of its nonzeros
+ *                   stream through shared-memory tiles (16-byte cp.async) while e_n is computed
+ *                   with one lane per nonzero walking k sequentially (the dot of
+ *                   mat2d.c:133-137); then L_new[i][k] is accumulated with lanes over features
+ *                   walking the nonzeros in order.  Writes e_n at its by-item position.
+ *   k_update_L_res  the same pass with the gathered rows resident in shared memory for both
+ *                   phases (one L2 gather per nonzero instead of two); chosen when eight
+ *                   warps' rows fit an SM.
+ *   k_dot           the dot phase alone for the long rows, one warp per chunk of <= 32
+ *                   nonzeros, so a row of thousands of nonzeros is spread over many warps.
+ *   k_chain         the sequential accumulations that remain: L rows of the long users and all
+ *                   R rows.  One warp per (row or column, 32 features) walks the nonzeros in
+ *                   file order with the gathered operands running ahead in a shared-memory
+ *                   ring (or in registers).
+ *   k_chain_ws      the same for the few longest chains, one CTA of specialised warps per
+ *                   chain: producers gather into a ring with cp.async + mbarriers, one
+ *                   consumer warp does nothing but the ordered additions.
+ *   k_apply_R       N shards only: R_new = R_old + G (G = sum of the partial
+ *                   gradients, the MPI_Iallreduce of matFact-mpi.c:208).
  *
  * The snapshot copies (mat2d_copy, matFact.c:38-39) do not exist: L and R are
  * double buffered, every touched row is rewritten each iteration and untouched
@@ -34,9 +40,6 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
-#ifdef MF_WS_DEBUG
-#include <cstdio>
-#endif
 #include "mf_types.h"
 #include "mf_async.cuh"
 

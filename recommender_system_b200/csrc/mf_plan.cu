@@ -388,6 +388,122 @@ static void shard_destroy(mf_shard *s)
 	cudaGetLastError();
 }
 
+/* ---- rank mode: exchange over peer memory ---------------------------------------------------
+ * Collective over the ranks of the communicator.  Every rank publishes CUDA IPC handles of its
+ * two G buffers and of a small flag block, and maps those of the others; the handles travel
+ * through one ncclAllGather.  If any rank cannot export or map (no peer access, IPC disabled),
+ * all ranks fall back to ncclAllReduce together. */
+struct XchgHandles {
+	cudaIpcMemHandle_t g[2], sync;
+	int ok, pad[15];
+};
+
+static bool xchg_all_ok(mfgpu_plan *pl, mf_shard *s, int mine, int *d_scratch)
+{
+	/* logical AND over the ranks: sum of (1 - ok) must be 0 */
+	int bad = mine ? 0 : 1, total = 1;
+	if (cudaMemcpyAsync(d_scratch, &bad, sizeof bad, cudaMemcpyHostToDevice, s->st) != cudaSuccess)
+		return false;
+	if (g_nccl.AllReduce(d_scratch, d_scratch, 1, /*ncclInt32*/ 2, /*ncclSum*/ 0, pl->comm->nccl, s->st) != 0)
+		return false;
+	if (cudaMemcpyAsync(&total, d_scratch, sizeof total, cudaMemcpyDeviceToHost, s->st) != cudaSuccess)
+		return false;
+	if (cudaStreamSynchronize(s->st) != cudaSuccess)
+		return false;
+	return total == 0;
+}
+
+int mf_xchg_setup(mfgpu_plan *pl)
+{
+	pl->xchg_ipc = 0;
+	if (!pl->comm || pl->nshards < 2 || (size_t)pl->n_touched * pl->ld == 0 || pl->opt_exchange == 0)
+		return MFGPU_OK;
+	mf_shard *s = &pl->sh[0];
+	const int n = pl->comm->nranks, me = pl->comm->rank;
+	CK(cudaSetDevice(s->dev));
+	CK(cudaMalloc((void **)&pl->d_sync, 64));
+	CK(cudaMemsetAsync(pl->d_sync, 0, 64, s->st));
+
+	XchgHandles mine;
+	memset(&mine, 0, sizeof mine);
+	mine.ok = cudaIpcGetMemHandle(&mine.g[0], s->G[0]) == cudaSuccess &&
+	          cudaIpcGetMemHandle(&mine.g[1], s->G[1]) == cudaSuccess &&
+	          cudaIpcGetMemHandle(&mine.sync, pl->d_sync) == cudaSuccess;
+	cudaGetLastError();
+
+	XchgHandles *d_all = nullptr;
+	std::vector<XchgHandles> all((size_t)n);
+	CK(cudaMalloc((void **)&d_all, sizeof(XchgHandles) * (size_t)(n + 1)));
+	CK(cudaMemcpyAsync(d_all + n, &mine, sizeof mine, cudaMemcpyHostToDevice, s->st));
+	NCK(g_nccl.AllGather(d_all + n, d_all, sizeof(XchgHandles), /*ncclInt8*/ 0, pl->comm->nccl, s->st));
+	CK(cudaMemcpyAsync(all.data(), d_all, sizeof(XchgHandles) * (size_t)n, cudaMemcpyDeviceToHost, s->st));
+	CK(cudaStreamSynchronize(s->st));
+
+	int ok = 1;
+	for (int h = 0; h < n; h++)
+		ok &= all[h].ok;
+	pl->n_ipc_mapped = 0;
+	for (int h = 0; h < n && ok; h++) {
+		if (h == me) {
+			pl->peer_G[0][h] = s->G[0];
+			pl->peer_G[1][h] = s->G[1];
+			pl->peer_sync[h] = pl->d_sync;
+			continue;
+		}
+		void *q[3] = {nullptr, nullptr, nullptr};
+		const cudaIpcMemHandle_t *hd[3] = {&all[h].g[0], &all[h].g[1], &all[h].sync};
+		for (int k = 0; k < 3 && ok; k++) {
+			if (cudaIpcOpenMemHandle(&q[k], *hd[k], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+				cudaGetLastError();
+				ok = 0;
+			} else {
+				pl->ipc_mapped[pl->n_ipc_mapped++] = q[k];
+			}
+		}
+		pl->peer_G[0][h] = (double *)q[0];
+		pl->peer_G[1][h] = (double *)q[1];
+		pl->peer_sync[h] = (unsigned long long *)q[2];
+	}
+	/* everybody, or nobody */
+	const bool all_ok = xchg_all_ok(pl, s, ok, (int *)d_all);
+	cudaFree(d_all);
+	if (!all_ok) {
+		for (int k = 0; k < pl->n_ipc_mapped; k++)
+			cudaIpcCloseMemHandle(pl->ipc_mapped[k]);
+		pl->n_ipc_mapped = 0;
+		cudaGetLastError();
+		if (pl->opt_exchange == 1 && getenv("MFGPU_TRACE"))
+			fprintf(stderr, "[mfgpu] peer-memory exchange unavailable, using ncclAllReduce\n");
+		return MFGPU_OK;
+	}
+	pl->xchg_ipc = 1;
+	return MFGPU_OK;
+}
+
+/* Collective: nobody may unmap or free while a peer's kernels can still read its G. */
+void mf_xchg_teardown(mfgpu_plan *pl)
+{
+	if (!pl->comm || !pl->d_sync)
+		return;
+	mf_shard *s = &pl->sh[0];
+	if (s->dev >= 0)
+		cudaSetDevice(s->dev);
+	if (pl->xchg_ipc && s->st) {
+		cudaStreamSynchronize(s->st);
+		if (s->st2) cudaStreamSynchronize(s->st2);
+		/* a one-word all-reduce as the barrier: a peer joins it only after its kernels */
+		if (g_nccl.AllReduce((int *)pl->d_sync + 14, (int *)pl->d_sync + 14, 1, 2, 0, pl->comm->nccl, s->st) == 0)
+			cudaStreamSynchronize(s->st);
+	}
+	for (int k = 0; k < pl->n_ipc_mapped; k++)
+		cudaIpcCloseMemHandle(pl->ipc_mapped[k]);
+	pl->n_ipc_mapped = 0;
+	cudaFree(pl->d_sync);
+	pl->d_sync = nullptr;
+	pl->xchg_ipc = 0;
+	cudaGetLastError();
+}
+
 static int plan_create(mfgpu_plan **out, int users, int items, int features, int nnz,
                        const mfgpu_entry *entries, double alpha, int ngpus, mfgpu_comm *comm)
 {
@@ -428,6 +544,7 @@ static int plan_create(mfgpu_plan **out, int users, int items, int features, int
 	pl->opt_resident = 1;
 	pl->opt_res_rows = 0;
 	pl->opt_chain_ws = 1;
+	pl->opt_exchange = -1;       /* peer memory when it can be had */
 
 	TraceClock tc;
 	int rc = mf_split_users(users, nnz, entries, nshards, pl->cut);
@@ -462,6 +579,8 @@ static int plan_create(mfgpu_plan **out, int users, int items, int features, int
 			pl->sh[0].user_lo = pl->cut[comm->rank];
 			pl->sh[0].user_hi = pl->cut[comm->rank + 1];
 			rc = shard_create(pl, &pl->sh[0], comm->device, entries, item_slot, touched);
+			if (rc == MFGPU_OK)
+				rc = mf_xchg_setup(pl);
 		} else {
 			for (int g = 0; g < nshards && rc == MFGPU_OK; g++) {
 				pl->sh[g].user_lo = pl->cut[g];
@@ -520,6 +639,7 @@ extern "C" void mfgpu_plan_destroy(mfgpu_plan *pl)
 	if (!pl)
 		return;
 	const int n = pl->comm ? 1 : pl->nshards;
+	mf_xchg_teardown(pl);            /* rank mode: collective, see there */
 	for (int g = 0; g < n; g++)
 		if (pl->sh[g].dev >= 0)
 			shard_destroy(&pl->sh[g]);
@@ -594,6 +714,15 @@ extern "C" int mfgpu_plan_user_range(mfgpu_plan *pl, int shard, int *lo, int *hi
 
 extern "C" long long mfgpu_plan_launch_count(mfgpu_plan *pl) { return pl ? pl->launches : 0; }
 
+extern "C" int mfgpu_plan_exchange_kind(mfgpu_plan *pl)
+{
+	if (!pl || pl->nshards < 2)
+		return 0;
+	if (!pl->comm)
+		return 3;
+	return pl->xchg_ipc ? 2 : 1;
+}
+
 extern "C" long long mfgpu_plan_bytes_per_iter(mfgpu_plan *pl)
 {
 	if (!pl)
@@ -629,6 +758,12 @@ extern "C" int mfgpu_plan_set_option(mfgpu_plan *pl, const char *name, int value
 	else if (!strcmp(name, "resident")) pl->opt_resident = value;
 	else if (!strcmp(name, "res_rows")) pl->opt_res_rows = value;
 	else if (!strcmp(name, "chain_ws")) pl->opt_chain_ws = value;
+	else if (!strcmp(name, "exchange")) {
+		/* rank mode, collective: 0 = ncclAllReduce, 1 / -1 = peer memory when available */
+		pl->opt_exchange = value;
+		mf_xchg_teardown(pl);
+		TRY(mf_xchg_setup(pl));
+	}
 	else
 		return mf_fail(MFGPU_EINVAL, "unknown option '%s'", name);
 	for (int g = 0; g < local_shards(pl); g++) {

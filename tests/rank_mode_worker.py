@@ -24,6 +24,9 @@ def main():
     inst = synth.random_instance(300, 200, 20, 0.1, 25, 0.002, seed=33)
     L, R = api.random_fill_LR(inst.users, inst.items, inst.features)
     plan = api.Plan(inst.users, inst.items, inst.features, inst.entries, inst.alpha, comm=comm)
+    if len(sys.argv) > 2 and sys.argv[2] == "nccl":
+        plan.set_option("exchange", 0)
+    kind = plan.exchange_kind()
     plan.set_factors(L, R)
     plan.iterate(17)           # graph path (16) + one direct iteration
     plan.iterate(8)
@@ -40,7 +43,7 @@ def main():
             L[a:b] = rows
             best_all[a:b] = bb
         replicas_equal = all(np.array_equal(parts[0][4].view(np.uint64), p[4].view(np.uint64)) for p in parts)
-        np.savez(out_path, L=L, R=R, best=best_all, replicas_equal=replicas_equal,
+        np.savez(out_path, L=L, R=R, best=best_all, replicas_equal=replicas_equal, exchange_kind=kind,
                  cut=np.array([p[0] for p in parts] + [inst.users]))
     dist.destroy_process_group()
 

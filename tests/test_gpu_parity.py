@@ -226,12 +226,14 @@ def test_multi_gpu_matches_sharded_oracle(gpu, oracle, nshards):
                                                  inst.entries, L0, R0))
 
 
+@pytest.mark.parametrize("exchange", ["peer", "nccl"])
 @pytest.mark.parametrize("nranks", [2, 4, 8])
-def test_rank_mode_nccl_allreduce(gpu, oracle, tmp_path, nranks):
-    """One process per GPU (what bench.py does under torchrun): NCCL all-reduce of the
-    R gradient.  Replicas of R bit-identical to each other; against the oracle's N-shard
-    ordering bit-identical for 2 ranks (a+b is commutative) and within 1e-9 of max|x|
-    otherwise (NCCL's reduction order is its own)."""
+def test_rank_mode_exchange(gpu, oracle, tmp_path, nranks, exchange):
+    """One process per GPU (what bench.py does under torchrun).  The R gradient is reduced either
+    by one kernel reading every rank's buffer over NVLink peer memory (the default; ranks are added
+    in rank order, so the result is bit-identical to the oracle's N-shard ordering for any N) or by
+    ncclAllReduce (bit-identical for 2 ranks, a+b being commutative, within 1e-9 of max|x| otherwise:
+    NCCL's reduction order is its own).  Replicas of R are bit-identical to each other either way."""
     import sys
     import socket
     if gpu.device_count() < nranks:
@@ -242,17 +244,18 @@ def test_rank_mode_nccl_allreduce(gpu, oracle, tmp_path, nranks):
     out = tmp_path / "rank_mode.npz"
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(nranks),
            "--master-addr", "127.0.0.1", "--master-port", str(port),
-           os.path.join(ROOT, "tests", "rank_mode_worker.py"), str(out)]
+           os.path.join(ROOT, "tests", "rank_mode_worker.py"), str(out), exchange]
     p = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert p.returncode == 0, p.stderr[-3000:]
     got = np.load(out)
+    assert int(got["exchange_kind"]) == (2 if exchange == "peer" else 1)
     inst = synth.random_instance(300, 200, 20, 0.1, 25, 0.002, seed=33)
     cut = gpu.split_users(inst.users, inst.entries, nranks)
     assert np.array_equal(got["cut"], cut)
     L0, R0 = oracle.init_LR(inst.users, inst.items, inst.features)
     oracle.factorize_sharded(inst.users, inst.items, inst.features, inst.entries, 25, inst.alpha, L0, R0, cut)
     assert bool(got["replicas_equal"])
-    if nranks == 2:
+    if nranks == 2 or exchange == "peer":
         assert bits_equal(L0, got["L"]) and bits_equal(R0, got["R"])
     else:
         for a, b in ((L0, got["L"]), (R0, got["R"])):
