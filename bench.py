@@ -370,7 +370,10 @@ def main():
                        "sharding": "users" if n_gpus > 1 else "none",
                        "exchange": {0: "none", 1: "nccl allreduce of the R gradient + apply",
                                     2: "fused reduce+apply kernel over NVLink peer memory (CUDA IPC), rank order",
-                                    3: "fused reduce+apply kernel over NVLink peer memory, shard order"}[xkind],
+                                    3: "fused reduce+apply kernel over NVLink peer memory, shard order",
+                                    4: "chain kernels store gradient rows into the owning rank over NVLink peer "
+                                       "memory (CUDA IPC); owner reduces in rank order, applies, stores R_new "
+                                       "rows into every replica"}[xkind],
                        "l2": "factor buffers %.0f MB vs 126 MB L2; no flush (the loop re-reads "
                              "its own output by construction)" % (32e-6 * F * (U + I))},
             "roofline": roofline, "cpu_baseline": cpu,

@@ -268,7 +268,8 @@ class Plan:
         return lib().mfgpu_plan_launch_count(self._h)
 
     def exchange_kind(self):
-        """0 none, 1 NCCL all-reduce, 2 peer memory across processes, 3 peer memory in one process."""
+        """0 none, 1 NCCL all-reduce, 2 peer memory across processes (pull), 3 peer memory in one
+        process, 4 peer memory across processes (push: chain kernels store into the reducing rank)."""
         return lib().mfgpu_plan_exchange_kind(self._h)
 
     def bytes_per_iter(self) -> int:

@@ -13,6 +13,18 @@
 
 #define MF_MAX_SHARDS 16
 
+/* sync block of a rank (unsigned long long words; peers write into it over NVLink):
+ *   pull:  [0..1] done[b]  [2..3] consumed[b]  [4] CTAs finished   [7] barrier scratch
+ *   push:  [16+h] done_from[h]   rank h has stored all its contributions of the iteration here
+ *          [32+h] ready_from[h]  rank h has stored its rows of R_new here
+ *          [48]   epoch          iterations completed by this rank
+ *          [49]   CTAs of k_reduce_bcast finished */
+#define MF_SYNC_WORDS 64
+#define MF_SYNC_DONE 16
+#define MF_SYNC_READY 32
+#define MF_SYNC_EPOCH 48
+#define MF_SYNC_CTAS 49
+
 /* ---- NCCL, bound at run time (only rank mode needs it) ---------------------- */
 typedef struct ncclComm *mf_ncclComm_t;
 typedef struct { char internal[128]; } mf_ncclUniqueId;
@@ -41,6 +53,8 @@ struct mf_shard {
 	double *d_val, *d_e_csc, *d_e_csr;
 	int *d_mask_ptr, *d_mask_col, *d_first_free;
 	int *d_item_slot, *d_touched_item;       /* N-shard only */
+	int *d_push_owner, *d_push_row;          /* rank mode, push exchange: item -> reducing rank, row in its receive buffer */
+	int r_plain;                             /* 1: R[] from cudaMalloc (exportable over CUDA IPC), 0: from the pool */
 	int *d_chunk_row, *d_chunk_pos;          /* chunks of the long rows (k_dot) */
 	/* factors, double buffered; L holds the shard's users only */
 	double *L[2], *R[2];
@@ -75,13 +89,20 @@ struct mfgpu_plan {
 	int have_factors;
 	long long launches;
 	float loop_ms, rec_ms;
-	/* rank mode over peer memory (mf_xchg_setup): every rank maps the G buffers and the flag
-	 * block of every other rank (CUDA IPC) and reduces + applies in one kernel */
-	int xchg_ipc;                                  /* 1: peer-memory exchange, 0: ncclAllReduce */
+	/* Rank mode over peer memory (mf_xchg_setup): every rank maps the G and R buffers and the
+	 * flag block of every other rank (CUDA IPC).  xchg_ipc:
+	 *   0  ncclAllReduce + k_apply_R
+	 *   1  pull: one kernel reads every rank's G over NVLink, adds in rank order, applies
+	 *   2  push (default): the chain kernels store each finished gradient row into the receive
+	 *      buffer of the rank that reduces that item; that rank adds the N contributions in rank
+	 *      order, applies, and stores its rows of R_new into every replica (k_reduce_bcast) */
+	int xchg_ipc;
+	int slots_per_rank;                            /* push: touched items reduced by one rank (the last may own fewer) */
 	double *peer_G[2][MF_MAX_SHARDS];              /* G[b] of rank h (own rank: the local buffer) */
-	unsigned long long *peer_sync[MF_MAX_SHARDS];  /* sync block of rank h: done[2], consumed[2]  */
+	double *peer_R[2][MF_MAX_SHARDS];              /* R[b] of rank h */
+	unsigned long long *peer_sync[MF_MAX_SHARDS];  /* sync block of rank h, MF_SYNC_WORDS words   */
 	unsigned long long *d_sync;                    /* own sync block                              */
-	void *ipc_mapped[3 * MF_MAX_SHARDS];
+	void *ipc_mapped[5 * MF_MAX_SHARDS];
 	int n_ipc_mapped;
 	/* options */
 	int opt_graph, opt_graph_iters, opt_long_row, opt_long_col, opt_ch, opt_chain_ring, opt_resident, opt_res_rows, opt_chain_ws, opt_exchange;

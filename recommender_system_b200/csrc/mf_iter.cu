@@ -112,6 +112,102 @@ k_apply_R_xchg(int n_touched, int F, int ld, const int *__restrict__ touched_ite
 	}
 }
 
+/* ---- rank mode, push exchange -------------------------------------------------------------
+ * The touched items are dealt to the ranks in blocks of `per` slots.  During the iteration the
+ * R-side chains store every finished gradient row into the receive buffer of the rank that
+ * owns the item (ChainSide::peer_out, mf_loop.cuh) -- the transfer rides under the chain
+ * kernels.  Then, per iteration and rank:
+ *   k_push_done     after the chain kernels: tell every rank "my contributions are with you"
+ *                   (doing this from the last chain CTA instead was measured: a system-scope
+ *                   fence at the end of every chain CTA costs 14 us per iteration at two ranks)
+ *   k_reduce_bcast  wait for that word from every rank; for the own block of items add the N
+ *                   contributions in rank order (bit-identical everywhere and to the oracle's
+ *                   N-shard order), add R_old, store the new rows into every replica of R_new;
+ *                   the last CTA tells every rank "my rows of R_new are with you" and waits for
+ *                   that word from every rank: R_new is then complete in this replica
+ * The receive buffer needs no double buffering: a rank stores into it again only after it has
+ * seen everybody's `ready` of the previous iteration, which follows everybody's reduce.  The
+ * words are iteration counts (never reset), each rank keeps its own count in `epoch`. */
+struct PushPeers {
+	double *Rnew[MF_MAX_SHARDS];
+	unsigned long long *sync[MF_MAX_SHARDS];
+	int n, me;
+};
+
+__device__ __forceinline__ void spin_until(const volatile unsigned long long *w, unsigned long long want)
+{
+	unsigned spins = 0;
+	while (*w < want)
+		if (++spins > (1u << 24))        /* a rank that never arrives: fail instead of hanging */
+			__trap();
+}
+
+__global__ void k_push_done(const PushPeers pp, const unsigned long long *sync_own)
+{
+	if ((int)threadIdx.x < pp.n) {
+		__threadfence_system();          /* the rows stored by the kernels before this one */
+		*(volatile unsigned long long *)(pp.sync[threadIdx.x] + MF_SYNC_DONE + pp.me) = sync_own[MF_SYNC_EPOCH] + 1;
+	}
+}
+
+__global__ void __launch_bounds__(256)
+k_reduce_bcast(const PushPeers pp, int per, int cnt, int ld, const int *__restrict__ own_item,
+               const double *__restrict__ Rold, const double *recv, unsigned long long *sync_own)
+{
+	__shared__ bool last_cta;
+	const unsigned long long want = sync_own[MF_SYNC_EPOCH] + 1;
+	if ((int)threadIdx.x < pp.n) {
+		spin_until(sync_own + MF_SYNC_DONE + threadIdx.x, want);
+		__threadfence_system();
+	}
+	__syncthreads();
+	const int ld2 = ld >> 1;
+	const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
+	if (t < (long)cnt * ld2) {
+		const int q = (int)(t / ld2), kp = (int)(t % ld2);
+		const double *g = recv + (size_t)q * ld + 2 * kp;
+		const size_t blk = (size_t)per * ld;
+		double2 sum = __ldcv(reinterpret_cast<const double2 *>(g));
+		for (int h = 1; h < pp.n; h++) {
+			const double2 x = __ldcv(reinterpret_cast<const double2 *>(g + h * blk));
+			sum.x = __dadd_rn(sum.x, x.x);
+			sum.y = __dadd_rn(sum.y, x.y);
+		}
+		const size_t o = (size_t)own_item[q] * ld + 2 * kp;
+		const double2 r = *reinterpret_cast<const double2 *>(Rold + o);
+		double2 v;
+		v.x = __dadd_rn(r.x, sum.x);
+		v.y = __dadd_rn(r.y, sum.y);
+		for (int d = 0; d < pp.n; d++) {         /* start with the neighbour: spread the links */
+			int h = pp.me + 1 + d;
+			if (h >= pp.n)
+				h -= pp.n;
+			*reinterpret_cast<double2 *>(pp.Rnew[h] + o) = v;
+		}
+	}
+	/* the last CTA to get here publishes: every CTA has stored its rows and read `epoch` */
+	__syncthreads();
+	if (threadIdx.x == 0) {
+		__threadfence_system();
+		last_cta = atomicAdd(sync_own + MF_SYNC_CTAS, 1ull) == (unsigned long long)gridDim.x - 1;
+	}
+	__syncthreads();
+	if (last_cta) {
+		if ((int)threadIdx.x < pp.n) {
+			__threadfence_system();
+			*(volatile unsigned long long *)(pp.sync[threadIdx.x] + MF_SYNC_READY + pp.me) = want;
+			/* ... and stays until everybody's rows are here: when this launch has finished,
+			 * R_new is complete in this replica */
+			spin_until(sync_own + MF_SYNC_READY + threadIdx.x, want);
+			__threadfence_system();
+		}
+		if (threadIdx.x == 0) {
+			sync_own[MF_SYNC_CTAS] = 0;
+			sync_own[MF_SYNC_EPOCH] = want;
+		}
+	}
+}
+
 } // namespace mf
 
 template <int NG>
@@ -165,6 +261,7 @@ static mf::ChainSide side_L(const mfgpu_plan *, const mf_shard *s, int c, int be
 	d.init = s->L[c]; d.src = s->R[c]; d.out = s->L[1 - c];
 	d.own_off = s->user_lo; d.src_off = 0;
 	d.out_slot = nullptr;
+	d.out_owner = nullptr;
 	return d;
 }
 
@@ -177,7 +274,15 @@ static mf::ChainSide side_R(const mfgpu_plan *pl, const mf_shard *s, int c, int 
 	d.init = pl->nshards > 1 ? nullptr : s->R[c];    /* N shards: the gradient G starts from 0.0 */
 	d.src = s->L[c]; d.out = rout;
 	d.own_off = 0; d.src_off = s->user_lo;
+	d.out_owner = nullptr;
 	d.out_slot = pl->nshards > 1 ? s->d_item_slot : nullptr;
+	if (pl->xchg_ipc == 2 && rout == nullptr) {
+		/* push exchange: rows go to the reducing rank's receive buffer (its G[0]) */
+		d.out_slot = s->d_push_row;
+		d.out_owner = s->d_push_owner;
+		for (int h = 0; h < pl->comm->nranks; h++)
+			d.peer_out[h] = pl->peer_G[0][h];
+	}
 	return d;
 }
 
@@ -292,10 +397,39 @@ static int enqueue_xchg(mfgpu_plan *pl, mf_shard *s, int c, int b)
 	return MFGPU_OK;
 }
 
+/* rank mode, push exchange: publish the contributions, reduce + broadcast the own block of
+ * items, wait until every block has arrived (kernels above) */
+static int enqueue_push(mfgpu_plan *pl, mf_shard *s, int c)
+{
+	mf::PushPeers pp;
+	pp.n = pl->comm->nranks;
+	pp.me = pl->comm->rank;
+	for (int h = 0; h < pp.n; h++) {
+		pp.Rnew[h] = pl->peer_R[1 - c][h];
+		pp.sync[h] = pl->peer_sync[h];
+	}
+	const int per = pl->slots_per_rank;
+	const int lo = std::min(pl->n_touched, pp.me * per), cnt = std::min(per, pl->n_touched - lo);
+	const long pairs = (long)cnt * (pl->ld / 2);
+	mf::k_push_done<<<1, 32, 0, s->st>>>(pp, pl->d_sync);
+	/* a rank without items of its own still takes part: it publishes `ready` */
+	mf::k_reduce_bcast<<<(unsigned)std::max(1L, (pairs + 255) / 256), 256, 0, s->st>>>(
+	    pp, per, cnt, pl->ld, s->d_touched_item + lo, s->R[c], s->G[0], pl->d_sync);
+	CK(cudaGetLastError());
+	pl->launches += 2;
+	return MFGPU_OK;
+}
+
 static int enqueue_iteration(mfgpu_plan *pl, mf_shard *s, int c)
 {
 	if (pl->nshards == 1)
 		return enqueue_loop_kernels(pl, s, c, s->R[1 - c]);
+	if (pl->xchg_ipc == 2) {
+		if ((size_t)pl->n_touched * pl->ld == 0)
+			return enqueue_loop_kernels(pl, s, c, s->G[0]);
+		TRY(enqueue_loop_kernels(pl, s, c, nullptr));
+		return enqueue_push(pl, s, c);
+	}
 	/* rank mode: the gradient goes to G[c] for the peer-memory exchange (double buffered,
 	 * see k_apply_R_xchg), to G[0] for NCCL */
 	TRY(enqueue_loop_kernels(pl, s, c, pl->xchg_ipc ? s->G[c] : s->G[0]));
@@ -460,7 +594,7 @@ extern "C" int mfgpu_plan_profile_kernels(mfgpu_plan *pl, int reps, float ms[5])
 	const int c = pl->cur;
 	const long long before = pl->launches;
 	CK(cudaSetDevice(s->dev));
-	double *rout = pl->nshards == 1 ? s->R[1 - c] : s->G[0];
+	double *rout = pl->nshards == 1 ? s->R[1 - c] : pl->xchg_ipc == 2 ? nullptr : s->G[0];
 	if (pl->xchg_ipc) {
 		/* the launches below write G[0] outside the exchange protocol: wait until no peer
 		 * can still be reducing it (a one-word all-reduce after everybody's last iteration) */
@@ -481,7 +615,9 @@ extern "C" int mfgpu_plan_profile_kernels(mfgpu_plan *pl, int reps, float ms[5])
 				TRY(launch_chain(pl, s, c, rout, false, s->st));
 			else if (phase == 3)
 				TRY(launch_chain(pl, s, c, rout, true, s->st));
-			else if (pl->xchg_ipc) {
+			else if (pl->xchg_ipc == 2) {
+				TRY(enqueue_push(pl, s, c));
+			} else if (pl->xchg_ipc) {
 				TRY(enqueue_xchg(pl, s, c, 0));
 			} else {
 				NCK(g_nccl.AllReduce(s->G[0], s->G[1], (size_t)pl->n_touched * pl->ld, 8, 0,

@@ -784,6 +784,16 @@ k_dot(const LoopArgs p, const double *__restrict__ Lold, const double *__restric
  *   R side (matFact.c:50-51): out = R_new (or G from 0.0 for N shards, matFact-mpi.c:187-205),
  *                             init = R_old, src = L_old, idx = users of the column
  */
+/* where the finished chain of row/column `own` is stored: the own matrix, the row of G, or --
+ * rank mode with the push exchange -- the receive buffer of the rank that reduces this item,
+ * written over NVLink while the other chains of the launch are still running */
+__device__ __forceinline__ double *chain_out(const ChainSide &sd, int own, int ld)
+{
+	const size_t orow = sd.out_slot ? (size_t)sd.out_slot[own] : (size_t)(own - sd.own_off);
+	double *base = sd.out_owner ? sd.peer_out[sd.out_owner[own]] : sd.out;
+	return base + orow * ld;
+}
+
 constexpr int CHAIN_BULK_REGS = 0, CHAIN_DEEP_REGS = 1, CHAIN_BULK_RING = 2, CHAIN_DEEP_RING = 3;
 constexpr int RING_BULK_ROWS = 8, RING_BULK_STAGES = 3;     /* 6.2 KB per warp  */
 constexpr int RING_DEEP_ROWS = 16, RING_DEEP_STAGES = 6;    /* 24 KB per warp */
@@ -826,10 +836,8 @@ k_chain(const ChainSide A, const ChainSide B, long warps_a, int F, int ld)
 		else
 			acc = chain_bulk<8>(acc, lane, sd.idx + b, sd.e + b, m, srck, ld);
 	}
-	if (active) {
-		const size_t orow = sd.out_slot ? (size_t)sd.out_slot[own] : (size_t)(own - sd.own_off);
-		sd.out[orow * ld + k] = acc;
-	}
+	if (active)
+		chain_out(sd, own, ld)[k] = acc;
 }
 
 /*
@@ -921,55 +929,52 @@ k_chain_ws(const ChainSide A, const ChainSide B, long units_a, int F, int ld)
 			if (lane == 0)
 				mbar_arrive(empty(slot));
 		}
-		if (active) {
-			const size_t orow = sd.out_slot ? (size_t)sd.out_slot[own] : (size_t)(own - sd.own_off);
-			sd.out[orow * ld + k] = acc;
+		if (active)
+			chain_out(sd, own, ld)[k] = acc;
+	} else {
+		/* ---- producer p: stages p, p + 2, ... (stage s = nonzeros 32s .. 32s+31) ---- */
+		const int p = warp - 1;
+		const int half = lane >> 4, piece = lane & 15;
+		const int gw = min(32, ld - g * 32);                 /* doubles of this group in a row (even) */
+		const bool piece_ok = 2 * piece < gw;
+		const double *src_g = sd.src + g * 32 + 2 * piece - (size_t)sd.src_off * ld;
+		const int *idx = sd.idx + b;
+		const double *ev = sd.e + b;
+		int *iring = (int *)(smem + WS_STAGES * WS_STAGE_DOUBLES + 2 * WS_STAGES) + p * WS_IDX_BLOCKS * 32;
+		auto request = [&](int t) {          /* indices of this producer's t-th stage */
+			const int s = 2 * t + p;
+			if (s < nst)
+				cp_async4(iring + (t % WS_IDX_BLOCKS) * 32 + lane, idx + min(s * 32 + lane, m - 1));
+			cp_async_commit();
+		};
+#pragma unroll
+		for (int t = 0; t < WS_IDX_AHEAD; t++)
+			request(t);
+		for (int t = 0; 2 * t + p < nst; t++) {
+			const int s = 2 * t + p, slot = s % WS_STAGES;
+			request(t + WS_IDX_AHEAD);
+			cp_async_wait<WS_IDX_AHEAD>();
+			__syncwarp();
+			const int *bi = iring + (t % WS_IDX_BLOCKS) * 32 + half;
+			int iu[WS_ROWS / 2];             /* all indices first: the copies are compiler barriers */
+#pragma unroll
+			for (int u = 0; u < WS_ROWS / 2; u++)
+				iu[u] = bi[2 * u];
+			if (s >= WS_STAGES)
+				mbar_wait(empty(slot), ((s / WS_STAGES) - 1) & 1);
+			double *st = smem + (size_t)slot * WS_STAGE_DOUBLES;
+			const uint32_t st_addr = smem_u32(st) + (uint32_t)(half * 32 + 2 * piece) * 8u;
+#pragma unroll
+			for (int u = 0; u < WS_ROWS / 2; u++)
+				cp_async16_if(st_addr + u * 512u, src_g + (size_t)iu[u] * ld, piece_ok);
+			const int n = s * WS_ROWS + lane;
+			if (n < m)
+				cp_async8(st + WS_ROWS * 32 + lane, ev + n);
+			mbar_arrive_on_copies(full(slot));
+			__syncwarp();                 /* ring entry t + WS_IDX_BLOCKS overwrites this block */
 		}
-		return;
+		cp_async_wait<0>();
 	}
-
-	/* ---- producer p: stages p, p + 2, ... (stage s = nonzeros 32s .. 32s+31) ---- */
-	const int p = warp - 1;
-	const int half = lane >> 4, piece = lane & 15;
-	const int gw = min(32, ld - g * 32);                 /* doubles of this group in a row (even) */
-	const bool piece_ok = 2 * piece < gw;
-	const double *src_g = sd.src + g * 32 + 2 * piece - (size_t)sd.src_off * ld;
-	const int *idx = sd.idx + b;
-	const double *ev = sd.e + b;
-	int *iring = (int *)(smem + WS_STAGES * WS_STAGE_DOUBLES + 2 * WS_STAGES) + p * WS_IDX_BLOCKS * 32;
-	auto request = [&](int t) {          /* indices of this producer's t-th stage */
-		const int s = 2 * t + p;
-		if (s < nst)
-			cp_async4(iring + (t % WS_IDX_BLOCKS) * 32 + lane, idx + min(s * 32 + lane, m - 1));
-		cp_async_commit();
-	};
-#pragma unroll
-	for (int t = 0; t < WS_IDX_AHEAD; t++)
-		request(t);
-	for (int t = 0; 2 * t + p < nst; t++) {
-		const int s = 2 * t + p, slot = s % WS_STAGES;
-		request(t + WS_IDX_AHEAD);
-		cp_async_wait<WS_IDX_AHEAD>();
-		__syncwarp();
-		const int *bi = iring + (t % WS_IDX_BLOCKS) * 32 + half;
-		int iu[WS_ROWS / 2];             /* all indices first: the copies are compiler barriers */
-#pragma unroll
-		for (int u = 0; u < WS_ROWS / 2; u++)
-			iu[u] = bi[2 * u];
-		if (s >= WS_STAGES)
-			mbar_wait(empty(slot), ((s / WS_STAGES) - 1) & 1);
-		double *st = smem + (size_t)slot * WS_STAGE_DOUBLES;
-		const uint32_t st_addr = smem_u32(st) + (uint32_t)(half * 32 + 2 * piece) * 8u;
-#pragma unroll
-		for (int u = 0; u < WS_ROWS / 2; u++)
-			cp_async16_if(st_addr + u * 512u, src_g + (size_t)iu[u] * ld, piece_ok);
-		const int n = s * WS_ROWS + lane;
-		if (n < m)
-			cp_async8(st + WS_ROWS * 32 + lane, ev + n);
-		mbar_arrive_on_copies(full(slot));
-		__syncwarp();                 /* ring entry t + WS_IDX_BLOCKS overwrites this block */
-	}
-	cp_async_wait<0>();
 }
 
 /* N shards: R_new[item] = R_old[item] + G[slot] for the touched items. */

@@ -310,16 +310,40 @@ static int shard_create(mfgpu_plan *pl, mf_shard *s, int dev, const mfgpu_entry 
 	const size_t nu = (size_t)(s->user_hi - s->user_lo);
 	const size_t lbytes = (nu * pl->ld + 2) * sizeof(double);
 	const size_t rbytes = ((size_t)pl->items * pl->ld + 2) * sizeof(double);
+	/* rank mode: peers store their rows of R_new straight into this replica (push exchange), so
+	 * R must be exportable over CUDA IPC, which pool memory is not */
+	s->r_plain = pl->comm != nullptr;
 	for (int b = 0; b < 2; b++) {
 		TRY(dev_alloc((void **)&s->L[b], lbytes, s->st));
-		TRY(dev_alloc((void **)&s->R[b], rbytes, s->st));
+		if (s->r_plain)
+			CK(cudaMalloc((void **)&s->R[b], rbytes));
+		else
+			TRY(dev_alloc((void **)&s->R[b], rbytes, s->st));
 		CK(cudaMemsetAsync(s->L[b], 0, lbytes, s->st));
 		CK(cudaMemsetAsync(s->R[b], 0, rbytes, s->st));
 	}
 	if (pl->nshards > 1) {
 		TRY(upload(&s->d_item_slot, item_slot, (size_t)pl->items, s->st));
 		TRY(upload(&s->d_touched_item, touched_item, (size_t)pl->n_touched, s->st));
-		const size_t gbytes = ((size_t)pl->n_touched * pl->ld + 2) * sizeof(double);
+		if (pl->comm) {
+			/* push exchange: touched item of slot t is reduced by rank t / slots_per_rank; this
+			 * rank's contribution goes to row rank * slots_per_rank + (t mod slots_per_rank) of
+			 * that rank's receive buffer */
+			const int per = pl->slots_per_rank, me = pl->comm->rank;
+			std::vector<int> owner((size_t)std::max(1, pl->items), 0), prow((size_t)std::max(1, pl->items), 0);
+			for (int j = 0; j < pl->items; j++)
+				if (item_slot[j] >= 0) {
+					owner[j] = item_slot[j] / per;
+					prow[j] = me * per + item_slot[j] % per;
+				}
+			TRY(upload(&s->d_push_owner, owner.data(), (size_t)pl->items, s->st));
+			TRY(upload(&s->d_push_row, prow.data(), (size_t)pl->items, s->st));
+			CK(cudaStreamSynchronize(s->st));     /* the vectors die with this scope */
+		}
+		/* G: one row per touched item; as the receive buffer of the push exchange, nshards
+		 * blocks of slots_per_rank rows (one block per contributing rank) */
+		const size_t grows = std::max((size_t)pl->n_touched, (size_t)pl->nshards * pl->slots_per_rank);
+		const size_t gbytes = (grows * pl->ld + 2) * sizeof(double);
 		for (int b = 0; b < 2; b++) {
 			CK(cudaMalloc((void **)&s->G[b], gbytes));
 			/* columns without a local nonzero are never written: they stay 0.0 */
@@ -359,13 +383,16 @@ static void shard_destroy(mf_shard *s)
 	for (int g = 0; g < 2; g++) {
 		if (s->ev_g[g]) cudaEventDestroy(s->ev_g[g]);
 		dev_free(s->L[g], s->st);
-		dev_free(s->R[g], s->st);
+		if (s->r_plain)
+			cudaFree(s->R[g]);
+		else
+			dev_free(s->R[g], s->st);
 		cudaFree(s->G[g]);
 	}
 	tc.lap("destroy: factor buffers");
 	void *ptrs[] = {s->d_row_id, s->d_row_ptr, s->d_col_idx, s->d_epos, s->d_col_id, s->d_col_ptr,
 	                s->d_row_idx, s->d_val, s->d_e_csc, s->d_e_csr, s->d_mask_ptr, s->d_mask_col,
-	                s->d_first_free, s->d_item_slot, s->d_touched_item, s->part_v, s->part_j,
+	                s->d_first_free, s->d_item_slot, s->d_touched_item, s->d_push_owner, s->d_push_row, s->part_v, s->part_j,
 	                s->nan_first, s->d_best, s->L_keep, s->R_keep, s->d_chunk_row, s->d_chunk_pos};
 	for (void *q : ptrs)
 		dev_free(q, s->st);
@@ -394,7 +421,7 @@ static void shard_destroy(mf_shard *s)
  * through one ncclAllGather.  If any rank cannot export or map (no peer access, IPC disabled),
  * all ranks fall back to ncclAllReduce together. */
 struct XchgHandles {
-	cudaIpcMemHandle_t g[2], sync;
+	cudaIpcMemHandle_t g[2], r[2], sync;
 	int ok, pad[15];
 };
 
@@ -416,18 +443,29 @@ static bool xchg_all_ok(mfgpu_plan *pl, mf_shard *s, int mine, int *d_scratch)
 int mf_xchg_setup(mfgpu_plan *pl)
 {
 	pl->xchg_ipc = 0;
-	if (!pl->comm || pl->nshards < 2 || (size_t)pl->n_touched * pl->ld == 0 || pl->opt_exchange == 0)
+	if (!pl->comm || pl->nshards < 2 || (size_t)pl->n_touched * pl->ld == 0)
 		return MFGPU_OK;
 	mf_shard *s = &pl->sh[0];
 	const int n = pl->comm->nranks, me = pl->comm->rank;
 	CK(cudaSetDevice(s->dev));
-	CK(cudaMalloc((void **)&pl->d_sync, 64));
-	CK(cudaMemsetAsync(pl->d_sync, 0, 64, s->st));
+	/* every transport relies on "rows of G nobody writes are 0.0", and each lays G out in its
+	 * own way: start clean (the all-reduce of xchg_all_ok below is the barrier after this) */
+	{
+		const size_t grows = std::max((size_t)pl->n_touched, (size_t)pl->nshards * pl->slots_per_rank);
+		for (int b = 0; b < 2; b++)
+			CK(cudaMemsetAsync(s->G[b], 0, (grows * pl->ld + 2) * sizeof(double), s->st));
+	}
+	if (pl->opt_exchange == 0)
+		return MFGPU_OK;
+	CK(cudaMalloc((void **)&pl->d_sync, MF_SYNC_WORDS * sizeof(unsigned long long)));
+	CK(cudaMemsetAsync(pl->d_sync, 0, MF_SYNC_WORDS * sizeof(unsigned long long), s->st));
 
 	XchgHandles mine;
 	memset(&mine, 0, sizeof mine);
 	mine.ok = cudaIpcGetMemHandle(&mine.g[0], s->G[0]) == cudaSuccess &&
 	          cudaIpcGetMemHandle(&mine.g[1], s->G[1]) == cudaSuccess &&
+	          cudaIpcGetMemHandle(&mine.r[0], s->R[0]) == cudaSuccess &&
+	          cudaIpcGetMemHandle(&mine.r[1], s->R[1]) == cudaSuccess &&
 	          cudaIpcGetMemHandle(&mine.sync, pl->d_sync) == cudaSuccess;
 	cudaGetLastError();
 
@@ -445,14 +483,16 @@ int mf_xchg_setup(mfgpu_plan *pl)
 	pl->n_ipc_mapped = 0;
 	for (int h = 0; h < n && ok; h++) {
 		if (h == me) {
-			pl->peer_G[0][h] = s->G[0];
-			pl->peer_G[1][h] = s->G[1];
+			for (int b = 0; b < 2; b++) {
+				pl->peer_G[b][h] = s->G[b];
+				pl->peer_R[b][h] = s->R[b];
+			}
 			pl->peer_sync[h] = pl->d_sync;
 			continue;
 		}
-		void *q[3] = {nullptr, nullptr, nullptr};
-		const cudaIpcMemHandle_t *hd[3] = {&all[h].g[0], &all[h].g[1], &all[h].sync};
-		for (int k = 0; k < 3 && ok; k++) {
+		void *q[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+		const cudaIpcMemHandle_t *hd[5] = {&all[h].g[0], &all[h].g[1], &all[h].r[0], &all[h].r[1], &all[h].sync};
+		for (int k = 0; k < 5 && ok; k++) {
 			if (cudaIpcOpenMemHandle(&q[k], *hd[k], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
 				cudaGetLastError();
 				ok = 0;
@@ -462,7 +502,9 @@ int mf_xchg_setup(mfgpu_plan *pl)
 		}
 		pl->peer_G[0][h] = (double *)q[0];
 		pl->peer_G[1][h] = (double *)q[1];
-		pl->peer_sync[h] = (unsigned long long *)q[2];
+		pl->peer_R[0][h] = (double *)q[2];
+		pl->peer_R[1][h] = (double *)q[3];
+		pl->peer_sync[h] = (unsigned long long *)q[4];
 	}
 	/* everybody, or nobody */
 	const bool all_ok = xchg_all_ok(pl, s, ok, (int *)d_all);
@@ -472,11 +514,11 @@ int mf_xchg_setup(mfgpu_plan *pl)
 			cudaIpcCloseMemHandle(pl->ipc_mapped[k]);
 		pl->n_ipc_mapped = 0;
 		cudaGetLastError();
-		if (pl->opt_exchange == 1 && getenv("MFGPU_TRACE"))
+		if (pl->opt_exchange > 0 && getenv("MFGPU_TRACE"))
 			fprintf(stderr, "[mfgpu] peer-memory exchange unavailable, using ncclAllReduce\n");
 		return MFGPU_OK;
 	}
-	pl->xchg_ipc = 1;
+	pl->xchg_ipc = pl->opt_exchange == 2 ? 1 : 2;     /* option exchange=2: the pull kernel */
 	return MFGPU_OK;
 }
 
@@ -559,6 +601,7 @@ static int plan_create(mfgpu_plan **out, int users, int items, int features, int
 				rc = cnt;
 			else {
 				pl->n_touched = cnt;
+				pl->slots_per_rank = std::max(1, (cnt + nshards - 1) / nshards);
 				touched = (int *)malloc(sizeof(int) * (size_t)(cnt ? cnt : 1));
 				if (!touched)
 					rc = MFGPU_ENOMEM;
@@ -720,7 +763,7 @@ extern "C" int mfgpu_plan_exchange_kind(mfgpu_plan *pl)
 		return 0;
 	if (!pl->comm)
 		return 3;
-	return pl->xchg_ipc ? 2 : 1;
+	return pl->xchg_ipc == 2 ? 4 : pl->xchg_ipc ? 2 : 1;
 }
 
 extern "C" long long mfgpu_plan_bytes_per_iter(mfgpu_plan *pl)
@@ -759,7 +802,8 @@ extern "C" int mfgpu_plan_set_option(mfgpu_plan *pl, const char *name, int value
 	else if (!strcmp(name, "res_rows")) pl->opt_res_rows = value;
 	else if (!strcmp(name, "chain_ws")) pl->opt_chain_ws = value;
 	else if (!strcmp(name, "exchange")) {
-		/* rank mode, collective: 0 = ncclAllReduce, 1 / -1 = peer memory when available */
+		/* rank mode, collective: 0 = ncclAllReduce; peer memory when available: 1 / -1 = push
+		 * (chain kernels store into the reducing rank, k_reduce_bcast), 2 = pull (k_apply_R_xchg) */
 		pl->opt_exchange = value;
 		mf_xchg_teardown(pl);
 		TRY(mf_xchg_setup(pl));

@@ -7,6 +7,8 @@
 
 namespace mf {
 
+constexpr int MAX_PEERS = 16;   /* = MF_MAX_SHARDS (mf_internal.h) */
+
 /* Rows (users with >= 1 nonzero) are stored longest first and fall in three classes:
  *   [0, n_deep_rows)        dots by k_dot, accumulation by k_chain<deep>
  *   [n_deep_rows, n_long)   dots by k_dot, accumulation by k_chain<bulk>
@@ -43,6 +45,11 @@ struct ChainSide {
 	double *out;
 	int own_off, src_off;     /* first row held by init/out and by src                  */
 	const int *out_slot;      /* nullptr, or out row = out_slot[id[r]] (N shards: G)   */
+	/* rank mode, push exchange: the finished row goes straight into the receive buffer of the
+	 * rank that owns the item (a store over NVLink peer memory): out = peer_out[out_owner[id[r]]],
+	 * row = out_slot[id[r]] inside that buffer.  out_owner == nullptr: plain `out`. */
+	const int *out_owner;
+	double *peer_out[MAX_PEERS];
 };
 
 constexpr int AM_TI = 64;      /* users per CTA           */

@@ -226,14 +226,18 @@ def test_multi_gpu_matches_sharded_oracle(gpu, oracle, nshards):
                                                  inst.entries, L0, R0))
 
 
-@pytest.mark.parametrize("exchange", ["peer", "nccl"])
+@pytest.mark.parametrize("exchange", ["push", "pull", "nccl"])
 @pytest.mark.parametrize("nranks", [2, 4, 8])
 def test_rank_mode_exchange(gpu, oracle, tmp_path, nranks, exchange):
-    """One process per GPU (what bench.py does under torchrun).  The R gradient is reduced either
-    by one kernel reading every rank's buffer over NVLink peer memory (the default; ranks are added
-    in rank order, so the result is bit-identical to the oracle's N-shard ordering for any N) or by
-    ncclAllReduce (bit-identical for 2 ranks, a+b being commutative, within 1e-9 of max|x| otherwise:
-    NCCL's reduction order is its own).  Replicas of R are bit-identical to each other either way."""
+    """One process per GPU (what bench.py does under torchrun).  The R gradient is reduced
+    - push (default): the chain kernels store each finished gradient row over NVLink peer memory
+      into the rank that owns the item; that rank adds the N contributions in rank order, applies
+      and stores its rows of R_new into every replica;
+    - pull: one kernel per rank reads every rank's whole gradient over NVLink, rank order;
+    - nccl: ncclAllReduce + apply.
+    Rank order means bit-identical to the oracle's N-shard ordering for any N; NCCL's order is its
+    own (bit-identical for 2 ranks, a+b being commutative, within 1e-9 of max|x| otherwise).
+    Replicas of R are bit-identical to each other in all three."""
     import sys
     import socket
     if gpu.device_count() < nranks:
@@ -248,14 +252,14 @@ def test_rank_mode_exchange(gpu, oracle, tmp_path, nranks, exchange):
     p = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert p.returncode == 0, p.stderr[-3000:]
     got = np.load(out)
-    assert int(got["exchange_kind"]) == (2 if exchange == "peer" else 1)
+    assert int(got["exchange_kind"]) == {"push": 4, "pull": 2, "nccl": 1}[exchange]
     inst = synth.random_instance(300, 200, 20, 0.1, 25, 0.002, seed=33)
     cut = gpu.split_users(inst.users, inst.entries, nranks)
     assert np.array_equal(got["cut"], cut)
     L0, R0 = oracle.init_LR(inst.users, inst.items, inst.features)
     oracle.factorize_sharded(inst.users, inst.items, inst.features, inst.entries, 25, inst.alpha, L0, R0, cut)
     assert bool(got["replicas_equal"])
-    if nranks == 2 or exchange == "peer":
+    if nranks == 2 or exchange != "nccl":
         assert bits_equal(L0, got["L"]) and bits_equal(R0, got["R"])
     else:
         for a, b in ((L0, got["L"]), (R0, got["R"])):
