@@ -373,7 +373,11 @@ def main():
                                     3: "fused reduce+apply kernel over NVLink peer memory, shard order",
                                     4: "chain kernels store gradient rows into the owning rank over NVLink peer "
                                        "memory (CUDA IPC); owner reduces in rank order, applies, stores R_new "
-                                       "rows into every replica"}[xkind],
+                                       "rows into every replica (fences + flag words)",
+                                    5: "chain kernels store gradient elements as (value, tag) pairs into the owning "
+                                       "rank over NVLink peer memory (CUDA IPC); one kernel reduces the own items "
+                                       "in rank order as pairs arrive, applies, stores R_new pairs into every "
+                                       "replica and unpacks the others' (no fences, no flags)"}[xkind],
                        "l2": "factor buffers %.0f MB vs 126 MB L2; no flush (the loop re-reads "
                              "its own output by construction)" % (32e-6 * F * (U + I))},
             "roofline": roofline, "cpu_baseline": cpu,

@@ -269,7 +269,8 @@ class Plan:
 
     def exchange_kind(self):
         """0 none, 1 NCCL all-reduce, 2 peer memory across processes (pull), 3 peer memory in one
-        process, 4 peer memory across processes (push: chain kernels store into the reducing rank)."""
+        process, 4 peer memory across processes (push: chain kernels store into the reducing rank,
+        fences + flags), 5 the same with (value, tag) pairs and no fences (low latency, default)."""
         return lib().mfgpu_plan_exchange_kind(self._h)
 
     def bytes_per_iter(self) -> int:

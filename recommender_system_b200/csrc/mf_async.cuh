@@ -100,4 +100,27 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
 			__trap();
 }
 
+
+/* (value, tag) pairs of the low-latency exchange (mf_iter.cu): one 16-byte store / load, which
+ * NVLink and L2 deliver whole, so a reader that sees the tag it waits for also has the value --
+ * no fence, no flag of its own (the idea of NCCL's LL protocol, with 8-byte payloads) */
+__device__ __forceinline__ void st_pair(double *p, double v, unsigned long long tag)
+{
+	asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(__double_as_longlong(v)), "l"(tag)
+	             : "memory");
+}
+
+__device__ __forceinline__ double ld_pair_when(const double *p, unsigned long long tag)
+{
+	unsigned long long v, t;
+	unsigned spins = 0;
+	for (;;) {
+		asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(v), "=l"(t) : "l"(p) : "memory");
+		if (t == tag)
+			return __longlong_as_double((long long)v);
+		if (++spins > (1u << 24))      /* a rank that never delivers: fail instead of hanging */
+			__trap();
+	}
+}
+
 } // namespace mf

@@ -54,6 +54,8 @@ struct mf_shard {
 	int *d_mask_ptr, *d_mask_col, *d_first_free;
 	int *d_item_slot, *d_touched_item;       /* N-shard only */
 	int *d_push_owner, *d_push_row;          /* rank mode, push exchange: item -> reducing rank, row in its receive buffer */
+	int *d_contrib;                          /* rank mode: per touched item, bit h = rank h has a nonzero in it */
+	double *G_scratch;                       /* profiling launches of the chain kernels write here */
 	int r_plain;                             /* 1: R[] from cudaMalloc (exportable over CUDA IPC), 0: from the pool */
 	int *d_chunk_row, *d_chunk_pos;          /* chunks of the long rows (k_dot) */
 	/* factors, double buffered; L holds the shard's users only */
@@ -93,9 +95,13 @@ struct mfgpu_plan {
 	 * flag block of every other rank (CUDA IPC).  xchg_ipc:
 	 *   0  ncclAllReduce + k_apply_R
 	 *   1  pull: one kernel reads every rank's G over NVLink, adds in rank order, applies
-	 *   2  push (default): the chain kernels store each finished gradient row into the receive
-	 *      buffer of the rank that reduces that item; that rank adds the N contributions in rank
-	 *      order, applies, and stores its rows of R_new into every replica (k_reduce_bcast) */
+	 *   2  push: the chain kernels store each finished gradient row into the receive buffer of
+	 *      the rank that reduces that item; that rank adds the N contributions in rank order,
+	 *      applies, and stores its rows of R_new into every replica (k_reduce_bcast); fences and
+	 *      flag words order the two phases
+	 *   3  low latency (default): as push, but every element travels as a (value, tag) pair in
+	 *      one 16-byte store and the readers poll for the tag of the iteration: no fences, no
+	 *      flag words; one launch (k_xchg_ll) reduces the own block and unpacks the others' */
 	int xchg_ipc;
 	int slots_per_rank;                            /* push: touched items reduced by one rank (the last may own fewer) */
 	double *peer_G[2][MF_MAX_SHARDS];              /* G[b] of rank h (own rank: the local buffer) */

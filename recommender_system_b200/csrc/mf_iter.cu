@@ -208,6 +208,100 @@ k_reduce_bcast(const PushPeers pp, int per, int cnt, int ld, const int *__restri
 	}
 }
 
+/* ---- rank mode, low-latency exchange ------------------------------------------------------
+ * The same data flow as the push exchange, but every element travels as a (value, tag) pair in
+ * one 16-byte store (st_pair / ld_pair_when, mf_async.cuh), tag = number of the iteration, and
+ * the readers poll the element itself: no fence, no flag word, no launch that only signals.
+ *   chain kernels   store (gradient value, tag) into the receive buffer of the reducing rank
+ *   k_xchg_ll       CTAs [0, reduce_ctas): one thread per element of the own block of items:
+ *                   take the contributions in rank order as they arrive (ranks without a
+ *                   nonzero in the item contribute +0.0 and are not waited for: `contrib`),
+ *                   add R_old, store R_new here and as (value, tag) into every other rank;
+ *                   the other CTAs: one thread per element of the other ranks' blocks: take the
+ *                   pair when it arrives and store the value into R_new.
+ * The reducing CTAs come first in the grid, so they are resident before any unpacking CTA:
+ * they wait only for the chain kernels of the other ranks, the unpacking CTAs only for the
+ * reducing CTAs of the other ranks -- no cycle.  Buffers are single: a rank stores
+ * contributions of the next iteration only after its own unpacking is complete, i.e. after
+ * every reducing rank has read all contributions of this one. */
+struct LLArgs {
+	double *stage[MF_MAX_SHARDS];     /* pair buffer for R_new rows of every rank (own: unused) */
+	const double *recv;               /* own pair buffer for contributions: [rank][slot in block][ld] */
+	const double *stage_own;
+	const double *Rold;
+	double *Rnew;
+	const int *touched_item, *contrib;
+	unsigned long long *sync_own;
+	int n, me, per, n_touched, lo, cnt, F, ld;
+	unsigned reduce_ctas;
+};
+
+__global__ void __launch_bounds__(256)
+k_xchg_ll(const LLArgs a)
+{
+	__shared__ bool last_cta;
+	const unsigned long long want = a.sync_own[MF_SYNC_EPOCH] + 1;
+	if (blockIdx.x < a.reduce_ctas) {
+		const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
+		if (t < (long)a.cnt * a.F) {
+			const int q = (int)(t / a.F), k = (int)(t % a.F);
+			const int slot = a.lo + q, who = a.contrib[slot];
+			const size_t blk = (size_t)a.per * a.ld;
+			const double *g = a.recv + 2 * ((size_t)q * a.ld + k);
+			double sum = (who & 1) ? ld_pair_when(g, want) : 0.0;
+			for (int h = 1; h < a.n; h++)
+				sum = __dadd_rn(sum, ((who >> h) & 1) ? ld_pair_when(g + 2 * h * blk, want) : 0.0);
+			const size_t o = (size_t)a.touched_item[slot] * a.ld + k;
+			const double v = __dadd_rn(a.Rold[o], sum);
+			a.Rnew[o] = v;
+			const size_t so = 2 * ((size_t)slot * a.ld + k);
+			for (int d = 1; d < a.n; d++) {          /* start with the neighbour: spread the links */
+				int h = a.me + d;
+				if (h >= a.n)
+					h -= a.n;
+				st_pair(a.stage[h] + so, v, want);
+			}
+		}
+	} else {
+		const long u = (long)(blockIdx.x - a.reduce_ctas) * blockDim.x + threadIdx.x;
+		if (u < (long)(a.n_touched - a.cnt) * a.F) {
+			int slot = (int)(u / a.F);
+			const int k = (int)(u % a.F);
+			if (slot >= a.lo)
+				slot += a.cnt;                        /* skip the own block */
+			const double v = ld_pair_when(a.stage_own + 2 * ((size_t)slot * a.ld + k), want);
+			a.Rnew[(size_t)a.touched_item[slot] * a.ld + k] = v;
+		}
+	}
+	/* the last CTA to get here closes the iteration */
+	__syncthreads();
+	if (threadIdx.x == 0) {
+		__threadfence();
+		last_cta = atomicAdd(a.sync_own + MF_SYNC_CTAS, 1ull) == (unsigned long long)gridDim.x - 1;
+	}
+	__syncthreads();
+	if (last_cta && threadIdx.x == 0) {
+		a.sync_own[MF_SYNC_CTAS] = 0;
+		a.sync_own[MF_SYNC_EPOCH] = want;
+	}
+}
+
+/* profiling only: this rank's contributions again, with the tag of the next exchange and no
+ * chain kernels before it (the values do not matter: the exchange writes the output buffer) */
+__global__ void __launch_bounds__(256)
+k_ll_repush(const LLArgs a, const PeerG recv_of)
+{
+	const unsigned long long want = a.sync_own[MF_SYNC_EPOCH] + 1;
+	const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= (long)a.n_touched * a.F)
+		return;
+	const int slot = (int)(t / a.F), k = (int)(t % a.F);
+	if (!((a.contrib[slot] >> a.me) & 1))
+		return;
+	const size_t row = (size_t)a.me * a.per + slot % a.per;
+	st_pair(const_cast<double *>(recv_of.g[slot / a.per]) + 2 * (row * a.ld + k), 0.0, want);
+}
+
 } // namespace mf
 
 template <int NG>
@@ -262,6 +356,7 @@ static mf::ChainSide side_L(const mfgpu_plan *, const mf_shard *s, int c, int be
 	d.own_off = s->user_lo; d.src_off = 0;
 	d.out_slot = nullptr;
 	d.out_owner = nullptr;
+	d.ll_epoch = nullptr;
 	return d;
 }
 
@@ -276,12 +371,15 @@ static mf::ChainSide side_R(const mfgpu_plan *pl, const mf_shard *s, int c, int 
 	d.own_off = 0; d.src_off = s->user_lo;
 	d.out_owner = nullptr;
 	d.out_slot = pl->nshards > 1 ? s->d_item_slot : nullptr;
-	if (pl->xchg_ipc == 2 && rout == nullptr) {
-		/* push exchange: rows go to the reducing rank's receive buffer (its G[0]) */
+	d.ll_epoch = nullptr;
+	if (pl->xchg_ipc >= 2 && rout == nullptr) {
+		/* push / low-latency exchange: rows go to the reducing rank's receive buffer (its G[0]) */
 		d.out_slot = s->d_push_row;
 		d.out_owner = s->d_push_owner;
 		for (int h = 0; h < pl->comm->nranks; h++)
 			d.peer_out[h] = pl->peer_G[0][h];
+		if (pl->xchg_ipc == 3)
+			d.ll_epoch = pl->d_sync + MF_SYNC_EPOCH;
 	}
 	return d;
 }
@@ -420,15 +518,48 @@ static int enqueue_push(mfgpu_plan *pl, mf_shard *s, int c)
 	return MFGPU_OK;
 }
 
+/* rank mode, low-latency exchange: one launch (k_xchg_ll above) */
+static mf::LLArgs ll_args(const mfgpu_plan *pl, const mf_shard *s, int c)
+{
+	mf::LLArgs a;
+	a.n = pl->comm->nranks;
+	a.me = pl->comm->rank;
+	for (int h = 0; h < a.n; h++)
+		a.stage[h] = pl->peer_G[1][h];
+	a.recv = s->G[0];
+	a.stage_own = s->G[1];
+	a.Rold = s->R[c];
+	a.Rnew = s->R[1 - c];
+	a.touched_item = s->d_touched_item;
+	a.contrib = s->d_contrib;
+	a.sync_own = pl->d_sync;
+	a.per = pl->slots_per_rank;
+	a.n_touched = pl->n_touched;
+	a.lo = std::min(pl->n_touched, a.me * a.per);
+	a.cnt = std::min(a.per, pl->n_touched - a.lo);
+	a.F = pl->F;
+	a.ld = pl->ld;
+	a.reduce_ctas = (unsigned)(((long)a.cnt * a.F + 255) / 256);
+	return a;
+}
+
+static int enqueue_ll(mfgpu_plan *pl, mf_shard *s, int c)
+{
+	const mf::LLArgs a = ll_args(pl, s, c);
+	const long unpack = ((long)(a.n_touched - a.cnt) * a.F + 255) / 256;
+	mf::k_xchg_ll<<<(unsigned)std::max(1L, (long)a.reduce_ctas + unpack), 256, 0, s->st>>>(a);
+	CK(cudaGetLastError());
+	pl->launches++;
+	return MFGPU_OK;
+}
+
 static int enqueue_iteration(mfgpu_plan *pl, mf_shard *s, int c)
 {
 	if (pl->nshards == 1)
 		return enqueue_loop_kernels(pl, s, c, s->R[1 - c]);
-	if (pl->xchg_ipc == 2) {
-		if ((size_t)pl->n_touched * pl->ld == 0)
-			return enqueue_loop_kernels(pl, s, c, s->G[0]);
+	if (pl->xchg_ipc >= 2) {
 		TRY(enqueue_loop_kernels(pl, s, c, nullptr));
-		return enqueue_push(pl, s, c);
+		return pl->xchg_ipc == 3 ? enqueue_ll(pl, s, c) : enqueue_push(pl, s, c);
 	}
 	/* rank mode: the gradient goes to G[c] for the peer-memory exchange (double buffered,
 	 * see k_apply_R_xchg), to G[0] for NCCL */
@@ -511,7 +642,7 @@ static long long launches_per_iteration(const mfgpu_plan *pl, const mf_shard *s)
 	n += (a.n_long - a.n_deep_rows > 0 || a.n_cols - a.n_deep_cols > 0);
 	n += (a.n_deep_rows > 0 || a.n_deep_cols > 0);
 	if (pl->nshards > 1 && (long)pl->n_touched * pl->F > 0)
-		n += pl->xchg_ipc ? 2 : 1;
+		n += pl->xchg_ipc == 3 ? 1 : pl->xchg_ipc ? 2 : 1;
 	return n;
 }
 
@@ -594,7 +725,13 @@ extern "C" int mfgpu_plan_profile_kernels(mfgpu_plan *pl, int reps, float ms[5])
 	const int c = pl->cur;
 	const long long before = pl->launches;
 	CK(cudaSetDevice(s->dev));
-	double *rout = pl->nshards == 1 ? s->R[1 - c] : pl->xchg_ipc == 2 ? nullptr : s->G[0];
+	double *rout = pl->nshards == 1 ? s->R[1 - c] : s->G[0];
+	if (pl->xchg_ipc >= 2) {
+		/* the chain launches below must not store into the other ranks outside an iteration */
+		if (!s->G_scratch)
+			CK(cudaMalloc((void **)&s->G_scratch, ((size_t)pl->n_touched * pl->ld + 2) * sizeof(double)));
+		rout = s->G_scratch;
+	}
 	if (pl->xchg_ipc) {
 		/* the launches below write G[0] outside the exchange protocol: wait until no peer
 		 * can still be reducing it (a one-word all-reduce after everybody's last iteration) */
@@ -615,7 +752,15 @@ extern "C" int mfgpu_plan_profile_kernels(mfgpu_plan *pl, int reps, float ms[5])
 				TRY(launch_chain(pl, s, c, rout, false, s->st));
 			else if (phase == 3)
 				TRY(launch_chain(pl, s, c, rout, true, s->st));
-			else if (pl->xchg_ipc == 2) {
+			else if (pl->xchg_ipc == 3) {
+				const mf::LLArgs a = ll_args(pl, s, c);
+				mf::PeerG recv_of;
+				recv_of.n = a.n;
+				for (int h = 0; h < a.n; h++)
+					recv_of.g[h] = pl->peer_G[0][h];
+				mf::k_ll_repush<<<(unsigned)(((long)a.n_touched * a.F + 255) / 256), 256, 0, s->st>>>(a, recv_of);
+				TRY(enqueue_ll(pl, s, c));
+			} else if (pl->xchg_ipc == 2) {
 				TRY(enqueue_push(pl, s, c));
 			} else if (pl->xchg_ipc) {
 				TRY(enqueue_xchg(pl, s, c, 0));

@@ -784,14 +784,18 @@ k_dot(const LoopArgs p, const double *__restrict__ Lold, const double *__restric
  *   R side (matFact.c:50-51): out = R_new (or G from 0.0 for N shards, matFact-mpi.c:187-205),
  *                             init = R_old, src = L_old, idx = users of the column
  */
-/* where the finished chain of row/column `own` is stored: the own matrix, the row of G, or --
- * rank mode with the push exchange -- the receive buffer of the rank that reduces this item,
- * written over NVLink while the other chains of the launch are still running */
-__device__ __forceinline__ double *chain_out(const ChainSide &sd, int own, int ld)
+/* The finished chain value of feature k of row/column `own` goes to the own matrix, to the row
+ * of G, or -- rank mode -- into the receive buffer of the rank that reduces this item, over NVLink
+ * while the other chains of the launch are still running; with the low-latency exchange as a
+ * (value, tag) pair that the reducer polls for (st_pair, mf_async.cuh). */
+__device__ __forceinline__ void chain_store(const ChainSide &sd, int own, int ld, int k, double acc)
 {
 	const size_t orow = sd.out_slot ? (size_t)sd.out_slot[own] : (size_t)(own - sd.own_off);
 	double *base = sd.out_owner ? sd.peer_out[sd.out_owner[own]] : sd.out;
-	return base + orow * ld;
+	if (sd.ll_epoch)
+		st_pair(base + 2 * (orow * ld + k), acc, *sd.ll_epoch + 1);
+	else
+		base[orow * ld + k] = acc;
 }
 
 constexpr int CHAIN_BULK_REGS = 0, CHAIN_DEEP_REGS = 1, CHAIN_BULK_RING = 2, CHAIN_DEEP_RING = 3;
@@ -837,7 +841,7 @@ k_chain(const ChainSide A, const ChainSide B, long warps_a, int F, int ld)
 			acc = chain_bulk<8>(acc, lane, sd.idx + b, sd.e + b, m, srck, ld);
 	}
 	if (active)
-		chain_out(sd, own, ld)[k] = acc;
+		chain_store(sd, own, ld, k, acc);
 }
 
 /*
@@ -930,7 +934,7 @@ k_chain_ws(const ChainSide A, const ChainSide B, long units_a, int F, int ld)
 				mbar_arrive(empty(slot));
 		}
 		if (active)
-			chain_out(sd, own, ld)[k] = acc;
+			chain_store(sd, own, ld, k, acc);
 	} else {
 		/* ---- producer p: stages p, p + 2, ... (stage s = nonzeros 32s .. 32s+31) ---- */
 		const int p = warp - 1;

@@ -122,6 +122,18 @@ static int upload(T **dst, const T *src, size_t n, cudaStream_t st)
 	return MFGPU_OK;
 }
 
+/* Bytes of one G buffer.  One process: a row of ld doubles per touched item.  Rank mode: the
+ * receive buffer of the push exchanges, nshards blocks (one per contributing rank) of
+ * slots_per_rank rows, and twice that for the (value, tag) pairs of the low-latency exchange
+ * (G[0]: contributions received, G[1]: rows of R_new received). */
+static size_t mf_g_bytes(const mfgpu_plan *pl)
+{
+	size_t rows = (size_t)pl->n_touched;
+	if (pl->comm)
+		rows = 2 * std::max(rows, (size_t)pl->nshards * pl->slots_per_rank);
+	return (rows * pl->ld + 2) * sizeof(double);
+}
+
 /* Launch geometry of k_update_L / k_update_R for one shard (see mf_loop.cuh). */
 int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
 {
@@ -264,7 +276,7 @@ int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
 }
 
 static int shard_create(mfgpu_plan *pl, mf_shard *s, int dev, const mfgpu_entry *entries,
-                        const int *item_slot, const int *touched_item)
+                        const int *item_slot, const int *touched_item, const int *contrib)
 {
 	s->dev = dev;
 	CK(cudaSetDevice(dev));
@@ -338,12 +350,12 @@ static int shard_create(mfgpu_plan *pl, mf_shard *s, int dev, const mfgpu_entry 
 				}
 			TRY(upload(&s->d_push_owner, owner.data(), (size_t)pl->items, s->st));
 			TRY(upload(&s->d_push_row, prow.data(), (size_t)pl->items, s->st));
+			TRY(upload(&s->d_contrib, contrib, (size_t)pl->n_touched, s->st));
 			CK(cudaStreamSynchronize(s->st));     /* the vectors die with this scope */
 		}
 		/* G: one row per touched item; as the receive buffer of the push exchange, nshards
 		 * blocks of slots_per_rank rows (one block per contributing rank) */
-		const size_t grows = std::max((size_t)pl->n_touched, (size_t)pl->nshards * pl->slots_per_rank);
-		const size_t gbytes = (grows * pl->ld + 2) * sizeof(double);
+		const size_t gbytes = mf_g_bytes(pl);
 		for (int b = 0; b < 2; b++) {
 			CK(cudaMalloc((void **)&s->G[b], gbytes));
 			/* columns without a local nonzero are never written: they stay 0.0 */
@@ -382,6 +394,7 @@ static void shard_destroy(mf_shard *s)
 	tc.lap("destroy: graphs");
 	for (int g = 0; g < 2; g++) {
 		if (s->ev_g[g]) cudaEventDestroy(s->ev_g[g]);
+		if (g == 0) cudaFree(s->G_scratch);
 		dev_free(s->L[g], s->st);
 		if (s->r_plain)
 			cudaFree(s->R[g]);
@@ -392,7 +405,7 @@ static void shard_destroy(mf_shard *s)
 	tc.lap("destroy: factor buffers");
 	void *ptrs[] = {s->d_row_id, s->d_row_ptr, s->d_col_idx, s->d_epos, s->d_col_id, s->d_col_ptr,
 	                s->d_row_idx, s->d_val, s->d_e_csc, s->d_e_csr, s->d_mask_ptr, s->d_mask_col,
-	                s->d_first_free, s->d_item_slot, s->d_touched_item, s->d_push_owner, s->d_push_row, s->part_v, s->part_j,
+	                s->d_first_free, s->d_item_slot, s->d_touched_item, s->d_push_owner, s->d_push_row, s->d_contrib, s->part_v, s->part_j,
 	                s->nan_first, s->d_best, s->L_keep, s->R_keep, s->d_chunk_row, s->d_chunk_pos};
 	for (void *q : ptrs)
 		dev_free(q, s->st);
@@ -450,11 +463,8 @@ int mf_xchg_setup(mfgpu_plan *pl)
 	CK(cudaSetDevice(s->dev));
 	/* every transport relies on "rows of G nobody writes are 0.0", and each lays G out in its
 	 * own way: start clean (the all-reduce of xchg_all_ok below is the barrier after this) */
-	{
-		const size_t grows = std::max((size_t)pl->n_touched, (size_t)pl->nshards * pl->slots_per_rank);
-		for (int b = 0; b < 2; b++)
-			CK(cudaMemsetAsync(s->G[b], 0, (grows * pl->ld + 2) * sizeof(double), s->st));
-	}
+	for (int b = 0; b < 2; b++)
+		CK(cudaMemsetAsync(s->G[b], 0, mf_g_bytes(pl), s->st));
 	if (pl->opt_exchange == 0)
 		return MFGPU_OK;
 	CK(cudaMalloc((void **)&pl->d_sync, MF_SYNC_WORDS * sizeof(unsigned long long)));
@@ -518,7 +528,8 @@ int mf_xchg_setup(mfgpu_plan *pl)
 			fprintf(stderr, "[mfgpu] peer-memory exchange unavailable, using ncclAllReduce\n");
 		return MFGPU_OK;
 	}
-	pl->xchg_ipc = pl->opt_exchange == 2 ? 1 : 2;     /* option exchange=2: the pull kernel */
+	/* option exchange: 2 = pull kernel, 3 = push with fences and flags, else low latency */
+	pl->xchg_ipc = pl->opt_exchange == 2 ? 1 : pl->opt_exchange == 3 ? 2 : 3;
 	return MFGPU_OK;
 }
 
@@ -590,7 +601,7 @@ static int plan_create(mfgpu_plan **out, int users, int items, int features, int
 
 	TraceClock tc;
 	int rc = mf_split_users(users, nnz, entries, nshards, pl->cut);
-	int *item_slot = nullptr, *touched = nullptr;
+	int *item_slot = nullptr, *touched = nullptr, *contrib = nullptr;
 	if (rc == MFGPU_OK && nshards > 1) {
 		item_slot = (int *)malloc(sizeof(int) * (size_t)(items ? items : 1));
 		if (!item_slot)
@@ -609,6 +620,22 @@ static int plan_create(mfgpu_plan **out, int users, int items, int features, int
 					for (int j = 0; j < items; j++)
 						if (item_slot[j] >= 0)
 							touched[item_slot[j]] = j;
+				if (rc == MFGPU_OK && comm) {
+					/* which ranks hold a nonzero of each touched item (rank of a user: cut[]) */
+					contrib = (int *)calloc((size_t)(cnt ? cnt : 1), sizeof(int));
+					if (!contrib)
+						rc = MFGPU_ENOMEM;
+					else
+						for (int n = 0; n < nnz; n++) {
+							const int u = entries[n].row;
+							if (u < 0 || u >= users) {
+								rc = MFGPU_EINVAL;
+								break;
+							}
+							const int r = (int)(std::upper_bound(pl->cut, pl->cut + nshards + 1, u) - pl->cut) - 1;
+							contrib[item_slot[entries[n].col]] |= 1 << r;
+						}
+				}
 			}
 		}
 	}
@@ -621,14 +648,14 @@ static int plan_create(mfgpu_plan **out, int users, int items, int features, int
 			/* rank mode: this process holds one shard, the users of its rank */
 			pl->sh[0].user_lo = pl->cut[comm->rank];
 			pl->sh[0].user_hi = pl->cut[comm->rank + 1];
-			rc = shard_create(pl, &pl->sh[0], comm->device, entries, item_slot, touched);
+			rc = shard_create(pl, &pl->sh[0], comm->device, entries, item_slot, touched, contrib);
 			if (rc == MFGPU_OK)
 				rc = mf_xchg_setup(pl);
 		} else {
 			for (int g = 0; g < nshards && rc == MFGPU_OK; g++) {
 				pl->sh[g].user_lo = pl->cut[g];
 				pl->sh[g].user_hi = pl->cut[g + 1];
-				rc = shard_create(pl, &pl->sh[g], devs[g], entries, item_slot, touched);
+				rc = shard_create(pl, &pl->sh[g], devs[g], entries, item_slot, touched, nullptr);
 			}
 			/* the peer exchange reads every other shard's G directly */
 			for (int g = 0; g < nshards && rc == MFGPU_OK && nshards > 1; g++) {
@@ -653,6 +680,7 @@ static int plan_create(mfgpu_plan **out, int users, int items, int features, int
 	}
 	free(item_slot);
 	free(touched);
+	free(contrib);
 	if (rc != MFGPU_OK) {
 		char keep[512];
 		snprintf(keep, sizeof keep, "%s", mfgpu_last_error());
@@ -763,7 +791,7 @@ extern "C" int mfgpu_plan_exchange_kind(mfgpu_plan *pl)
 		return 0;
 	if (!pl->comm)
 		return 3;
-	return pl->xchg_ipc == 2 ? 4 : pl->xchg_ipc ? 2 : 1;
+	return pl->xchg_ipc == 3 ? 5 : pl->xchg_ipc == 2 ? 4 : pl->xchg_ipc ? 2 : 1;
 }
 
 extern "C" long long mfgpu_plan_bytes_per_iter(mfgpu_plan *pl)
@@ -802,8 +830,9 @@ extern "C" int mfgpu_plan_set_option(mfgpu_plan *pl, const char *name, int value
 	else if (!strcmp(name, "res_rows")) pl->opt_res_rows = value;
 	else if (!strcmp(name, "chain_ws")) pl->opt_chain_ws = value;
 	else if (!strcmp(name, "exchange")) {
-		/* rank mode, collective: 0 = ncclAllReduce; peer memory when available: 1 / -1 = push
-		 * (chain kernels store into the reducing rank, k_reduce_bcast), 2 = pull (k_apply_R_xchg) */
+		/* rank mode, collective: 0 = ncclAllReduce; peer memory when available: 1 / -1 = low
+		 * latency (value, tag) exchange (k_xchg_ll), 2 = pull (k_apply_R_xchg), 3 = push with
+		 * fences and flags (k_reduce_bcast) */
 		pl->opt_exchange = value;
 		mf_xchg_teardown(pl);
 		TRY(mf_xchg_setup(pl));

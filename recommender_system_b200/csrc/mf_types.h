@@ -50,6 +50,9 @@ struct ChainSide {
 	 * row = out_slot[id[r]] inside that buffer.  out_owner == nullptr: plain `out`. */
 	const int *out_owner;
 	double *peer_out[MAX_PEERS];
+	/* low-latency exchange: the row is stored as (value, tag) pairs, tag = *ll_epoch + 1 (the
+	 * iteration being computed); element (row, k) lives at doubles 2*(row*ld + k).  nullptr: off */
+	const unsigned long long *ll_epoch;
 };
 
 constexpr int AM_TI = 64;      /* users per CTA           */

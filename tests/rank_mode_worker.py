@@ -24,9 +24,9 @@ def main():
     inst = synth.random_instance(300, 200, 20, 0.1, 25, 0.002, seed=33)
     L, R = api.random_fill_LR(inst.users, inst.items, inst.features)
     plan = api.Plan(inst.users, inst.items, inst.features, inst.entries, inst.alpha, comm=comm)
-    how = sys.argv[2] if len(sys.argv) > 2 else "push"
-    if how != "push":
-        plan.set_option("exchange", {"nccl": 0, "pull": 2}[how])
+    how = sys.argv[2] if len(sys.argv) > 2 else "ll"
+    if how != "ll":
+        plan.set_option("exchange", {"nccl": 0, "pull": 2, "push": 3}[how])
     kind = plan.exchange_kind()
     plan.set_factors(L, R)
     plan.iterate(17)           # graph path (16) + one direct iteration

@@ -226,18 +226,20 @@ def test_multi_gpu_matches_sharded_oracle(gpu, oracle, nshards):
                                                  inst.entries, L0, R0))
 
 
-@pytest.mark.parametrize("exchange", ["push", "pull", "nccl"])
+@pytest.mark.parametrize("exchange", ["ll", "push", "pull", "nccl"])
 @pytest.mark.parametrize("nranks", [2, 4, 8])
 def test_rank_mode_exchange(gpu, oracle, tmp_path, nranks, exchange):
     """One process per GPU (what bench.py does under torchrun).  The R gradient is reduced
-    - push (default): the chain kernels store each finished gradient row over NVLink peer memory
-      into the rank that owns the item; that rank adds the N contributions in rank order, applies
-      and stores its rows of R_new into every replica;
+    - ll (default): the chain kernels store each finished gradient element as a (value, tag) pair
+      over NVLink peer memory into the rank that owns the item; that rank adds the contributions
+      in rank order as they arrive, applies, and stores its rows of R_new as pairs into every
+      replica, which unpacks them -- one launch, no fences, no flag words;
+    - push: the same data flow with plain stores, ordered by system fences and flag words;
     - pull: one kernel per rank reads every rank's whole gradient over NVLink, rank order;
     - nccl: ncclAllReduce + apply.
     Rank order means bit-identical to the oracle's N-shard ordering for any N; NCCL's order is its
     own (bit-identical for 2 ranks, a+b being commutative, within 1e-9 of max|x| otherwise).
-    Replicas of R are bit-identical to each other in all three."""
+    Replicas of R are bit-identical to each other in all four."""
     import sys
     import socket
     if gpu.device_count() < nranks:
@@ -252,7 +254,7 @@ def test_rank_mode_exchange(gpu, oracle, tmp_path, nranks, exchange):
     p = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert p.returncode == 0, p.stderr[-3000:]
     got = np.load(out)
-    assert int(got["exchange_kind"]) == {"push": 4, "pull": 2, "nccl": 1}[exchange]
+    assert int(got["exchange_kind"]) == {"ll": 5, "push": 4, "pull": 2, "nccl": 1}[exchange]
     inst = synth.random_instance(300, 200, 20, 0.1, 25, 0.002, seed=33)
     cut = gpu.split_users(inst.users, inst.entries, nranks)
     assert np.array_equal(got["cut"], cut)
