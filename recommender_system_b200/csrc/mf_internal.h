@@ -64,6 +64,7 @@ struct mf_shard {
 	double *L_keep, *R_keep;                 /* mfgpu_plan_save_factors           */
 	mf::LoopArgs la;
 	int warps;                               /* 8 or 1: k_update_L template      */
+	int acc_rows;                            /* 1 or 3: rows in flight ahead in its accumulation phase */
 	int k1_blocks, dot_blocks;
 	int res_ng;                              /* > 0: k_update_L_res<res_ng> does the short rows */
 	size_t res_smem;
@@ -111,7 +112,7 @@ struct mfgpu_plan {
 	void *ipc_mapped[5 * MF_MAX_SHARDS];
 	int n_ipc_mapped;
 	/* options */
-	int opt_graph, opt_graph_iters, opt_long_row, opt_long_col, opt_ch, opt_chain_ring, opt_resident, opt_res_rows, opt_chain_ws, opt_exchange;
+	int opt_graph, opt_graph_iters, opt_long_row, opt_long_col, opt_ch, opt_chain_ring, opt_resident, opt_res_rows, opt_chain_ws, opt_exchange, opt_dot_stages, opt_acc_rows;
 };
 
 /* ---- shared helpers (defined in mf_capi.cu) ----------------------------------- */

@@ -330,14 +330,18 @@ int mf_kernels_prepare(int warps, size_t k1_smem, int res_ng, size_t res_smem)
 	default: break;
 	}
 	if (warps == 8) {
-		CK(cudaFuncSetAttribute(mf::k_update_L<8>, attr, (int)k1_smem));
-		CK(cudaFuncSetAttribute(mf::k_dot<8>, attr, (int)k1_smem));
+		CK(cudaFuncSetAttribute(mf::k_update_L<8, 1, 2>, attr, (int)k1_smem));
+		CK(cudaFuncSetAttribute(mf::k_update_L<8, 3, 2>, attr, (int)k1_smem));
+		CK(cudaFuncSetAttribute(mf::k_update_L<8, 1, 4>, attr, (int)k1_smem));
+		CK(cudaFuncSetAttribute(mf::k_update_L<8, 3, 4>, attr, (int)k1_smem));
+		CK(cudaFuncSetAttribute(mf::k_dot<8, 2>, attr, (int)k1_smem));
+		CK(cudaFuncSetAttribute(mf::k_dot<8, 4>, attr, (int)k1_smem));
 		CK(cudaFuncSetAttribute(mf::k_chain<8, mf::CHAIN_DEEP_RING>, attr,
 		                        8 * mf::ring_doubles(mf::RING_DEEP_ROWS, mf::RING_DEEP_STAGES) * (int)sizeof(double)));
 		CK(cudaFuncSetAttribute(mf::k_chain<8, mf::CHAIN_BULK_RING>, attr,
 		                        8 * mf::ring_doubles(mf::RING_BULK_ROWS, mf::RING_BULK_STAGES) * (int)sizeof(double)));
 	} else {
-		CK(cudaFuncSetAttribute(mf::k_update_L<1>, attr, (int)k1_smem));
+		CK(cudaFuncSetAttribute(mf::k_update_L<1, 1, 2>, attr, (int)k1_smem));
 	}
 	return MFGPU_OK;
 }
@@ -398,10 +402,16 @@ static int launch_fused(mfgpu_plan *pl, mf_shard *s, int c, cudaStream_t st)
 			MF_RES(1) MF_RES(2) MF_RES(3) MF_RES(4) MF_RES(5) MF_RES(6) MF_RES(7) MF_RES(8)
 		default: return mf_fail(MFGPU_EINVAL, "resident kernel: bad group count %d", s->res_ng);
 		}
-	} else if (s->warps == 8)
-		mf::k_update_L<8><<<s->k1_blocks, 256, s->k1_smem, st>>>(s->la, s->L[c], s->L[1 - c], s->R[c]);
-	else
-		mf::k_update_L<1><<<s->k1_blocks, 32, s->k1_smem, st>>>(s->la, s->L[c], s->L[1 - c], s->R[c]);
+	} else if (s->warps == 8) {
+		const bool deep_acc = s->acc_rows > 1, deep_dot = s->la.NT > 2;
+#define MF_UPD(P, NT) mf::k_update_L<8, P, NT><<<s->k1_blocks, 256, s->k1_smem, st>>>(s->la, s->L[c], s->L[1 - c], s->R[c])
+		if (deep_acc && deep_dot) MF_UPD(3, 4);
+		else if (deep_acc) MF_UPD(3, 2);
+		else if (deep_dot) MF_UPD(1, 4);
+		else MF_UPD(1, 2);
+#undef MF_UPD
+	} else
+		mf::k_update_L<1, 1, 2><<<s->k1_blocks, 32, s->k1_smem, st>>>(s->la, s->L[c], s->L[1 - c], s->R[c]);
 #undef MF_RES
 	CK(cudaGetLastError());
 	pl->launches++;
@@ -412,7 +422,10 @@ static int launch_dot(mfgpu_plan *pl, mf_shard *s, int c, cudaStream_t st)
 {
 	if (s->dot_blocks <= 0)
 		return MFGPU_OK;
-	mf::k_dot<8><<<s->dot_blocks, 256, s->k1_smem, st>>>(s->la, s->L[c], s->R[c]);
+	if (s->la.NT > 2)
+		mf::k_dot<8, 4><<<s->dot_blocks, 256, s->k1_smem, st>>>(s->la, s->L[c], s->R[c]);
+	else
+		mf::k_dot<8, 2><<<s->dot_blocks, 256, s->k1_smem, st>>>(s->la, s->L[c], s->R[c]);
 	CK(cudaGetLastError());
 	pl->launches++;
 	return MFGPU_OK;

@@ -112,13 +112,17 @@ __device__ __forceinline__ double dot_tile(double s, const double *l, const doub
 
 /* Lout[k] = ((init[k] + es[0]*R[j_0][k]) + es[1]*R[j_1][k]) + ...  for the NG feature groups
  * k = kb + g*32 + lane of this lane (matFact.c:48-49 order within the row).  The R values of
- * nonzero n+1 are loaded (coalesced, 256 B per group) while those of n are being added. */
-template <int NG>
+ * the next P nonzeros are in flight (coalesced loads, 256 B per group) while one is added: P = 1
+ * when the launch has warps to spare and only throughput counts, P = 3 when a shard is so
+ * small that a warp's own latency decides (rank mode with many ranks).  Loads are never
+ * predicated (a predicated load is followed by a select that waits for it): rows shorter than
+ * P fetch their last nonzero again instead. */
+template <int NG, int P>
 __device__ __forceinline__ void row_update(const double *init, double *Lout,
                                            const double *__restrict__ Rold, int j, const double *es,
                                            int cnt, int ld, int kb, int F, int lane)
 {
-	double acc[NG], x[NG], xn[NG];
+	double acc[NG], x[P][NG], xn[NG];
 	const bool last_ok = kb + (NG - 1) * 32 + lane < F;   /* only the last group can be partial */
 	size_t off[NG];
 #pragma unroll
@@ -127,30 +131,38 @@ __device__ __forceinline__ void row_update(const double *init, double *Lout,
 		off[g] = ok ? (size_t)(kb + g * 32 + lane) : 0;    /* idle lanes read a valid address */
 		acc[g] = ok ? init[off[g]] : 0.0;
 	}
-	{
-		const double *row = Rold + (size_t)__shfl_sync(FULL, j, 0) * ld;
+#pragma unroll
+	for (int u = 0; u < P; u++) {
+		const double *row = Rold + (size_t)__shfl_sync(FULL, j, min(u, cnt - 1)) * ld;
 #pragma unroll
 		for (int g = 0; g < NG; g++)
-			x[g] = row[off[g]];
+			x[u][g] = row[off[g]];
 	}
-	for (int n = 0; n + 1 < cnt; n++) {
+	int n = 0;
+	for (; n + P < cnt; n++) {
 		const double e = es[n];
-		const double *row = Rold + (size_t)__shfl_sync(FULL, j, n + 1) * ld;
+		const double *row = Rold + (size_t)__shfl_sync(FULL, j, n + P) * ld;
 #pragma unroll
 		for (int g = 0; g < NG; g++)
 			xn[g] = row[off[g]];
 #pragma unroll
 		for (int g = 0; g < NG; g++) {
-			acc[g] = __dadd_rn(acc[g], __dmul_rn(e, x[g]));
-			x[g] = xn[g];
+			acc[g] = __dadd_rn(acc[g], __dmul_rn(e, x[0][g]));
+#pragma unroll
+			for (int u = 0; u + 1 < P; u++)
+				x[u][g] = x[u + 1][g];
+			x[P - 1][g] = xn[g];
 		}
 	}
-	{
-		const double e = es[cnt - 1];      /* the last nonzero: nothing left to fetch */
+	/* the last min(P, cnt) nonzeros: nothing left to fetch */
 #pragma unroll
-		for (int g = 0; g < NG; g++)
-			acc[g] = __dadd_rn(acc[g], __dmul_rn(e, x[g]));
-	}
+	for (int u = 0; u < P; u++)
+		if (n + u < cnt) {
+			const double e = es[n + u];
+#pragma unroll
+			for (int g = 0; g < NG; g++)
+				acc[g] = __dadd_rn(acc[g], __dmul_rn(e, x[u][g]));
+		}
 #pragma unroll
 	for (int g = 0; g < NG; g++)
 		if (g < NG - 1 || last_ok)
@@ -369,50 +381,75 @@ __device__ __forceinline__ double chain_ring(double acc, int lane, const int *__
 	return acc;
 }
 
+/* wait until at most n of this thread's copy groups are pending (n is not a constant here) */
+__device__ __forceinline__ void cp_async_wait_dyn(int n)
+{
+	switch (n) {
+	case 0: cp_async_wait<0>(); break;
+	case 1: cp_async_wait<1>(); break;
+	case 2: cp_async_wait<2>(); break;
+	case 3: cp_async_wait<3>(); break;
+	case 4: cp_async_wait<4>(); break;
+	case 5: cp_async_wait<5>(); break;
+	case 6: cp_async_wait<6>(); break;
+	default: cp_async_wait<7>(); break;
+	}
+}
+
 /* e_n = alpha2 * (a_n - L_i . R_j) for the chunk's nonzero of this lane (lane < cnt): one
- * lane per nonzero walks k sequentially (mat2d.c:133-137) while the R rows stream through the
- * two tiles T0/T1, the next tile in flight while the current one is added.  Ls must be the
+ * lane per nonzero walks k sequentially (mat2d.c:133-137) while the R rows stream through a
+ * ring of NT tiles of `td` doubles each, NT - 1 tiles in flight while one is added (NT = 2 when
+ * the other warps of the SM hide the latency, more when the shard is small).  Ls must be the
  * warp's copy of L_i; copies issued by the caller before this call join the first group. */
-__device__ __forceinline__ double chunk_error(double *T0, double *T1, const double *Ls,
+template <int NT>
+__device__ __forceinline__ double chunk_error(double *tiles, int td, const double *Ls,
                                               const double *__restrict__ Rold, int j, double a, int cnt,
                                               int F, int ld, double alpha2, int lane)
 {
 	const int ntiles = (F + KT - 1) / KT;
 	StagePlan sp;
 	stage_plan(sp, Rold, j, cnt, ld, lane);
-	stage_tile(T0, sp, 0, ld);
-	cp_async_commit();
-	double s = 0.0;
-	for (int t = 0; t < ntiles; t++) {
-		double *cur = (t & 1) ? T1 : T0;
-		if (t + 1 < ntiles)
-			stage_tile((t & 1) ? T0 : T1, sp, (t + 1) * KT, ld);
+#pragma unroll
+	for (int t = 0; t < NT - 1; t++) {
+		if (t < ntiles)
+			stage_tile(tiles + t * td, sp, t * KT, ld);
 		cp_async_commit();
-		cp_async_wait<1>();           /* everything but the tile just issued has landed */
+	}
+	double s = 0.0;
+	int slot = 0, fill = NT - 1;      /* ring slots of the tile being added / being filled */
+	for (int t = 0; t < ntiles; t++) {
+		if (t + NT - 1 < ntiles)
+			stage_tile(tiles + fill * td, sp, (t + NT - 1) * KT, ld);
+		cp_async_commit();
+		cp_async_wait<NT - 1>();      /* everything but the NT - 1 newest groups has landed */
 		__syncwarp();
 		if (lane < cnt)
-			s = dot_tile(s, Ls + t * KT, cur + lane * TS, min(KT, F - t * KT));
-		__syncwarp();                 /* tile `cur` may be overwritten by the next issue */
+			s = dot_tile(s, Ls + t * KT, tiles + slot * td + lane * TS, min(KT, F - t * KT));
+		__syncwarp();                 /* the slot may be overwritten by the next issue */
+		slot = slot + 1 == NT ? 0 : slot + 1;
+		fill = fill + 1 == NT ? 0 : fill + 1;
 	}
 	return __dmul_rn(alpha2, __dsub_rn(a, s));
 }
 
 /*
  * By-user pass of the short rows [n_long, n_rows): one warp per row does everything.
- * Dynamic shared memory per warp: two dot-phase tiles [CH][TS], the user's L row [ld], es[32].
+ * Dynamic shared memory per warp: NT dot-phase tiles [CH][TS], the user's L row [ld], es[32]
+ * (NT must be LoopArgs::NT, which sized the launch).
+ * P: rows in flight ahead of the one being added in the accumulation phase (row_update).
  */
-template <int WARPS>
-__global__ void __launch_bounds__(WARPS * 32)
+template <int WARPS, int P, int NT>
+__global__ void __launch_bounds__(WARPS * 32, WARPS == 8 ? (P > 1 ? 2 : 3) : 1)
 k_update_L(const LoopArgs p, const double *__restrict__ Lold, double *__restrict__ Lnew,
            const double *__restrict__ Rold)
 {
 	extern __shared__ __align__(16) double smem[];
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 	const int F = p.F, ld = p.ld, CH = p.CH;
-	const size_t per_warp = (size_t)2 * CH * TS + ld + 32;
-	double *T0 = smem + per_warp * warp;
-	double *T1 = T0 + (size_t)CH * TS;
-	double *Ls = T1 + (size_t)CH * TS;
+	const int td = CH * TS;
+	const size_t per_warp = (size_t)NT * td + ld + 32;
+	double *tiles = smem + per_warp * warp;
+	double *Ls = tiles + (size_t)NT * td;
 	double *es = Ls + ld;
 
 	const int r = p.n_long + (int)blockIdx.x * WARPS + warp;
@@ -436,7 +473,7 @@ k_update_L(const LoopArgs p, const double *__restrict__ Lold, double *__restrict
 			a = p.val[pos];
 		}
 		j = __shfl_sync(FULL, j, min(lane, cnt - 1));   /* idle lanes mirror a valid item */
-		const double e = chunk_error(T0, T1, Ls, Rold, j, a, cnt, F, ld, p.alpha2, lane);
+		const double e = chunk_error<NT>(tiles, td, Ls, Rold, j, a, cnt, F, ld, p.alpha2, lane);
 		if (lane < cnt) {
 			p.e_csc[p.epos[pos]] = e;
 			es[lane] = e;
@@ -447,32 +484,17 @@ k_update_L(const LoopArgs p, const double *__restrict__ Lold, double *__restrict
 		for (int kb = 0; kb < F; kb += 256) {
 			const double *init = (c0 == 0) ? Ls : Lout;
 			switch (min(8, (F - kb + 31) >> 5)) {
-			case 1: row_update<1>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
-			case 2: row_update<2>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
-			case 3: row_update<3>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
-			case 4: row_update<4>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
-			case 5: row_update<5>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
-			case 6: row_update<6>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
-			case 7: row_update<7>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
-			default: row_update<8>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
+			case 1: row_update<1, P>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
+			case 2: row_update<2, P>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
+			case 3: row_update<3, P>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
+			case 4: row_update<4, P>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
+			case 5: row_update<5, P>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
+			case 6: row_update<6, P>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
+			case 7: row_update<7, P>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
+			default: row_update<8, P>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
 			}
 		}
 		__syncwarp();                 /* es is rewritten by the next chunk */
-	}
-}
-
-/* wait until at most n of this thread's copy groups are pending (n is not a constant here) */
-__device__ __forceinline__ void cp_async_wait_dyn(int n)
-{
-	switch (n) {
-	case 0: cp_async_wait<0>(); break;
-	case 1: cp_async_wait<1>(); break;
-	case 2: cp_async_wait<2>(); break;
-	case 3: cp_async_wait<3>(); break;
-	case 4: cp_async_wait<4>(); break;
-	case 5: cp_async_wait<5>(); break;
-	case 6: cp_async_wait<6>(); break;
-	default: cp_async_wait<7>(); break;
 	}
 }
 
@@ -741,17 +763,17 @@ k_update_L_res(const LoopArgs p, const double *__restrict__ Lold, double *__rest
  * its by-user and by-item positions; k_chain does the accumulations.
  * Dynamic shared memory per warp: as k_update_L.
  */
-template <int WARPS>
+template <int WARPS, int NT>
 __global__ void __launch_bounds__(WARPS * 32)
 k_dot(const LoopArgs p, const double *__restrict__ Lold, const double *__restrict__ Rold)
 {
 	extern __shared__ __align__(16) double smem[];
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 	const int F = p.F, ld = p.ld, CH = p.CH;
-	const size_t per_warp = (size_t)2 * CH * TS + ld + 32;
-	double *T0 = smem + per_warp * warp;
-	double *T1 = T0 + (size_t)CH * TS;
-	double *Ls = T1 + (size_t)CH * TS;
+	const int td = CH * TS;
+	const size_t per_warp = (size_t)NT * td + ld + 32;
+	double *tiles = smem + per_warp * warp;
+	double *Ls = tiles + (size_t)NT * td;
 
 	const int c = (int)blockIdx.x * WARPS + warp;
 	if (c >= p.n_chunks)
@@ -770,7 +792,7 @@ k_dot(const LoopArgs p, const double *__restrict__ Lold, const double *__restric
 		a = p.val[pos];
 	}
 	j = __shfl_sync(FULL, j, min(lane, cnt - 1));
-	const double e = chunk_error(T0, T1, Ls, Rold, j, a, cnt, F, ld, p.alpha2, lane);
+	const double e = chunk_error<NT>(tiles, td, Ls, Rold, j, a, cnt, F, ld, p.alpha2, lane);
 	if (lane < cnt) {
 		p.e_csr[pos] = e;
 		p.e_csc[p.epos[pos]] = e;

@@ -145,10 +145,23 @@ int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
 	int CH = std::max(1, std::min(32, s->pat.max_row_len));
 	if (pl->opt_ch > 0)
 		CH = std::max(1, std::min(32, pl->opt_ch));
-	auto warp_doubles = [&](int ch) { return (size_t)2 * ch * TS + pl->ld + 32; };
+	/* Depth of the two pipelines of a k_update_L warp: NT tiles in the dot-phase ring (2 or 4),
+	 * acc_rows rows in flight ahead of the addition in the accumulation phase (1 or 3).  The
+	 * shallow ones are the default at every size: measured on B200 at F = 200, the deep variants
+	 * (fewer warps per SM: 10.5 KB of tiles, 128 registers) lose both on the full inst60000 shape
+	 * (273 -> 327 / 347 us) and on one eighth of it, the shard of one rank of eight (41 -> 49 /
+	 * 51 us): resident warps hide latency better than a deeper pipeline per warp.  Options
+	 * dot_stages / acc_rows select them for experiments. */
+	int NT = pl->opt_dot_stages > 2 ? 4 : 2;
+	s->acc_rows = pl->opt_acc_rows > 1 ? 3 : 1;
+	auto warp_doubles = [&](int ch) { return (size_t)NT * ch * TS + pl->ld + 32; };
 	int warps = 8;
 	if (8 * warp_doubles(CH) * sizeof(double) > (size_t)max_smem)
-		warps = 1;
+		NT = 2;
+	if (8 * warp_doubles(CH) * sizeof(double) > (size_t)max_smem) {
+		warps = 1;      /* one warp per CTA: k_update_L<1, 1, 2> */
+		s->acc_rows = 1;
+	}
 	if (warps * warp_doubles(CH) * sizeof(double) > (size_t)max_smem)
 		return mf_fail(MFGPU_EINVAL, "features=%d does not fit shared memory (%d bytes)", F, max_smem);
 	s->warps = warps;
@@ -217,6 +230,7 @@ int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
 	a.F = F;
 	a.ld = pl->ld;
 	a.CH = CH;
+	a.NT = NT;
 	a.CR = CR;
 	a.RST = RST;
 	a.n_rows = pt.n_rows;
@@ -829,6 +843,8 @@ extern "C" int mfgpu_plan_set_option(mfgpu_plan *pl, const char *name, int value
 	else if (!strcmp(name, "resident")) pl->opt_resident = value;
 	else if (!strcmp(name, "res_rows")) pl->opt_res_rows = value;
 	else if (!strcmp(name, "chain_ws")) pl->opt_chain_ws = value;
+	else if (!strcmp(name, "dot_stages")) pl->opt_dot_stages = value;
+	else if (!strcmp(name, "acc_rows")) pl->opt_acc_rows = value;
 	else if (!strcmp(name, "exchange")) {
 		/* rank mode, collective: 0 = ncclAllReduce; peer memory when available: 1 / -1 = low
 		 * latency (value, tag) exchange (k_xchg_ll), 2 = pull (k_apply_R_xchg), 3 = push with

@@ -18,6 +18,7 @@ struct LoopArgs {
 	int F;            /* features                                         */
 	int ld;           /* row stride of L and R in doubles (even, >= F)    */
 	int CH;           /* nonzeros per chunk of the dot phase (<= 32)      */
+	int NT;           /* tiles in the dot-phase ring of a warp (2..4)     */
 	int CR, RST;      /* k_update_L_res: resident rows per chunk, their stride in doubles */
 	int n_rows, n_long, n_deep_rows;
 	int n_cols, n_deep_cols;

@@ -38,7 +38,7 @@ def main():
                 best = min(best, plan.timer_stop() / 64)
             k = plan.profile_kernels(20)
             print("%-40s iter %7.1f us | %s" % (opts, best * 1e3, "  ".join(
-                "%s %6.1f" % (n, 1e3 * t) for n, t in zip(api.KERNELS, k) if t > 1e-3)), flush=True)
+                "%s %6.1f" % (n, 1e3 * t) for n, t in k.items() if t > 1e-3)), flush=True)
 
 
 if __name__ == "__main__":
