@@ -15,8 +15,8 @@ CFLAGS   = -O2 -ffp-contract=off -Wall -Wextra -fPIC -Iinclude
 PKG      = recommender_system_b200
 LIB      = $(PKG)/libmatfact_b200.so
 CSRC     = $(PKG)/csrc
-HDRS     = include/matfact_b200.h $(PKG)/host/mf_prep.h $(CSRC)/mf_internal.h $(CSRC)/mf_types.h $(CSRC)/mf_loop.cuh $(CSRC)/mf_argmax.cuh
-OBJS     = build/mf_capi.o build/mf_plan.o build/mf_iter.o build/mf_prep.o
+HDRS     = include/matfact_b200.h $(PKG)/host/mf_prep.h $(PKG)/host/mf_ingest.h $(CSRC)/mf_internal.h $(CSRC)/mf_types.h $(CSRC)/mf_loop.cuh $(CSRC)/mf_argmax.cuh
+OBJS     = build/mf_capi.o build/mf_plan.o build/mf_iter.o build/mf_prep.o build/mf_ingest.o
 
 all: $(LIB) bin/matFact
 
@@ -27,6 +27,10 @@ build/%.o: $(CSRC)/%.cu $(HDRS)
 build/mf_prep.o: $(PKG)/host/mf_prep.c $(PKG)/host/mf_prep.h include/matfact_b200.h
 	@mkdir -p build
 	$(CC) $(CFLAGS) -c $< -o $@
+
+build/mf_ingest.o: $(PKG)/host/mf_ingest.c $(PKG)/host/mf_ingest.h include/matfact_b200.h
+	@mkdir -p build
+	$(CC) $(CFLAGS) -O3 -c $< -o $@
 
 $(LIB): $(OBJS)
 	$(NVCC) $(ARCH) -shared -o $@ $(OBJS) -ldl

@@ -172,8 +172,24 @@ void mfgpu_comm_destroy(mfgpu_comm *comm);
 int mfgpu_split_users(int users, int nnz, const mfgpu_entry *entries, int nshards, int *cut);
 /* The reference's initialisation, kept on the host: srandom(0), L then R_init
  * drawn as (double)random()/RAND_MAX/features, R stored transposed
- * (mat2d.c:61-72,115-124; matFact.c:113-120). */
+ * (mat2d.c:61-72,115-124; matFact.c:113-120).  The draws come from a lock-free
+ * restatement of glibc's generator (host/mf_ingest.c), identical draw for draw, and R is
+ * written straight into its transposed layout a cache line of features at a time. */
 void mfgpu_random_fill_LR(int users, int items, int features, double *L, double *R);
+/* The input parser of the reference's main (matFact.c:72-110: fscanf "%d", "%lf", "%d",
+ * "%d %d %d", then non_zero x "%d %d %lf"; util.c:12-34) over the file read in one piece,
+ * with the acceptance of glibc's fscanf for every token (host/mf_ingest.c, pinned by a
+ * differential test against fscanf).  Returns 0 and a malloc'ed entry list (release it with
+ * mfgpu_free), or the class of the first error: mfgpu_read_error(rc) is the reference's
+ * die() message for it ("Unable to open input file.", "Error in int argument.", ...). */
+int mfgpu_read_instance(const char *path, int *iters, double *alpha, int *features,
+                        int *users, int *items, int *non_zero, mfgpu_entry **entries);
+const char *mfgpu_read_error(int rc);
+void mfgpu_free(void *p);
+/* n draws of the library's restatement of glibc's random() after srandom(seed) compared with
+ * the C library's own: index of the first difference, -1 if none (self-test of the
+ * initialisation sequence on the machine at hand; uses the process-wide srandom state). */
+long mfgpu_selftest_random(unsigned seed, long n);
 /* Rated-item mask of print_output for user range [0, users): fills
  * mask_count[i] and first_free[i]; returns total matched entries or <0. */
 int mfgpu_mask_stats(int users, int items, int nnz, const mfgpu_entry *entries,

@@ -33,6 +33,7 @@ EXPORTS = [
     "mfgpu_plan_profile_kernels", "mfgpu_plan_kernel_bytes", "mfgpu_plan_timer_start", "mfgpu_plan_timer_stop",
     "mfgpu_comm_unique_id", "mfgpu_comm_create", "mfgpu_comm_destroy",
     "mfgpu_split_users", "mfgpu_random_fill_LR", "mfgpu_mask_stats",
+    "mfgpu_read_instance", "mfgpu_read_error", "mfgpu_free", "mfgpu_selftest_random",
 ]
 
 UID_BYTES = 128
@@ -96,6 +97,15 @@ def lib():
     L.mfgpu_split_users.argtypes = [i, i, vp, i, vp]
     L.mfgpu_random_fill_LR.argtypes = [i, i, i, vp, vp]
     L.mfgpu_random_fill_LR.restype = None
+    L.mfgpu_read_instance.argtypes = [cp, ctypes.POINTER(i), ctypes.POINTER(ctypes.c_double), ctypes.POINTER(i),
+                                      ctypes.POINTER(i), ctypes.POINTER(i), ctypes.POINTER(i),
+                                      ctypes.POINTER(vp)]
+    L.mfgpu_read_error.argtypes = [i]
+    L.mfgpu_read_error.restype = cp
+    L.mfgpu_free.argtypes = [vp]
+    L.mfgpu_free.restype = None
+    L.mfgpu_selftest_random.argtypes = [ctypes.c_uint, ctypes.c_long]
+    L.mfgpu_selftest_random.restype = ctypes.c_long
     L.mfgpu_mask_stats.argtypes = [i, i, i, vp, vp, vp]
     _lib = L
     return L
@@ -120,6 +130,31 @@ def _f64(a, shape):
 
 def device_count() -> int:
     return lib().mfgpu_device_count()
+
+
+def read_instance(path):
+    """The library's parser (the reference's fscanf sequence, matFact.c:72-110): returns
+    (iters, alpha, features, users, items, entries) or raises MatFactError carrying the
+    reference's die() message for the first error."""
+    it, f, u, m, nz = (ctypes.c_int() for _ in range(5))
+    al = ctypes.c_double()
+    ent = ctypes.c_void_p()
+    rc = lib().mfgpu_read_instance(str(path).encode(), ctypes.byref(it), ctypes.byref(al), ctypes.byref(f),
+                                   ctypes.byref(u), ctypes.byref(m), ctypes.byref(nz), ctypes.byref(ent))
+    if rc != 0:
+        raise MatFactError(rc, lib().mfgpu_read_error(rc).decode())
+    try:
+        buf = (ctypes.c_char * (16 * nz.value)).from_address(ent.value) if nz.value else b""
+        entries = np.frombuffer(bytes(buf), dtype=ENTRY_DTYPE).copy()
+    finally:
+        lib().mfgpu_free(ent)
+    return it.value, al.value, f.value, u.value, m.value, entries
+
+
+def selftest_random(seed=0, n=1_000_000):
+    """Index of the first draw where the library's restatement of glibc's random() differs from
+    the C library's own after srandom(seed); -1 if the first n agree."""
+    return lib().mfgpu_selftest_random(seed, n)
 
 
 def random_fill_LR(users, items, features):

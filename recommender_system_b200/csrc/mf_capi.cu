@@ -9,6 +9,7 @@
  * file: without an sm_100 device every compute entry returns MFGPU_ENODEV.
  */
 #include "mf_internal.h"
+#include "../host/mf_ingest.h"
 
 #include <dlfcn.h>
 #include <stdlib.h>
@@ -146,13 +147,42 @@ extern "C" int mfgpu_split_users(int users, int nnz, const mfgpu_entry *entries,
  * mat2d_transpose (mat2d.c:115-124, matFact.c:118-120) would give it. */
 extern "C" void mfgpu_random_fill_LR(int users, int items, int features, double *L, double *R)
 {
-	const double norm = (double)features;
-	srandom(0);
-	for (long n = 0, e = (long)users * features; n < e; n++)
-		L[n] = ((double)random() / (double)RAND_MAX) / norm;
-	for (int k = 0; k < features; k++)
-		for (long j = 0; j < items; j++)
-			R[j * features + k] = ((double)random() / (double)RAND_MAX) / norm;
+	mf_random_fill_LR(users, items, features, L, R);      /* host/mf_ingest.c */
+}
+
+extern "C" int mfgpu_read_instance(const char *path, int *iters, double *alpha, int *features,
+                                   int *users, int *items, int *non_zero, mfgpu_entry **entries)
+{
+	if (!path || !iters || !alpha || !features || !users || !items || !non_zero || !entries)
+		return MF_PARSE_OPEN;
+	mf_instance in;
+	const int rc = mf_parse_instance(path, &in);
+	*entries = nullptr;
+	if (rc != MF_PARSE_OK)
+		return rc;
+	*iters = in.iters;
+	*alpha = in.alpha;
+	*features = in.features;
+	*users = in.users;
+	*items = in.items;
+	*non_zero = in.non_zero;
+	*entries = in.entries;
+	return 0;
+}
+
+extern "C" const char *mfgpu_read_error(int rc) { return mf_parse_message(rc); }
+
+extern "C" void mfgpu_free(void *p) { free(p); }
+
+extern "C" long mfgpu_selftest_random(unsigned seed, long n)
+{
+	mf_rand g;
+	mf_rand_seed(&g, seed);
+	srandom(seed);
+	for (long i = 0; i < n; i++)
+		if ((long)mf_rand_next(&g) != random())
+			return i;
+	return -1;
 }
 
 extern "C" int mfgpu_mask_stats(int users, int items, int nnz, const mfgpu_entry *entries,

@@ -47,31 +47,13 @@ int main(int argc, char **argv)
 		die("Missing input file name.");
 	}
 	const double t_start = now_s();
-	FILE *fp = fopen(argv[1], "r");
-	if (fp == NULL)
-		die("Unable to open input file.");
-
+	/* matFact.c:72-110 / util.c:12-34: same tokens accepted, same message for the first error */
 	int iters, features, users, items, non_zero;
 	double alpha;
-	if (fscanf(fp, "%d", &iters) != 1)
-		die("Error in int argument.");
-	if (fscanf(fp, "%lf", &alpha) != 1)
-		die("Error in double argument.");
-	if (fscanf(fp, "%d", &features) != 1)
-		die("Error in int argument.");
-	if (fscanf(fp, "%d %d %d", &users, &items, &non_zero) != 3)
-		die("Error in multiple int argument.");
-	if (users < 0 || items < 0 || non_zero < 0 || features < 0)
-		die("Error in multiple int argument.");
-
-	mfgpu_entry *entries = malloc(sizeof *entries * (non_zero > 0 ? (size_t)non_zero : 1));
-	if (!entries)
-		die("Out of memory.");
-	for (int n = 0; n < non_zero; n++)
-		if (fscanf(fp, "%d %d %lf", &entries[n].row, &entries[n].col, &entries[n].value) != 3)
-			die("Error in non-zero entry.");
-	if (fclose(fp) == EOF)
-		die("Unable to close input file.");
+	mfgpu_entry *entries = NULL;
+	const int prc = mfgpu_read_instance(argv[1], &iters, &alpha, &features, &users, &items, &non_zero, &entries);
+	if (prc != 0)
+		die(mfgpu_read_error(prc));
 	const double t_parsed = now_s();
 
 	const size_t nl = (size_t)users * features, nr = (size_t)items * features;
@@ -120,6 +102,6 @@ int main(int argc, char **argv)
 	free(best);
 	free(R);
 	free(L);
-	free(entries);
+	mfgpu_free(entries);
 	return 0;
 }

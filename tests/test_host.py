@@ -184,3 +184,48 @@ def test_threaded_pattern_build_is_deterministic(tmp_path):
                     os.path.join(ROOT, "recommender_system_b200", "host", "mf_prep.c"), "-lpthread"], check=True)
     p = subprocess.run([exe], capture_output=True, text=True)
     assert p.returncode == 0 and p.stdout.strip().endswith("OK"), p.stdout
+
+
+def test_host_ingest_matches_the_c_library(tmp_path):
+    """host/mf_ingest.c: the lock-free restatement of glibc's random() equals
+    srandom()/random() draw for draw, mf_random_fill_LR equals the reference's init sequence bit for
+    bit, and the buffer parser classifies 200 000 fuzzed inputs exactly like the reference's fscanf
+    sequence and returns the same values (tests/ingest_check.c)."""
+    exe = str(tmp_path / "ingest_check")
+    subprocess.run(["gcc", "-O2", "-Wall", "-Wextra", "-I" + os.path.join(ROOT, "include"),
+                    "-I" + os.path.join(ROOT, "recommender_system_b200", "host"), "-o", exe,
+                    os.path.join(ROOT, "tests", "ingest_check.c"),
+                    os.path.join(ROOT, "recommender_system_b200", "host", "mf_ingest.c")], check=True)
+    p = subprocess.run([exe], capture_output=True, text=True)
+    assert p.returncode == 0 and p.stdout.strip().endswith("OK"), p.stdout[-2000:]
+
+
+def test_library_parser_reads_the_samples_and_reports_reference_errors(built_lib, tmp_path):
+    """mfgpu_read_instance through the C ABI: equal to the Python reader on the reference's
+    samples; the reference's die() messages for broken files (util.c:12-34, matFact.c:69-70)."""
+    import gzip
+    api = built_lib
+    for name in ("inst30-40-10-2-10.in", "inst0.in", "inst1.in", "inst2.in"):
+        path = os.path.join(ROOT, "tests", "golden", name)
+        inst = mfio.read_instance(path)
+        it, al, f, u, m, ent = api.read_instance(path)
+        assert (it, al, f, u, m) == (inst.iters, inst.alpha, inst.features, inst.users, inst.items)
+        assert np.array_equal(ent, inst.entries)
+    big = tmp_path / "ml100k.in"
+    with gzip.open(os.path.join(ROOT, "tests", "golden", "instML100k.in.gz"), "rb") as fh:
+        big.write_bytes(fh.read())
+    inst = mfio.read_instance(str(big))
+    it, al, f, u, m, ent = api.read_instance(str(big))
+    assert (it, al, f, u, m) == (inst.iters, inst.alpha, inst.features, inst.users, inst.items)
+    assert np.array_equal(ent, inst.entries)
+    cases = {"": "Error in int argument.", "10 x": "Error in double argument.",
+             "10 0.1 y": "Error in int argument.", "10 0.1 2 3 4": "Error in multiple int argument.",
+             "10 0.1 2 3 4 2 0 0 1.0 1": "Error in non-zero entry."}
+    for text, msg in cases.items():
+        bad = tmp_path / "bad.in"
+        bad.write_text(text)
+        with pytest.raises(api.MatFactError, match=msg.replace(".", r"\.")):
+            api.read_instance(str(bad))
+    with pytest.raises(api.MatFactError, match="Unable to open input file"):
+        api.read_instance(str(tmp_path / "missing.in"))
+    assert api.selftest_random(0, 200000) == -1 and api.selftest_random(7, 1000) == -1
