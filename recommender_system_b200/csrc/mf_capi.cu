@@ -129,6 +129,7 @@ extern "C" void mfgpu_comm_destroy(mfgpu_comm *c)
 {
 	if (!c)
 		return;
+	mf_arena_reset(c);               /* collective, like the destruction of the communicator */
 	if (c->nccl && g_nccl.handle)
 		g_nccl.CommDestroy(c->nccl);
 	delete c;

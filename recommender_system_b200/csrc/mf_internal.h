@@ -38,10 +38,30 @@ struct mf_nccl_api {
 	const char *(*GetErrorString)(int);
 };
 
+/* Exchange buffers of a rank, kept by the communicator from one plan to the next: the two G
+ * buffers, the two replicas of R, the flag block, and the peer mappings of all of them (CUDA
+ * IPC).  cudaMalloc / cudaIpcOpenMemHandle / cudaFree of these cost tens of milliseconds per
+ * plan on eight ranks; a plan whose sizes fit borrows them instead (mf_plan.cu).  Identical on
+ * every rank by construction: all ranks create the same plans in the same order. */
+struct mf_xchg_arena {
+	size_t g_bytes, r_bytes;                /* capacity of each G / R buffer          */
+	double *G[2], *R[2];
+	unsigned long long *sync;
+	int mapped;                             /* 0 not tried, 1 peers mapped, -1 IPC unavailable */
+	double *peer_G[2][MF_MAX_SHARDS], *peer_R[2][MF_MAX_SHARDS];
+	unsigned long long *peer_sync[MF_MAX_SHARDS];
+	void *ipc_mapped[5 * MF_MAX_SHARDS];
+	int n_ipc_mapped;
+	int in_use;                             /* a live plan has borrowed it            */
+};
+
 struct mfgpu_comm {
 	int nranks, rank, device;
 	mf_ncclComm_t nccl;
+	mf_xchg_arena arena;
 };
+
+void mf_arena_reset(mfgpu_comm *c);        /* mf_plan.cu; collective over the ranks */
 
 struct mf_shard {
 	int dev;
@@ -57,6 +77,7 @@ struct mf_shard {
 	int *d_contrib;                          /* rank mode: per touched item, bit h = rank h has a nonzero in it */
 	double *G_scratch;                       /* profiling launches of the chain kernels write here */
 	int r_plain;                             /* 1: R[] from cudaMalloc (exportable over CUDA IPC), 0: from the pool */
+	int borrowed;                            /* 1: G[], R[] belong to the communicator's arena */
 	int *d_chunk_row, *d_chunk_pos;          /* chunks of the long rows (k_dot) */
 	/* factors, double buffered; L holds the shard's users only */
 	double *L[2], *R[2];
@@ -104,6 +125,7 @@ struct mfgpu_plan {
 	 *      one 16-byte store and the readers poll for the tag of the iteration: no fences, no
 	 *      flag words; one launch (k_xchg_ll) reduces the own block and unpacks the others' */
 	int xchg_ipc;
+	mf_xchg_arena *arena;                          /* borrowed exchange buffers, or NULL (own) */
 	int slots_per_rank;                            /* push: touched items reduced by one rank (the last may own fewer) */
 	double *peer_G[2][MF_MAX_SHARDS];              /* G[b] of rank h (own rank: the local buffer) */
 	double *peer_R[2][MF_MAX_SHARDS];              /* R[b] of rank h */

@@ -289,6 +289,56 @@ int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
 	return MFGPU_OK;
 }
 
+/* ---- rank mode: the communicator's exchange arena (mf_internal.h) ---------------------- */
+
+/* Collective: unmap the peers' buffers and free the own ones.  Nobody may do that while a peer's
+ * kernels can still touch them, hence the one-word all-reduce as a barrier first. */
+void mf_arena_reset(mfgpu_comm *c)
+{
+	mf_xchg_arena *ar = &c->arena;
+	if (!ar->G[0] && !ar->sync)
+		return;
+	cudaSetDevice(c->device);
+	cudaDeviceSynchronize();
+	if (ar->sync && g_nccl.handle && c->nccl &&
+	    g_nccl.AllReduce((int *)ar->sync + 14, (int *)ar->sync + 14, 1, 2, 0, c->nccl, 0) == 0)
+		cudaDeviceSynchronize();
+	for (int k = 0; k < ar->n_ipc_mapped; k++)
+		cudaIpcCloseMemHandle(ar->ipc_mapped[k]);
+	for (int b = 0; b < 2; b++) {
+		cudaFree(ar->G[b]);
+		cudaFree(ar->R[b]);
+	}
+	cudaFree(ar->sync);
+	cudaGetLastError();
+	memset(ar, 0, sizeof *ar);
+}
+
+/* Buffers of at least the given sizes for a new plan of this communicator: the arena's when no
+ * live plan holds it (re-created, collectively, when it is too small), else nothing (the plan
+ * allocates its own). */
+static int arena_borrow(mfgpu_comm *c, size_t gbytes, size_t rbytes, mf_xchg_arena **out)
+{
+	mf_xchg_arena *ar = &c->arena;
+	*out = nullptr;
+	if (ar->in_use)
+		return MFGPU_OK;
+	if (!ar->G[0] || ar->g_bytes < gbytes || ar->r_bytes < rbytes) {
+		mf_arena_reset(c);
+		for (int b = 0; b < 2; b++) {
+			CK(cudaMalloc((void **)&ar->G[b], gbytes));
+			CK(cudaMalloc((void **)&ar->R[b], rbytes));
+		}
+		CK(cudaMalloc((void **)&ar->sync, MF_SYNC_WORDS * sizeof(unsigned long long)));
+		CK(cudaMemset(ar->sync, 0, MF_SYNC_WORDS * sizeof(unsigned long long)));
+		ar->g_bytes = gbytes;
+		ar->r_bytes = rbytes;
+	}
+	ar->in_use = 1;
+	*out = ar;
+	return MFGPU_OK;
+}
+
 static int shard_create(mfgpu_plan *pl, mf_shard *s, int dev, const mfgpu_entry *entries,
                         const int *item_slot, const int *touched_item, const int *contrib)
 {
@@ -339,9 +389,15 @@ static int shard_create(mfgpu_plan *pl, mf_shard *s, int dev, const mfgpu_entry 
 	/* rank mode: peers store their rows of R_new straight into this replica (push exchange), so
 	 * R must be exportable over CUDA IPC, which pool memory is not */
 	s->r_plain = pl->comm != nullptr;
+	if (pl->comm && pl->nshards > 1) {
+		TRY(arena_borrow(pl->comm, mf_g_bytes(pl), rbytes, &pl->arena));
+		s->borrowed = pl->arena != nullptr;
+	}
 	for (int b = 0; b < 2; b++) {
 		TRY(dev_alloc((void **)&s->L[b], lbytes, s->st));
-		if (s->r_plain)
+		if (s->borrowed)
+			s->R[b] = pl->arena->R[b];
+		else if (s->r_plain)
 			CK(cudaMalloc((void **)&s->R[b], rbytes));
 		else
 			TRY(dev_alloc((void **)&s->R[b], rbytes, s->st));
@@ -371,7 +427,10 @@ static int shard_create(mfgpu_plan *pl, mf_shard *s, int dev, const mfgpu_entry 
 		 * blocks of slots_per_rank rows (one block per contributing rank) */
 		const size_t gbytes = mf_g_bytes(pl);
 		for (int b = 0; b < 2; b++) {
-			CK(cudaMalloc((void **)&s->G[b], gbytes));
+			if (s->borrowed)
+				s->G[b] = pl->arena->G[b];
+			else
+				CK(cudaMalloc((void **)&s->G[b], gbytes));
 			/* columns without a local nonzero are never written: they stay 0.0 */
 			CK(cudaMemsetAsync(s->G[b], 0, gbytes, s->st));
 		}
@@ -410,11 +469,15 @@ static void shard_destroy(mf_shard *s)
 		if (s->ev_g[g]) cudaEventDestroy(s->ev_g[g]);
 		if (g == 0) cudaFree(s->G_scratch);
 		dev_free(s->L[g], s->st);
-		if (s->r_plain)
+		if (s->borrowed)
+			;                                   /* the communicator's arena keeps G and R */
+		else if (s->r_plain) {
 			cudaFree(s->R[g]);
-		else
+			cudaFree(s->G[g]);
+		} else {
 			dev_free(s->R[g], s->st);
-		cudaFree(s->G[g]);
+			cudaFree(s->G[g]);
+		}
 	}
 	tc.lap("destroy: factor buffers");
 	void *ptrs[] = {s->d_row_id, s->d_row_ptr, s->d_col_idx, s->d_epos, s->d_col_id, s->d_col_ptr,
@@ -481,8 +544,28 @@ int mf_xchg_setup(mfgpu_plan *pl)
 		CK(cudaMemsetAsync(s->G[b], 0, mf_g_bytes(pl), s->st));
 	if (pl->opt_exchange == 0)
 		return MFGPU_OK;
-	CK(cudaMalloc((void **)&pl->d_sync, MF_SYNC_WORDS * sizeof(unsigned long long)));
+	mf_xchg_arena *ar = pl->arena;
+	if (ar && ar->mapped < 0)
+		return MFGPU_OK;                 /* IPC was found unavailable before: ncclAllReduce */
+	if (ar)
+		pl->d_sync = ar->sync;
+	else
+		CK(cudaMalloc((void **)&pl->d_sync, MF_SYNC_WORDS * sizeof(unsigned long long)));
 	CK(cudaMemsetAsync(pl->d_sync, 0, MF_SYNC_WORDS * sizeof(unsigned long long), s->st));
+	if (ar && ar->mapped > 0) {
+		/* the peers' buffers are mapped already: only the barrier after the clean-up above */
+		for (int h = 0; h < n; h++) {
+			for (int b = 0; b < 2; b++) {
+				pl->peer_G[b][h] = ar->peer_G[b][h];
+				pl->peer_R[b][h] = ar->peer_R[b][h];
+			}
+			pl->peer_sync[h] = ar->peer_sync[h];
+		}
+		if (!xchg_all_ok(pl, s, 1, (int *)pl->d_sync + 14))
+			return mf_fail(MFGPU_ECOMM, "exchange set-up: barrier failed");
+		pl->xchg_ipc = pl->opt_exchange == 2 ? 1 : pl->opt_exchange == 3 ? 2 : 3;
+		return MFGPU_OK;
+	}
 
 	XchgHandles mine;
 	memset(&mine, 0, sizeof mine);
@@ -538,9 +621,27 @@ int mf_xchg_setup(mfgpu_plan *pl)
 			cudaIpcCloseMemHandle(pl->ipc_mapped[k]);
 		pl->n_ipc_mapped = 0;
 		cudaGetLastError();
+		if (ar) {
+			ar->mapped = -1;
+			pl->d_sync = nullptr;
+		}
 		if (pl->opt_exchange > 0 && getenv("MFGPU_TRACE"))
 			fprintf(stderr, "[mfgpu] peer-memory exchange unavailable, using ncclAllReduce\n");
 		return MFGPU_OK;
+	}
+	if (ar) {
+		/* the mappings now belong to the arena and outlive this plan */
+		for (int h = 0; h < n; h++) {
+			for (int b = 0; b < 2; b++) {
+				ar->peer_G[b][h] = pl->peer_G[b][h];
+				ar->peer_R[b][h] = pl->peer_R[b][h];
+			}
+			ar->peer_sync[h] = pl->peer_sync[h];
+		}
+		memcpy(ar->ipc_mapped, pl->ipc_mapped, sizeof(void *) * (size_t)pl->n_ipc_mapped);
+		ar->n_ipc_mapped = pl->n_ipc_mapped;
+		pl->n_ipc_mapped = 0;
+		ar->mapped = 1;
 	}
 	/* option exchange: 2 = pull kernel, 3 = push with fences and flags, else low latency */
 	pl->xchg_ipc = pl->opt_exchange == 2 ? 1 : pl->opt_exchange == 3 ? 2 : 3;
@@ -565,7 +666,8 @@ void mf_xchg_teardown(mfgpu_plan *pl)
 	for (int k = 0; k < pl->n_ipc_mapped; k++)
 		cudaIpcCloseMemHandle(pl->ipc_mapped[k]);
 	pl->n_ipc_mapped = 0;
-	cudaFree(pl->d_sync);
+	if (!pl->arena)
+		cudaFree(pl->d_sync);            /* else the flag block is the arena's */
 	pl->d_sync = nullptr;
 	pl->xchg_ipc = 0;
 	cudaGetLastError();
@@ -728,6 +830,8 @@ extern "C" void mfgpu_plan_destroy(mfgpu_plan *pl)
 	for (int g = 0; g < n; g++)
 		if (pl->sh[g].dev >= 0)
 			shard_destroy(&pl->sh[g]);
+	if (pl->arena)
+		pl->arena->in_use = 0;       /* the next plan of this communicator may borrow it */
 	delete pl;
 }
 

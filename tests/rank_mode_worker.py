@@ -21,12 +21,31 @@ def main():
     uid = [api.Comm.unique_id() if rank == 0 else None]
     dist.broadcast_object_list(uid, src=0)
     comm = api.Comm(world, rank, uid[0], local)
+    how = sys.argv[2] if len(sys.argv) > 2 else "ll"
+
+    def set_how(p):
+        if how != "ll":
+            p.set_option("exchange", {"nccl": 0, "pull": 2, "push": 3}[how])
+
+    # a smaller problem first: the communicator keeps its exchange buffers, the plans below
+    # find them too small (re-created) and then, the second time round, reuse them as they are
+    small = synth.random_instance(60, 50, 6, 0.2, 5, 0.002, seed=5)
+    Ls, Rs = api.random_fill_LR(small.users, small.items, small.features)
+    with api.Plan(small.users, small.items, small.features, small.entries, small.alpha, comm=comm) as p0:
+        set_how(p0)
+        p0.set_factors(Ls, Rs)
+        p0.iterate(5)
+        p0.sync()
     inst = synth.random_instance(300, 200, 20, 0.1, 25, 0.002, seed=33)
     L, R = api.random_fill_LR(inst.users, inst.items, inst.features)
+    L1, R1 = L.copy(), R.copy()
+    with api.Plan(inst.users, inst.items, inst.features, inst.entries, inst.alpha, comm=comm) as p1:
+        set_how(p1)
+        p1.set_factors(L1, R1)
+        p1.iterate(25)
+        p1.get_factors(L1, R1)
     plan = api.Plan(inst.users, inst.items, inst.features, inst.entries, inst.alpha, comm=comm)
-    how = sys.argv[2] if len(sys.argv) > 2 else "ll"
-    if how != "ll":
-        plan.set_option("exchange", {"nccl": 0, "pull": 2, "push": 3}[how])
+    set_how(plan)
     kind = plan.exchange_kind()
     plan.set_factors(L, R)
     plan.iterate(17)           # graph path (16) + one direct iteration
@@ -35,6 +54,9 @@ def main():
     plan.get_factors(L, R)
     best = plan.recommend()
     plan.close()
+    # the plan that reused the buffers of the one before it gives the same doubles
+    assert np.array_equal(R.view(np.uint64), R1.view(np.uint64)), "second plan on the same communicator differs"
+    assert np.array_equal(L[lo:hi].view(np.uint64), L1[lo:hi].view(np.uint64))
     comm.close()
     parts = [None] * world
     dist.all_gather_object(parts, (lo, hi, L[lo:hi].copy(), best[lo:hi].copy(), R.copy()))
