@@ -170,6 +170,12 @@ void mfgpu_comm_destroy(mfgpu_comm *comm);
 
 /* Contiguous user ranges with balanced nonzero counts; cut has nshards+1 ints. */
 int mfgpu_split_users(int users, int nnz, const mfgpu_entry *entries, int nshards, int *cut);
+/* Layout of the rank-mode exchange for `nranks` ranks (mfgpu_split_users cut): item_slot[j] =
+ * position of item j among the items with a nonzero (-1: none), contrib[slot] = bit r set when
+ * rank r holds a nonzero of that item (contrib needs room for `items` ints).  Slot t is reduced
+ * by rank t / slots_per_rank.  Returns the number of touched items or < 0. */
+int mfgpu_exchange_layout(int users, int items, int nnz, const mfgpu_entry *entries, int nranks,
+                          int *item_slot, int *contrib, int *slots_per_rank);
 /* The reference's initialisation, kept on the host: srandom(0), L then R_init
  * drawn as (double)random()/RAND_MAX/features, R stored transposed
  * (mat2d.c:61-72,115-124; matFact.c:113-120).  The draws come from a lock-free

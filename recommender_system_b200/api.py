@@ -34,6 +34,7 @@ EXPORTS = [
     "mfgpu_comm_unique_id", "mfgpu_comm_create", "mfgpu_comm_destroy",
     "mfgpu_split_users", "mfgpu_random_fill_LR", "mfgpu_mask_stats",
     "mfgpu_read_instance", "mfgpu_read_error", "mfgpu_free", "mfgpu_selftest_random",
+    "mfgpu_exchange_layout",
 ]
 
 UID_BYTES = 128
@@ -106,6 +107,7 @@ def lib():
     L.mfgpu_free.restype = None
     L.mfgpu_selftest_random.argtypes = [ctypes.c_uint, ctypes.c_long]
     L.mfgpu_selftest_random.restype = ctypes.c_long
+    L.mfgpu_exchange_layout.argtypes = [i, i, i, vp, i, vp, vp, ctypes.POINTER(i)]
     L.mfgpu_mask_stats.argtypes = [i, i, i, vp, vp, vp]
     _lib = L
     return L
@@ -149,6 +151,21 @@ def read_instance(path):
     finally:
         lib().mfgpu_free(ent)
     return it.value, al.value, f.value, u.value, m.value, entries
+
+
+def exchange_layout(users, items, entries, nranks):
+    """Rank-mode exchange layout (host/mf_prep.c): (item_slot[items], contrib[n_touched],
+    slots_per_rank).  Touched item of slot t is reduced by rank t // slots_per_rank; bit r of
+    contrib[t] = rank r holds a nonzero of it."""
+    e = _entries(entries)
+    slot = np.empty(max(items, 1), dtype=np.int32)
+    contrib = np.zeros(max(items, 1), dtype=np.int32)
+    per = ctypes.c_int()
+    n = lib().mfgpu_exchange_layout(users, items, len(e), e.ctypes.data, nranks, slot.ctypes.data,
+                                    contrib.ctypes.data, ctypes.byref(per))
+    if n < 0:
+        raise MatFactError(n, lib().mfgpu_last_error().decode())
+    return slot[:items], contrib[:n], per.value
 
 
 def selftest_random(seed=0, n=1_000_000):

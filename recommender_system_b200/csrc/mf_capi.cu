@@ -143,6 +143,25 @@ extern "C" int mfgpu_split_users(int users, int nnz, const mfgpu_entry *entries,
 	return rc == MFGPU_OK ? rc : fail(rc, "mfgpu_split_users: bad argument");
 }
 
+extern "C" int mfgpu_exchange_layout(int users, int items, int nnz, const mfgpu_entry *entries, int nranks,
+                                     int *item_slot, int *contrib, int *slots_per_rank)
+{
+	if (!item_slot || !contrib || !slots_per_rank || nranks < 1 || nranks > MF_MAX_SHARDS || items < 0)
+		return fail(MFGPU_EINVAL, "mfgpu_exchange_layout: bad argument");
+	int cut[MF_MAX_SHARDS + 1];
+	int rc = mf_split_users(users, nnz, entries, nranks, cut);
+	if (rc != MFGPU_OK)
+		return fail(rc, "mfgpu_exchange_layout: bad argument");
+	const int cnt = mf_touched_items(items, nnz, entries, item_slot);
+	if (cnt < 0)
+		return fail(cnt, "mfgpu_exchange_layout: an entry lies outside the users x items matrix");
+	const int per = mf_exchange_layout(users, nnz, entries, nranks, cut, item_slot, cnt, contrib);
+	if (per < 0)
+		return fail(per, "mfgpu_exchange_layout: bad argument");
+	*slots_per_rank = per;
+	return cnt;
+}
+
 /* mat2d.c:61-72 (draw order: all of L row-major, then R_init = features x items
  * row-major) with R written straight into the transposed position that
  * mat2d_transpose (mat2d.c:115-124, matFact.c:118-120) would give it. */

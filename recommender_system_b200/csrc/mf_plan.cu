@@ -737,20 +737,17 @@ static int plan_create(mfgpu_plan **out, int users, int items, int features, int
 						if (item_slot[j] >= 0)
 							touched[item_slot[j]] = j;
 				if (rc == MFGPU_OK && comm) {
-					/* which ranks hold a nonzero of each touched item (rank of a user: cut[]) */
+					/* blocks of touched items per reducing rank, contributors of every item */
 					contrib = (int *)calloc((size_t)(cnt ? cnt : 1), sizeof(int));
 					if (!contrib)
 						rc = MFGPU_ENOMEM;
-					else
-						for (int n = 0; n < nnz; n++) {
-							const int u = entries[n].row;
-							if (u < 0 || u >= users) {
-								rc = MFGPU_EINVAL;
-								break;
-							}
-							const int r = (int)(std::upper_bound(pl->cut, pl->cut + nshards + 1, u) - pl->cut) - 1;
-							contrib[item_slot[entries[n].col]] |= 1 << r;
-						}
+					else {
+						const int per = mf_exchange_layout(users, nnz, entries, nshards, pl->cut, item_slot, cnt, contrib);
+						if (per < 0)
+							rc = per;
+						else
+							pl->slots_per_rank = per;
+					}
 				}
 			}
 		}

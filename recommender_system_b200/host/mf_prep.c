@@ -409,3 +409,36 @@ int mf_touched_items(int items, int nnz, const mfgpu_entry *entries, int *item_s
 			item_slot[j] = cnt++;
 	return cnt;
 }
+
+/* Layout of the rank-mode exchange (csrc/mf_iter.cu, k_xchg_ll / k_reduce_bcast): the touched
+ * items (item_slot >= 0, mf_touched_items) are dealt to the ranks in blocks of
+ * per = ceil(n_touched / nranks) consecutive slots -- rank slot / per adds up the
+ * contributions to the item and stores its new row into every replica -- and contrib[slot]
+ * has bit r set when rank r (users [cut[r], cut[r+1])) holds a nonzero of the item: the only
+ * contributions the reducing rank waits for.  Returns per, or an MFGPU_E* code (< 0). */
+int mf_exchange_layout(int users, int nnz, const mfgpu_entry *entries, int nranks, const int *cut,
+                       const int *item_slot, int n_touched, int *contrib)
+{
+	if (nranks < 1 || nranks > 31 || n_touched < 0 || !cut || !item_slot || !contrib)
+		return MFGPU_EINVAL;
+	for (int t = 0; t < n_touched; t++)
+		contrib[t] = 0;
+	int r = 0;
+	for (int n = 0; n < nnz; n++) {
+		const int u = entries[n].row;
+		if (u < 0 || u >= users)
+			return MFGPU_EINVAL;
+		/* entries usually come sorted by user: the rank of the previous one is a good guess */
+		while (r + 1 < nranks && u >= cut[r + 1])      /* cut[nranks] = users > u */
+			r++;
+		while (r > 0 && u < cut[r])                    /* cut[0] = 0 <= u */
+			r--;
+		const int t = item_slot[entries[n].col];
+		if (t < 0 || t >= n_touched)
+			return MFGPU_EINVAL;
+		contrib[t] |= 1 << r;
+	}
+	const int per = (n_touched + nranks - 1) / nranks;
+	return per > 0 ? per : 1;
+}
+

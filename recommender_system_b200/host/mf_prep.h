@@ -79,6 +79,11 @@ int mf_split_users(int users, int nnz, const mfgpu_entry *entries, int nshards, 
  * item_slot[j] = position of item j in that list or -1. */
 int mf_touched_items(int items, int nnz, const mfgpu_entry *entries, int *item_slot);
 
+/* Rank-mode exchange layout: slots per reducing rank (returned) and, per touched item, the set
+ * of ranks that hold a nonzero of it (bit r of contrib[slot]); see mf_prep.c. */
+int mf_exchange_layout(int users, int nnz, const mfgpu_entry *entries, int nranks, const int *cut,
+                       const int *item_slot, int n_touched, int *contrib);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,6 +1,7 @@
 """Kernel-time sweeps on one GPU (development aid, not part of the bench contract).
 
     python tools/tune.py <users> <items> <features> [name=value,name=value ...]
+    python tools/tune.py ml:<users>:<nnz> <items> <features> [...]      (MovieLens-like rows)
 
 Builds an inst60000-like instance of the given shape (10..20 nonzeros per user, seed 12346),
 and for every option set given (comma-separated plan options; '-' = defaults) prints the
@@ -15,9 +16,15 @@ from recommender_system_b200 import api, synth  # noqa: E402
 
 
 def main():
-    U, I, F = int(sys.argv[1]), int(sys.argv[2]), int(sys.argv[3])
+    I, F = int(sys.argv[2]), int(sys.argv[3])
     sets = sys.argv[4:] or ["-"]
-    inst = synth.inst60000_like(users=U, items=I, features=F)
+    if sys.argv[1].startswith("ml:"):
+        _, u, n = sys.argv[1].split(":")
+        U = int(u)
+        inst = synth.ml_like(users=U, items=I, nnz=int(n), features=F)
+    else:
+        U = int(sys.argv[1])
+        inst = synth.inst60000_like(users=U, items=I, features=F)
     L, R = api.random_fill_LR(U, I, F)
     print("U=%d I=%d F=%d nnz=%d" % (U, I, F, inst.nnz), flush=True)
     for opts in sets:
