@@ -315,6 +315,12 @@ def main():
                 "iteration": {"algorithmic_bytes": b_it, "ms": it_ms,
                               "achieved": b_it / (it_ms * 1e-3) / 1e9,
                               "frac": b_it / (it_ms * 1e-3) / 1e9 / peak}}
+    if n_gpus > 1:
+        # kernel_ms.exchange_apply is the exchange launched on its own (for the low-latency
+        # exchange together with a re-send of the contributions); what an iteration pays for the
+        # exchange is what is left of it beside the loop kernels (the longer of each concurrent pair)
+        beside = max(k_ms["k_update_L"], k_ms["k_dot"]) + max(k_ms["k_chain_bulk"], k_ms["k_chain_deep"])
+        roofline["iteration"]["exchange_in_situ_ms"] = max(0.0, it_ms - beside)
     # determinism check outside the timed region: the K-th factorization equals the first
     best = plan.recommend()
     plan.close()
