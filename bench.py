@@ -24,6 +24,7 @@ Workloads (BASELINE.json configs):
 from __future__ import annotations
 
 import argparse
+import ctypes
 import json
 import os
 import sys
@@ -129,6 +130,13 @@ def time_reference(inst, kind, budget_s, threads):
     import pyoracle
     os.environ["OMP_NUM_THREADS"] = str(threads)
     os.environ.setdefault("OMP_PROC_BIND", "close")
+    if kind == "omp" and pyoracle.ref_available(kind):
+        # libgomp reads OMP_NUM_THREADS once; later calls in this process go through its API
+        try:
+            pyoracle._ref_lib(kind)
+            ctypes.CDLL("libgomp.so.1").omp_set_num_threads(int(threads))
+        except OSError:
+            pass
     U, I, F = inst.users, inst.items, inst.features
     L0, R0 = pyoracle.init_LR(U, I, F)
     if pyoracle.ref_available(kind):
@@ -361,6 +369,16 @@ def main():
     cpu = None
     if rank == 0 and n_gpus == 1 and not args.no_cpu_baseline:
         cpu = time_reference(inst, "omp", 15.0, cpu_threads())
+        if args.workload == "ml100k":
+            # the reference's serial and OpenMP programs over the thread counts of its own report
+            # (deliverables/report-omp.pdf Table 2: 1/2/4/8), on this box's host cores; cheap on this
+            # input (its trailing mat2d_prod is 0.1 GFLOP), ~2.5 s each
+            sweep = {"serial": time_reference(inst, "serial", 2.5, 1)["value"]}
+            t = 1
+            while t <= cpu_threads():
+                sweep["omp_%d" % t] = time_reference(inst, "omp", 2.5, t)["value"]
+                t *= 2
+            cpu["by_threads"] = sweep
     if comm:
         comm.close()
     if world > 1:
