@@ -116,7 +116,10 @@ long long mfgpu_plan_launch_count(mfgpu_plan *plan);
 /* How the partial R gradients of the shards meet: 0 = one shard, nothing to exchange;
  * 1 = ncclAllReduce + apply (one process per GPU); 2 = one kernel that reads every rank's
  * gradient over NVLink peer memory (CUDA IPC) and applies the sum (one process per GPU);
- * 3 = the same inside one process driving N GPUs. */
+ * 3 = the same inside one process driving N GPUs; 4 = chain kernels store the gradient rows
+ * into the rank that owns the item, the owner reduces, applies and stores its rows of R_new
+ * into every replica, ordered by fences and flag words; 5 = the same flow with (value, tag)
+ * pairs polled by the readers, one launch (the default of one process per GPU). */
 int mfgpu_plan_exchange_kind(mfgpu_plan *plan);
 /* Algorithmic bytes of ONE iteration, SURVEY.md section 8(d):
  * 16*F*(U_t + I_t) + 12*nnz, with U_t / I_t the users / items having >=1 nonzero. */
@@ -131,7 +134,9 @@ int mfgpu_plan_restore_factors(mfgpu_plan *plan);
  * are left unchanged.  ms[0] = by-user pass of the short rows (k_update_L),
  * ms[1] = dots of the long rows (k_dot), ms[2] / ms[3] = sequential accumulations
  * (k_chain for the bulk of the chains / k_chain_ws for the longest ones), ms[4] =
- * exchange + apply (rank mode, else 0). */
+ * exchange + apply launched on its own (rank mode, else 0; collective: every rank
+ * must call it; for the default exchange the figure includes a re-send of the rank's
+ * contributions, which an iteration does inside its chain kernels). */
 int mfgpu_plan_profile_kernels(mfgpu_plan *plan, int reps, float ms[5]);
 /* Algorithmic (compulsory) bytes of one launch of each of those kernels on shard 0. */
 int mfgpu_plan_kernel_bytes(mfgpu_plan *plan, long long bytes[5]);
@@ -152,6 +157,14 @@ int mfgpu_plan_timer_stop(mfgpu_plan *plan, float *ms);
  *   "res_rows"     n     resident rows per chunk (1..32)
  *   "chain_ws"     1/0   warp-specialised kernel for the longest chains (default 1)
  *   "chain_ring"   1/0   k_chain gathers through a shared-memory ring / registers
+ *   "dot_stages"   2/4   tiles in the dot-phase ring of a k_update_L / k_dot warp (default 2)
+ *   "acc_rows"     1/3   rows in flight ahead of the addition in k_update_L (default 1)
+ *   "exchange"     rank mode only, collective (every rank sets it at the same point):
+ *                        0 ncclAllReduce + apply; otherwise over peer memory (CUDA IPC) when
+ *                        every rank can map the others: 1 or -1 (default) (value, tag) pairs
+ *                        polled by the readers, one launch; 2 pull (one kernel reads every
+ *                        rank's gradient); 3 push with fences and flag words.  The three
+ *                        peer-memory transports add in rank order (bit-identical results).
  * May be set between iterate calls (the plan is reconfigured); unknown names return
  * MFGPU_EINVAL. */
 int mfgpu_plan_set_option(mfgpu_plan *plan, const char *name, int value);
