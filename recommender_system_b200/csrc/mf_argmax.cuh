@@ -76,6 +76,43 @@ k_masked_argmax(const ArgmaxArgs p, const double *__restrict__ L, const double *
 	const int lrow = tid >> 2;            /* 0..63 */
 	const int lk = (tid & 3) * 4;         /* 0,4,8,12 */
 
+	/* The panel after the one being multiplied is already on its way from L2 into registers
+	 * (lv, rv): a panel is 16 steps of 32 FP64 operations per thread, long enough to cover the
+	 * load.  fetch() reads this thread's 4 features of one user row and one item row of panel
+	 * (tile tt, features kk0..); rows / features outside the matrices read as 0.0. */
+	double lv[4], rv[4];
+	auto fetch = [&](int tt, int kk0) {
+		const int kc = min(AM_KC, F - kk0);
+		const int u = u0 + lrow, j = tt * AM_TJ + lrow;
+#pragma unroll
+		for (int q = 0; q < 4; q++)
+			lv[q] = rv[q] = 0.0;
+		if (u < p.users_hi) {
+			const double *src = L + (size_t)(u - p.l_row0) * ld + kk0 + lk;
+			if (lk + 4 <= kc) {               /* rows are 16-byte aligned, kk0 + lk is a multiple of 4 */
+				const double2 x = *reinterpret_cast<const double2 *>(src);
+				const double2 y = *reinterpret_cast<const double2 *>(src + 2);
+				lv[0] = x.x; lv[1] = x.y; lv[2] = y.x; lv[3] = y.y;
+			} else {
+#pragma unroll
+				for (int q = 0; q < 4; q++) if (lk + q < kc) lv[q] = src[q];
+			}
+		}
+		if (j < p.items) {
+			const double *src = R + (size_t)j * ld + kk0 + lk;
+			if (lk + 4 <= kc) {
+				const double2 x = *reinterpret_cast<const double2 *>(src);
+				const double2 y = *reinterpret_cast<const double2 *>(src + 2);
+				rv[0] = x.x; rv[1] = x.y; rv[2] = y.x; rv[3] = y.y;
+			} else {
+#pragma unroll
+				for (int q = 0; q < 4; q++) if (lk + q < kc) rv[q] = src[q];
+			}
+		}
+	};
+	if (t_begin < t_end && F > 0)
+		fetch(t_begin, 0);
+
 	for (int t = t_begin; t < t_end; t++) {
 		const int j0 = t * AM_TJ;
 		double acc[4][4];
@@ -104,27 +141,17 @@ k_masked_argmax(const ArgmaxArgs p, const double *__restrict__ L, const double *
 
 		for (int k0 = 0; k0 < F; k0 += AM_KC) {
 			const int kc = min(AM_KC, F - k0);
-			{
-				const int u = u0 + lrow, j = j0 + lrow;
-				double lv[4] = {0.0, 0.0, 0.0, 0.0}, rv[4] = {0.0, 0.0, 0.0, 0.0};
-				if (u < p.users_hi) {
-					const double *src = L + (size_t)(u - p.l_row0) * ld + k0 + lk;
+			__syncthreads();   /* previous panel fully consumed */
 #pragma unroll
-					for (int q = 0; q < 4; q++) if (lk + q < kc) lv[q] = src[q];
-				}
-				if (j < p.items) {
-					const double *src = R + (size_t)j * ld + k0 + lk;
-#pragma unroll
-					for (int q = 0; q < 4; q++) if (lk + q < kc) rv[q] = src[q];
-				}
-				__syncthreads();   /* previous panel fully consumed */
-#pragma unroll
-				for (int q = 0; q < 4; q++) {
-					Ls[lk + q][lrow] = lv[q];
-					Rs[lk + q][lrow] = rv[q];
-				}
+			for (int q = 0; q < 4; q++) {
+				Ls[lk + q][lrow] = lv[q];
+				Rs[lk + q][lrow] = rv[q];
 			}
 			__syncthreads();
+			if (k0 + AM_KC < F)
+				fetch(t, k0 + AM_KC);
+			else if (t + 1 < t_end)
+				fetch(t + 1, 0);
 			if (kc == AM_KC) {
 #pragma unroll
 				for (int kk = 0; kk < AM_KC; kk++) {
