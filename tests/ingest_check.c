@@ -47,8 +47,11 @@ static int check_rand(void)
 static int check_fill(void)
 {
 	const int shapes[][3] = {{3, 5, 2}, {30, 40, 10}, {7, 100, 8}, {5, 33, 17}, {0, 9, 4},
-	                         {9, 0, 4}, {4, 4, 0}, {100, 1000, 23}, {1, 1, 1}};
-	for (int q = 0; q < 9; q++) {
+	                         {9, 0, 4}, {4, 4, 0}, {100, 1000, 23}, {1, 1, 1},
+	                         /* several blocks of L and of R, several worker threads, block widths
+	                          * of 64 / 36 and of 8 / 1 features */
+	                         {170000, 30000, 100}, {100, 3000000, 9}, {3, 70000, 150}};
+	for (int q = 0; q < 12; q++) {
 		const int U = shapes[q][0], I = shapes[q][1], F = shapes[q][2];
 		const size_t nl = (size_t)U * F, nr = (size_t)I * F;
 		double *L = malloc(8 * (nl + 1)), *R = malloc(8 * (nr + 1));

@@ -195,7 +195,7 @@ def test_host_ingest_matches_the_c_library(tmp_path):
     subprocess.run(["gcc", "-O2", "-Wall", "-Wextra", "-I" + os.path.join(ROOT, "include"),
                     "-I" + os.path.join(ROOT, "recommender_system_b200", "host"), "-o", exe,
                     os.path.join(ROOT, "tests", "ingest_check.c"),
-                    os.path.join(ROOT, "recommender_system_b200", "host", "mf_ingest.c")], check=True)
+                    os.path.join(ROOT, "recommender_system_b200", "host", "mf_ingest.c"), "-lpthread"], check=True)
     p = subprocess.run([exe], capture_output=True, text=True)
     assert p.returncode == 0 and p.stdout.strip().endswith("OK"), p.stdout[-2000:]
 
