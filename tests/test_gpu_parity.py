@@ -175,6 +175,24 @@ def test_full_size_ml1m_shape(gpu, oracle):
     _check_against_oracle(gpu, oracle, inst)
 
 
+# Shapes of the reference's remaining published instances (report-mpi.pdf p.4; inputs missing
+# upstream): synthetic stand-ins with the same users x items x features and
+# nonzeros-per-user range, a few iterations, bit-exact against the oracle.
+OTHER_SHAPES = [
+    # name,                         users, items, F,  per-user nonzeros, iters
+    ("inst1e6-100-700-1-3 (1/10)", 100000, 100, 700, (1, 3), 1),      # wide factors, tiny rows; U scaled 1/10
+    ("inst1000-80000-20-10-1000", 1000, 80000, 20, (10, 1000), 3),    # long ragged rows, short columns
+    ("inst20000-10000-40-2-50", 20000, 10000, 40, (2, 50), 2),
+]
+
+
+@pytest.mark.parametrize("shape", OTHER_SHAPES, ids=[s[0] for s in OTHER_SHAPES])
+def test_other_published_shapes(gpu, oracle, shape):
+    _, U, I, F, (lo, hi), iters = shape
+    inst = synth.inst60000_like(users=U, items=I, features=F, iters=iters, alpha=0.0005, lo=lo, hi=hi, seed=777)
+    _check_against_oracle(gpu, oracle, inst)
+
+
 def test_full_size_inst1000_1e6(gpu, expected):
     """samples/inst1000-1e6-1000-1-3.in as it is: 1e6 items x 1000 features (R = 8 GB per buffer,
     1e9 draws of the init sequence), the configuration whose run time is the masked arg-max over
