@@ -140,6 +140,10 @@ int mfgpu_plan_restore_factors(mfgpu_plan *plan);
 int mfgpu_plan_profile_kernels(mfgpu_plan *plan, int reps, float ms[5]);
 /* Algorithmic (compulsory) bytes of one launch of each of those kernels on shard 0. */
 int mfgpu_plan_kernel_bytes(mfgpu_plan *plan, long long bytes[5]);
+/* Bytes each of those launches requests from L2: as above, but one gathered row of the other
+ * factor for every nonzero and pass instead of once per distinct row (the diagnostic traffic
+ * model of the loop: the gathers, not the compulsory HBM bytes, are what bounds it). */
+int mfgpu_plan_kernel_gather_bytes(mfgpu_plan *plan, long long bytes[5]);
 /* Device stopwatch on the plan's stream(s): start records an event, stop records
  * another, waits for it and returns the elapsed device time (max over the
  * plan's devices).  Everything enqueued on the plan in between is covered. */

@@ -30,7 +30,7 @@ EXPORTS = [
     "mfgpu_plan_last_loop_ms", "mfgpu_plan_recommend", "mfgpu_plan_last_recommend_ms",
     "mfgpu_plan_user_range", "mfgpu_plan_launch_count", "mfgpu_plan_exchange_kind", "mfgpu_plan_bytes_per_iter",
     "mfgpu_plan_set_option", "mfgpu_plan_save_factors", "mfgpu_plan_restore_factors",
-    "mfgpu_plan_profile_kernels", "mfgpu_plan_kernel_bytes", "mfgpu_plan_timer_start", "mfgpu_plan_timer_stop",
+    "mfgpu_plan_profile_kernels", "mfgpu_plan_kernel_bytes", "mfgpu_plan_kernel_gather_bytes", "mfgpu_plan_timer_start", "mfgpu_plan_timer_stop",
     "mfgpu_comm_unique_id", "mfgpu_comm_create", "mfgpu_comm_destroy",
     "mfgpu_split_users", "mfgpu_random_fill_LR", "mfgpu_mask_stats",
     "mfgpu_read_instance", "mfgpu_read_error", "mfgpu_free", "mfgpu_selftest_random",
@@ -89,6 +89,7 @@ def lib():
     L.mfgpu_plan_restore_factors.argtypes = [vp]
     L.mfgpu_plan_profile_kernels.argtypes = [vp, i, ctypes.POINTER(ctypes.c_float)]
     L.mfgpu_plan_kernel_bytes.argtypes = [vp, ctypes.POINTER(ctypes.c_longlong)]
+    L.mfgpu_plan_kernel_gather_bytes.argtypes = [vp, ctypes.POINTER(ctypes.c_longlong)]
     L.mfgpu_plan_timer_start.argtypes = [vp]
     L.mfgpu_plan_timer_stop.argtypes = [vp, ctypes.POINTER(ctypes.c_float)]
     L.mfgpu_comm_unique_id.argtypes = [vp]
@@ -353,6 +354,11 @@ class Plan:
     def kernel_bytes(self):
         b = (ctypes.c_longlong * 5)()
         _check(lib().mfgpu_plan_kernel_bytes(self._h, b))
+        return dict(zip(KERNELS, [int(x) for x in b]))
+
+    def kernel_gather_bytes(self):
+        b = (ctypes.c_longlong * 5)()
+        _check(lib().mfgpu_plan_kernel_gather_bytes(self._h, b))
         return dict(zip(KERNELS, [int(x) for x in b]))
 
     def close(self):

@@ -92,6 +92,7 @@ struct mf_shard {
 	void *host_ws;                           /* page-locked workspace of `pat`, from the arena cache */
 	size_t host_ws_bytes;
 	long long kbytes[5];                     /* algorithmic bytes per launch of each kernel */
+	long long gbytes[5];                     /* bytes each launch requests from L2 (a gathered row per nonzero and pass) */
 	size_t k1_smem;
 	cudaGraphExec_t gexec[2];                /* by starting parity                */
 	cudaEvent_t ev0, ev1, ev_g[2], ev_t0, ev_t1, ev_fork, ev_join, ev_a, ev_b;

@@ -280,6 +280,17 @@ int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
 		s->kbytes[3] = 2 * Fb * n_deep_rows + Fb * touched(nnz_deep_r, pt.n_cols) + 12 * nnz_deep_r +
 		               2 * Fb * n_deep_cols + Fb * touched(nnz_deep_c, pt.n_rows) + 12 * nnz_deep_c;
 		s->kbytes[4] = pl->nshards > 1 ? 3 * Fb * pl->n_touched : 0;
+		/* bytes the launch requests from L2 (the diagnostic model of SURVEY.md 8d): the own rows
+		 * as above, but a gathered row of the other factor for EVERY nonzero and pass -- twice
+		 * per nonzero in the tiled k_update_L (dot, accumulation), once in the resident one */
+		const long long passes = s->res_ng ? 1 : 2;
+		s->gbytes[0] = 2 * Fb * (pt.n_rows - n_long) + passes * Fb * nnz_short + 24 * nnz_short;
+		s->gbytes[1] = Fb * n_long + Fb * nnz_long + 32 * nnz_long;
+		s->gbytes[2] = 2 * Fb * (n_long - n_deep_rows) + Fb * (nnz_long - nnz_deep_r) + 12 * (nnz_long - nnz_deep_r) +
+		               2 * Fb * (pt.n_cols - n_deep_cols) + Fb * (pt.nnz - nnz_deep_c) + 12 * (pt.nnz - nnz_deep_c);
+		s->gbytes[3] = 2 * Fb * n_deep_rows + Fb * nnz_deep_r + 12 * nnz_deep_r +
+		               2 * Fb * n_deep_cols + Fb * nnz_deep_c + 12 * nnz_deep_c;
+		s->gbytes[4] = s->kbytes[4];
 	}
 	for (int g = 0; g < 2; g++)
 		if (s->gexec[g]) {
@@ -928,6 +939,15 @@ extern "C" int mfgpu_plan_kernel_bytes(mfgpu_plan *pl, long long bytes[5])
 		return mf_fail(MFGPU_EINVAL, "null argument");
 	for (int k = 0; k < 5; k++)
 		bytes[k] = pl->sh[0].kbytes[k];
+	return MFGPU_OK;
+}
+
+extern "C" int mfgpu_plan_kernel_gather_bytes(mfgpu_plan *pl, long long bytes[5])
+{
+	if (!pl || !bytes)
+		return mf_fail(MFGPU_EINVAL, "null argument");
+	for (int k = 0; k < 5; k++)
+		bytes[k] = pl->sh[0].gbytes[k];
 	return MFGPU_OK;
 }
 
