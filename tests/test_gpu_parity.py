@@ -83,6 +83,7 @@ def test_random_instances_bit_exact(gpu, oracle, shape):
     {"chain_ring": 1, "long_col": 10, "long_row": 20},
     {"chain_ws": 0}, {"chain_ws": 0, "long_col": 10, "long_row": 20}, {"chain_ws": 1, "long_col": 1, "long_row": 1},
     {"chain_ws": 1, "long_col": 40, "long_row": 100},
+    {"dot_stages": 4}, {"acc_rows": 3, "resident": 0}, {"dot_stages": 4, "acc_rows": 3, "resident": 0, "long_row": 1000000},
     {"resident": 0}, {"resident": 0, "long_row": 1000000}, {"resident": 2, "res_rows": 3, "long_row": 1000000},
     {"resident": 2, "res_rows": 8, "long_row": 1000000}, {"resident": 2, "res_rows": 32, "long_row": 150},
 ])
