@@ -163,6 +163,35 @@ def time_reference(inst, kind, budget_s, threads):
                       % (n, inst.iters, "matFact-omp.c" if kind == "omp" else "matFact.c", loop_s, t_zero)}
 
 
+def time_reference_mpi(inst, prog, nranks, threads, budget_s):
+    """Loop-only nonzero-updates/s of the reference's distributed program (prog 'mpi' =
+    matFact-mpi.c, 'hybrid' = matFact-hybrid.c, compiled unmodified against the single-node MPI
+    stand-in oracle/mpi_shim -- no MPI on this box) with `nranks` processes x `threads` OpenMP
+    threads, on a bounded number of iterations of the same workload written to a scratch input
+    file; the time is the program's own MPI_Wtime bracket around matrix_factorization
+    (matFact-mpi.c:647-653).  None when oracle/_ref does not hold the program."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import pyoracle
+    import tempfile
+    from recommender_system_b200.io import Instance, write_instance
+    if not pyoracle.mpi_available(prog):
+        return None
+    with tempfile.TemporaryDirectory() as tmp:
+        path = os.path.join(tmp, "sample.in")
+
+        def run(n):
+            write_instance(path, Instance(n, inst.alpha, inst.features, inst.users, inst.items, inst.entries))
+            return pyoracle.run_ref_mpi(path, nranks, prog, threads, timeout=600)[1]
+        per_iter = max(run(2) / 2, 1e-6)
+        n = int(max(2, min(inst.iters, budget_s / per_iter)))
+        loop_s = max(run(n), 1e-9)
+    return {"value": inst.nnz * n / loop_s, "unit": UNIT, "cores": nranks * threads, "kind": "reference",
+            "ranks": nranks, "threads_per_rank": threads,
+            "sample": "%d of %d iterations of the same workload, %s over oracle/mpi_shim (single-node "
+                      "shared-memory MPI stand-in), %.2f s by its own MPI_Wtime bracket"
+                      % (n, inst.iters, "matFact-mpi.c" if prog == "mpi" else "matFact-hybrid.c", loop_s)}
+
+
 def kernel_bytes(F, U_t, I_t, nnz):
     """Algorithmic (compulsory) HBM bytes of one ITERATION, SURVEY.md 8(d): every touched
     factor element read once and written once, A read once: 16*F*(U_t+I_t) + 12*nnz.  (The
@@ -387,7 +416,27 @@ def main():
             while t <= cpu_threads():
                 sweep["omp_%d" % t] = time_reference(inst, "omp", 2.5, t)["value"]
                 t *= 2
+            # ... and its MPI and hybrid programs over the rank counts of deliverables/report-mpi.pdf
+            # that fit this box, through the MPI stand-in
+            t = 1
+            while t <= min(cpu_threads(), 64):
+                r = time_reference_mpi(inst, "mpi", t, 1, 2.5)
+                if r:
+                    sweep["mpi_%d" % t] = r["value"]
+                t *= 2
+            if cpu_threads() >= 4:
+                half = 1
+                while half * 2 * 2 <= min(cpu_threads(), 64):
+                    half *= 2
+                r = time_reference_mpi(inst, "hybrid", half, 2, 2.5)
+                if r:
+                    sweep["hybrid_%dx2" % half] = r["value"]
             cpu["by_threads"] = sweep
+        else:
+            nr = 1
+            while nr * 2 <= min(cpu_threads(), 64):
+                nr *= 2
+            cpu["mpi"] = time_reference_mpi(inst, "mpi", nr, 1, 6.0)
     if comm:
         comm.close()
     if world > 1:

@@ -4,7 +4,7 @@
  * A single-node, shared-memory stand-in for the MPI subset the reference's distributed
  * programs use (matFact-mpi.c, matFact-hybrid.c, mpiutil.c: 27 entry points), so that they can
  * be compiled UNMODIFIED from /root/reference and timed on the host cores of a box that has no
- * MPI installation.  Ranks are processes started by oracle/_ref/mpirun_shim; they share one
+ * MPI installation.  Ranks are processes started by oracle/_build/mpirun_shim; they share one
  * anonymous memory file (rings for point-to-point messages, per-communicator staging slots
  * for collectives).  It is not a general MPI: messages between two ranks match in the order
  * they were sent (a tag or communicator mismatch aborts), requests complete inside the call

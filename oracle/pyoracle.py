@@ -126,3 +126,40 @@ def ref_factorize(kind, users, items, features, entries, iters, alpha, L, R):
     if s < 0:
         raise MemoryError("ref_factorize")
     return s
+
+
+def mpi_available(prog="mpi"):
+    """True when oracle/_ref holds the reference's distributed program (matFact-mpi.c or
+    matFact-hybrid.c built against oracle/mpi_shim)."""
+    return os.path.exists(os.path.join(REF_DIR, "matFact_%s" % prog))
+
+
+def mpirun_shim():
+    """Path of the launcher of the MPI stand-in (oracle/mpi_shim), compiled on demand."""
+    p = os.path.join(HERE, "_build", "mpirun_shim")
+    if not os.path.exists(p):
+        build(ref=False)
+    return p
+
+
+def run_ref_mpi(path, nranks, prog="mpi", threads=1, timeout=None):
+    """Run the UNMODIFIED reference program (prog: 'mpi' = matFact-mpi.c, 'hybrid' =
+    matFact-hybrid.c) on the input file `path` with `nranks` processes under
+    oracle/_build/mpirun_shim (threads = OMP_NUM_THREADS of each rank).  Returns
+    (recommendation lines as the serial program would print them, seconds its own
+    MPI_Wtime bracket reports for matrix_factorization -- matFact-mpi.c:647-653).
+    The programs interleave diagnostics on stdout; the recommendations are the lines
+    that are a bare integer."""
+    env = dict(os.environ, OMP_NUM_THREADS=str(threads))
+    p = subprocess.run([mpirun_shim(), "-np", str(nranks),
+                        os.path.join(REF_DIR, "matFact_%s" % prog), str(path)],
+                       stdout=subprocess.PIPE, stderr=subprocess.PIPE, env=env, timeout=timeout, text=True)
+    if p.returncode != 0:
+        raise RuntimeError("matFact_%s -np %d exited %d: %s" % (prog, nranks, p.returncode, p.stderr[-400:]))
+    out, took = [], None
+    for line in p.stdout.splitlines():
+        if line.isdigit():
+            out.append(line)
+        elif line.startswith("Matrix factorization took "):
+            took = float(line.split()[3])
+    return "".join(s + "\n" for s in out), took
