@@ -150,7 +150,9 @@ def run_ref_mpi(path, nranks, prog="mpi", threads=1, timeout=None):
     MPI_Wtime bracket reports for matrix_factorization -- matFact-mpi.c:647-653).
     The programs interleave diagnostics on stdout; the recommendations are the lines
     that are a bare integer."""
-    env = dict(os.environ, OMP_NUM_THREADS=str(threads))
+    # OMP_PROC_BIND must not be inherited: libgomp would bind the initial thread of EVERY rank to
+    # the first place (all ranks on one core)
+    env = dict(os.environ, OMP_NUM_THREADS=str(threads), OMP_PROC_BIND="false")
     p = subprocess.run([mpirun_shim(), "-np", str(nranks),
                         os.path.join(REF_DIR, "matFact_%s" % prog), str(path)],
                        stdout=subprocess.PIPE, stderr=subprocess.PIPE, env=env, timeout=timeout, text=True)
