@@ -17,6 +17,11 @@ CLI = os.path.join(HERE, "_build", "matfact_oracle")
 REF_DIR = os.path.join(HERE, "_ref")
 
 _lib = None
+# the CPUs this process may use, before any OpenMP runtime binds the calling thread
+try:
+    _ALL_CPUS = os.sched_getaffinity(0)
+except AttributeError:
+    _ALL_CPUS = None
 
 
 def build(ref: bool = True) -> None:
@@ -153,9 +158,18 @@ def run_ref_mpi(path, nranks, prog="mpi", threads=1, timeout=None):
     # OMP_PROC_BIND must not be inherited: libgomp would bind the initial thread of EVERY rank to
     # the first place (all ranks on one core)
     env = dict(os.environ, OMP_NUM_THREADS=str(threads), OMP_PROC_BIND="false")
-    p = subprocess.run([mpirun_shim(), "-np", str(nranks),
-                        os.path.join(REF_DIR, "matFact_%s" % prog), str(path)],
-                       stdout=subprocess.PIPE, stderr=subprocess.PIPE, env=env, timeout=timeout, text=True)
+    # ... and neither must the CPU mask of this thread, which an in-process OpenMP run with
+    # OMP_PROC_BIND may have narrowed to one core (children inherit it)
+    mask = os.sched_getaffinity(0) if _ALL_CPUS else None
+    if _ALL_CPUS:
+        os.sched_setaffinity(0, _ALL_CPUS)
+    try:
+        p = subprocess.run([mpirun_shim(), "-np", str(nranks),
+                            os.path.join(REF_DIR, "matFact_%s" % prog), str(path)],
+                           stdout=subprocess.PIPE, stderr=subprocess.PIPE, env=env, timeout=timeout, text=True)
+    finally:
+        if _ALL_CPUS:
+            os.sched_setaffinity(0, mask)
     if p.returncode != 0:
         raise RuntimeError("matFact_%s -np %d exited %d: %s" % (prog, nranks, p.returncode, p.stderr[-400:]))
     out, took = [], None
