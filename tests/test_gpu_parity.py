@@ -314,3 +314,40 @@ def test_rank_mode_exchange(gpu, oracle, tmp_path, nranks, exchange):
             assert np.max(np.abs(a - b)) <= 1e-9 * np.max(np.abs(a))
     assert np.array_equal(got["best"], oracle.recommend(inst.users, inst.items, inst.features,
                                                         inst.entries, L0, R0))
+
+
+@pytest.mark.parametrize("sample", ["inst0", "inst1", "inst2"])
+def test_gpu_trace_against_the_mats_samples(gpu, oracle, sample):
+    """samples/instN.mats (L, R, B at init, after the first iterations, at the end; 6 decimals)
+    against the trace tools/mats_trace.py prints from the device factors: every printed number
+    within the tolerance the oracle is held to (tests/test_oracle.py::test_mats_traces -- the
+    sample traces come from the course's program), and the factors after every traced iteration
+    bit-equal to the oracle's."""
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import mats_trace
+    from test_oracle import _parse_mats
+    inst = load_instance(sample)
+    gold = _parse_mats(gold_path(sample + ".mats"))
+    its = sorted(t for (t, n) in gold if isinstance(t, int) and n == "L")
+    path = os.path.join(ROOT, "gpurun_out", "trace_%s.mats" % sample)
+    os.makedirs(os.path.dirname(path), exist_ok=True)
+    with open(path, "w") as fh:
+        fh.write(mats_trace.trace(inst, its))
+    mine = _parse_mats(path)
+    assert set(mine) == set(gold)
+    for key, want in gold.items():
+        tol = 0.51e-6 if key[0] == "init" else 2.1e-6
+        assert mine[key].shape == want.shape and np.allclose(mine[key], want, rtol=0, atol=tol), key
+    # the same steps on the oracle, bit for bit
+    L0, R0 = oracle.init_LR(inst.users, inst.items, inst.features)
+    L1, R1 = L0.copy(), R0.copy()
+    with gpu.Plan(inst.users, inst.items, inst.features, inst.entries, inst.alpha) as plan:
+        plan.set_factors(L1, R1)
+        done = 0
+        for it in its + [inst.iters - 1]:
+            oracle.factorize(inst.users, inst.items, inst.features, inst.entries, it + 1 - done, inst.alpha, L0, R0)
+            plan.iterate(it + 1 - done)
+            done = it + 1
+            plan.get_factors(L1, R1)
+            assert bits_equal(L0, L1) and bits_equal(R0, R1), it
