@@ -14,15 +14,33 @@
  * srandom(seed) fills a table of 31 words with the Lehmer sequence x -> 16807 x mod (2^31 - 1)
  * (seed 0 counts as 1), sets the front index to 3 and the rear index to 0 and discards 310
  * draws; a draw adds table[rear] to table[front] (mod 2^32), returns that sum >> 1 and steps
- * both indices round the table.  The front index is always rear + 3 (mod 31), so `pos` = rear
- * is the whole position.  What mat2d_random_fill_LR relies on (mat2d.c:61-72: srandom(0), then
- * users*features + features*items calls of random()) is exactly this sequence; the tests compare
- * it draw for draw with the C library's own random() (tests/test_host.py).
+ * both indices round the table.  Written as one sequence x: x[i] = table[(i + 3) mod 31] for
+ * i < 31, then x[n] = x[n-3] + x[n-31] (mod 2^32), and draw k is x[341 + k] >> 1.  What
+ * mat2d_random_fill_LR relies on (mat2d.c:61-72: srandom(0), then users*features +
+ * features*items calls of random()) is exactly this sequence; the tests compare it draw for draw
+ * with the C library's own random() (tests/test_host.py).
+ *
+ * The recurrence has a dependent chain three draws long, ~1 ns per draw however it is
+ * scheduled.  With S the shift by one draw, x = (S^3 + S^31) x, hence x = (S^3 + S^31)^4 x:
+ *     x[n] = x[n-12] + 4 x[n-40] + 6 x[n-68] + 4 x[n-96] + x[n-124]   (mod 2^32)
+ * wherever the plain recurrence held for the 93 values before, i.e. from x[124] on (the first
+ * draw is x[341]).  Twelve consecutive values are independent of each other in this form, so
+ * blocks are generated eight at a time in vector registers.
  */
+static inline uint32_t raw_next(mf_rand *g)
+{
+	const uint64_t n = g->n;
+	const uint32_t v = g->h[(n - 3) & 127] + g->h[(n - 31) & 127];
+	g->h[n & 127] = v;
+	g->n = n + 1;
+	return v;
+}
+
 void mf_rand_seed(mf_rand *g, unsigned seed)
 {
+	uint32_t table[31];
 	int32_t word = seed ? (int32_t)seed : 1;
-	g->s[0] = (uint32_t)word;
+	table[0] = (uint32_t)word;
 	for (int i = 1; i < 31; i++) {
 		/* 16807 * word mod 2147483647 without overflow (Schrage) */
 		const long hi = word / 127773, lo = word % 127773;
@@ -30,36 +48,65 @@ void mf_rand_seed(mf_rand *g, unsigned seed)
 		if (w < 0)
 			w += 2147483647;
 		word = (int32_t)w;
-		g->s[i] = (uint32_t)word;
+		table[i] = (uint32_t)word;
 	}
-	g->pos = 0;
+	memset(g->h, 0, sizeof g->h);
+	for (int i = 0; i < 31; i++)
+		g->h[i] = table[(i + 3) % 31];
+	g->n = 31;
 	for (int i = 0; i < 310; i++)
-		(void)mf_rand_next(g);
+		(void)raw_next(g);
 }
 
-uint32_t mf_rand_next(mf_rand *g)
-{
-	const int r = g->pos, f = r + 3 >= 31 ? r + 3 - 31 : r + 3;
-	const uint32_t v = g->s[f] += g->s[r];
-	g->pos = r + 1 == 31 ? 0 : r + 1;
-	return v >> 1;
-}
+uint32_t mf_rand_next(mf_rand *g) { return raw_next(g) >> 1; }
 
+typedef uint32_t v8u __attribute__((vector_size(32), aligned(4), may_alias));
+typedef int32_t v8i __attribute__((vector_size(32)));
+
+#define MF_RAND_CHUNK 2048   /* raw values kept unshifted behind the generating front (>= 124) */
+
+#if defined(__x86_64__) && defined(__GNUC__) && !defined(__clang__)
+__attribute__((target_clones("avx2", "default")))
+#endif
 void mf_rand_block(mf_rand *g, uint32_t *out, size_t n)
 {
-	size_t i = 0;
-	while (i < n && g->pos != 0)
-		out[i++] = mf_rand_next(g);
-	/* whole turns of the table: rear 0..27 feeds front 3..30, rear 28..30 feeds front 0..2 */
-	uint32_t *s = g->s;
-	for (; i + 31 <= n; i += 31) {
-		for (int r = 0; r < 28; r++)
-			out[i + r] = (s[r + 3] += s[r]) >> 1;
-		for (int r = 28; r < 31; r++)
-			out[i + r] = (s[r - 28] += s[r]) >> 1;
+	if (n < 2 * MF_RAND_CHUNK) {
+		for (size_t i = 0; i < n; i++)
+			out[i] = raw_next(g) >> 1;
+		return;
 	}
-	while (i < n)
-		out[i++] = mf_rand_next(g);
+	/* raw values first: 124 from the ring, the rest from the block itself; a value is shifted
+	 * to its draw once the front is a chunk past it */
+	for (size_t i = 0; i < 124; i++)
+		out[i] = raw_next(g);
+	size_t shifted = 0;
+	for (size_t c0 = 124; c0 < n; c0 += MF_RAND_CHUNK) {
+		const size_t c1 = n - c0 < MF_RAND_CHUNK ? n : c0 + MF_RAND_CHUNK;
+		size_t i = c0;
+		/* the lag-12 operand straddles the two vectors stored last: taken from registers (a
+		 * load would wait for both stores to retire) */
+		v8u p2 = *(const v8u *)(out + i - 16), p1 = *(const v8u *)(out + i - 8);
+		const v8i mid = {4, 5, 6, 7, 8, 9, 10, 11};
+		for (; i + 8 <= c1; i += 8) {
+			const v8u a = __builtin_shuffle(p2, p1, mid), b = *(const v8u *)(out + i - 40),
+			          c = *(const v8u *)(out + i - 68), d = *(const v8u *)(out + i - 96),
+			          e = *(const v8u *)(out + i - 124);
+			const v8u rest = e + ((b + d) << 2) + (c << 2) + (c << 1);   /* off the dependent chain */
+			const v8u x = a + rest;
+			*(v8u *)(out + i) = x;
+			p2 = p1;
+			p1 = x;
+		}
+		for (; i < c1; i++)
+			out[i] = out[i - 3] + out[i - 31];
+		for (const size_t upto = c0 - 124; shifted < upto; shifted++)
+			out[shifted] >>= 1;
+	}
+	g->n += n - 124;
+	for (size_t k = 1; k <= 124; k++)
+		g->h[(g->n - k) & 127] = out[n - k];
+	for (; shifted < n; shifted++)
+		out[shifted] >>= 1;
 }
 
 /* ---- initial factors --------------------------------------------------------------------

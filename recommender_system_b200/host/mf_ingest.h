@@ -27,8 +27,8 @@ extern "C" {
 #endif
 
 typedef struct {
-	uint32_t s[31];     /* the generator's table, glibc's state[] of TYPE_3 */
-	int pos;            /* rear index (0..30); the front is pos + 3 mod 31   */
+	uint32_t h[128];    /* the last 128 values of the generator's sequence x: h[m & 127] = x[m] */
+	uint64_t n;         /* index of the next value                                              */
 } mf_rand;
 
 void mf_rand_seed(mf_rand *g, unsigned seed);                 /* srandom(seed) */
