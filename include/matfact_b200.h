@@ -94,6 +94,13 @@ void mfgpu_plan_destroy(mfgpu_plan *plan);
 
 /* Host -> device copy of the full L (users x features) and R (items x features). */
 int mfgpu_plan_set_factors(mfgpu_plan *plan, const double *L, const double *R);
+/* The reference's initial factors (mat2d_random_fill_LR + mat2d_transpose, mat2d.c:61-72,115-124,
+ * called matFact.c:113-120) generated straight into the device buffers: the same values, bit
+ * for bit, as mfgpu_random_fill_LR followed by mfgpu_plan_set_factors, without the host copies
+ * of L and R (the random() stream is produced on the calling thread and crosses as 4-byte
+ * draws; the divisions run on the device, overlapped with the generation of the next block).
+ * In rank mode every rank calls it; each keeps its own rows of L and all of R. */
+int mfgpu_plan_init_factors(mfgpu_plan *plan);
 /* Device -> host.  In rank mode only the rows of L owned by this rank are
  * written (the others are left untouched); R is complete on every rank. */
 int mfgpu_plan_get_factors(mfgpu_plan *plan, double *L, double *R);

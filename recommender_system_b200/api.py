@@ -26,7 +26,7 @@ EXPORTS = [
     "mfgpu_device_count", "mfgpu_last_error", "mfgpu_version",
     "mfgpu_factorize", "mfgpu_recommend", "mfgpu_run",
     "mfgpu_plan_create", "mfgpu_plan_create_rank", "mfgpu_plan_destroy",
-    "mfgpu_plan_set_factors", "mfgpu_plan_get_factors", "mfgpu_plan_iterate", "mfgpu_plan_sync",
+    "mfgpu_plan_set_factors", "mfgpu_plan_init_factors", "mfgpu_plan_get_factors", "mfgpu_plan_iterate", "mfgpu_plan_sync",
     "mfgpu_plan_last_loop_ms", "mfgpu_plan_recommend", "mfgpu_plan_last_recommend_ms",
     "mfgpu_plan_user_range", "mfgpu_plan_launch_count", "mfgpu_plan_exchange_kind", "mfgpu_plan_bytes_per_iter",
     "mfgpu_plan_set_option", "mfgpu_plan_save_factors", "mfgpu_plan_restore_factors",
@@ -71,6 +71,7 @@ def lib():
     L.mfgpu_plan_destroy.argtypes = [vp]
     L.mfgpu_plan_destroy.restype = None
     L.mfgpu_plan_set_factors.argtypes = [vp, vp, vp]
+    L.mfgpu_plan_init_factors.argtypes = [vp]
     L.mfgpu_plan_get_factors.argtypes = [vp, vp, vp]
     L.mfgpu_plan_iterate.argtypes = [vp, i]
     L.mfgpu_plan_sync.argtypes = [vp]
@@ -285,6 +286,10 @@ class Plan:
     def set_factors(self, L, R):
         _f64(L, (self.users, self.features)); _f64(R, (self.items, self.features))
         _check(lib().mfgpu_plan_set_factors(self._h, L.ctypes.data, R.ctypes.data))
+
+    def init_factors(self):
+        """The reference's initial L and R (srandom(0) sequence) generated on the device."""
+        _check(lib().mfgpu_plan_init_factors(self._h))
 
     def get_factors(self, L, R):
         _f64(L, (self.users, self.features)); _f64(R, (self.items, self.features))

@@ -12,6 +12,7 @@
  * ld = features rounded up to even so every row starts 16-byte aligned.
  */
 #include "mf_internal.h"
+#include "../host/mf_ingest.h"
 
 #include <stdlib.h>
 #include <string.h>
@@ -863,6 +864,123 @@ extern "C" int mfgpu_plan_set_factors(mfgpu_plan *pl, const double *L, const dou
 		CK(cudaMemcpyAsync(s->R[1], s->R[0], (size_t)pl->items * ld * 8, cudaMemcpyDeviceToDevice, s->st));
 	}
 	for (int g = 0; g < local_shards(pl); g++)
+		CK(cudaStreamSynchronize(pl->sh[g].st));
+	pl->cur = 0;
+	pl->have_factors = 1;
+	return MFGPU_OK;
+}
+
+/* ---- initial factors generated straight into the device buffers ------------------------------
+ *
+ * mat2d_random_fill_LR + mat2d_transpose (mat2d.c:61-72,115-124) without the host matrices:
+ * the calling thread produces the random() stream block by block into page-locked staging
+ * (host/mf_ingest.c: mf_rand_block), each block crosses as 4-byte draws and a kernel turns it
+ * into ((double)r / RAND_MAX) / F -- two IEEE divisions, the reference's expression -- at the
+ * element the draw belongs to: draw d < U*F is L[d / F][d % F], draw U*F + e is R[e % I][e / I]
+ * (R is drawn feature by feature and used transposed).  Block b+1 is generated while block b
+ * is copied and converted. */
+#define MF_INIT_BLOCK ((size_t)1 << 22)
+
+__global__ void __launch_bounds__(256)
+k_init_factors(const uint32_t *__restrict__ draws, unsigned long long d0, unsigned count, unsigned long long nl,
+               int F, int I, int ld, int user_lo, int user_hi, double *__restrict__ L, double *__restrict__ R)
+{
+	const unsigned t = blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= count)
+		return;
+	const unsigned long long d = d0 + t;
+	const double v = __ddiv_rn(__ddiv_rn((double)draws[t], 2147483647.0), (double)F);
+	if (d < nl) {
+		const unsigned long long i = d / (unsigned)F;
+		const int k = (int)(d - i * (unsigned)F);
+		if (i >= (unsigned long long)user_lo && i < (unsigned long long)user_hi)
+			L[(size_t)(i - (unsigned long long)user_lo) * ld + k] = v;
+	} else {
+		const unsigned long long e = d - nl, k = e / (unsigned)I, j = e - k * (unsigned)I;
+		R[(size_t)j * ld + k] = v;
+	}
+}
+
+struct InitStaging {
+	uint32_t *host[2] = {nullptr, nullptr};
+	uint32_t *dev[MF_MAX_SHARDS][2] = {};
+	cudaEvent_t done[MF_MAX_SHARDS][2] = {};
+	int devs[MF_MAX_SHARDS] = {};
+	int n = 0;
+	~InitStaging()
+	{
+		for (int g = 0; g < n; g++) {
+			cudaSetDevice(devs[g]);
+			for (int b = 0; b < 2; b++) {
+				if (done[g][b])
+					cudaEventDestroy(done[g][b]);
+				if (dev[g][b])
+					cudaFree(dev[g][b]);
+			}
+		}
+		for (int b = 0; b < 2; b++)
+			if (host[b])
+				cudaFreeHost(host[b]);
+	}
+};
+
+extern "C" int mfgpu_plan_init_factors(mfgpu_plan *pl)
+{
+	if (!pl)
+		return mf_fail(MFGPU_EINVAL, "null plan");
+	const unsigned long long nl = (unsigned long long)pl->users * pl->F, nr = (unsigned long long)pl->items * pl->F;
+	const unsigned long long total = nl + nr;
+	const int ns = local_shards(pl);
+	mf_rand gen;
+	mf_rand_seed(&gen, 0);                               /* mat2d.c:62: srandom(0) */
+	if (total) {
+		InitStaging sg;
+		const size_t cap = (size_t)std::min<unsigned long long>(total, MF_INIT_BLOCK);
+		for (int b = 0; b < 2; b++)
+			CK(cudaHostAlloc((void **)&sg.host[b], cap * sizeof(uint32_t), cudaHostAllocDefault));
+		for (int g = 0; g < ns; g++) {
+			CK(cudaSetDevice(pl->sh[g].dev));
+			sg.devs[g] = pl->sh[g].dev;
+			sg.n = g + 1;
+			for (int b = 0; b < 2; b++) {
+				CK(cudaMalloc((void **)&sg.dev[g][b], cap * sizeof(uint32_t)));
+				CK(cudaEventCreateWithFlags(&sg.done[g][b], cudaEventDisableTiming));
+			}
+		}
+		unsigned long long d0 = 0;
+		for (int blk = 0; d0 < total; blk++) {
+			const int b = blk & 1;
+			const unsigned count = (unsigned)std::min<unsigned long long>(total - d0, cap);
+			if (blk >= 2)                            /* the staging pair is free once block blk-2 has been copied */
+				for (int g = 0; g < ns; g++)
+					CK(cudaEventSynchronize(sg.done[g][b]));
+			mf_rand_block(&gen, sg.host[b], count);
+			for (int g = 0; g < ns; g++) {
+				mf_shard *s = &pl->sh[g];
+				CK(cudaSetDevice(s->dev));
+				CK(cudaMemcpyAsync(sg.dev[g][b], sg.host[b], (size_t)count * sizeof(uint32_t),
+				                   cudaMemcpyHostToDevice, s->st));
+				k_init_factors<<<(count + 255) / 256, 256, 0, s->st>>>(sg.dev[g][b], d0, count, nl, pl->F, pl->items,
+				                                                       pl->ld, s->user_lo, s->user_hi, s->L[0], s->R[0]);
+				CK(cudaGetLastError());
+				CK(cudaEventRecord(sg.done[g][b], s->st));
+			}
+			d0 += count;
+		}
+		for (int g = 0; g < ns; g++) {
+			CK(cudaSetDevice(pl->sh[g].dev));
+			CK(cudaStreamSynchronize(pl->sh[g].st));
+		}
+	}
+	for (int g = 0; g < ns; g++) {
+		mf_shard *s = &pl->sh[g];
+		CK(cudaSetDevice(s->dev));
+		const size_t nu = (size_t)(s->user_hi - s->user_lo);
+		/* rows without a nonzero are never rewritten, so both buffers start equal */
+		CK(cudaMemcpyAsync(s->L[1], s->L[0], nu * pl->ld * 8, cudaMemcpyDeviceToDevice, s->st));
+		CK(cudaMemcpyAsync(s->R[1], s->R[0], (size_t)pl->items * pl->ld * 8, cudaMemcpyDeviceToDevice, s->st));
+	}
+	for (int g = 0; g < ns; g++)
 		CK(cudaStreamSynchronize(pl->sh[g].st));
 	pl->cur = 0;
 	pl->have_factors = 1;

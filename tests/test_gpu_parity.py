@@ -249,6 +249,41 @@ def test_cli_is_a_drop_in(gpu, tmp_path):
     assert p.returncode == 0 and "loop_ms" in p.stderr
     assert p.stdout == load_out("inst30-40-10-2-10")
     assert dump.stat().st_size == (30 + 40) * 10 * 8
+    # the dump is L then R as raw doubles: the CLI's device-side initialisation + loop, bit for bit
+    import hashlib
+    import json
+    with open(os.path.join(ROOT, "tests", "golden", "expected.json")) as fh:
+        want = json.load(fh)["inst30-40-10-2-10"]["lr_sha256"]
+    assert hashlib.sha256(dump.read_bytes()).hexdigest() == want
+
+
+@pytest.mark.parametrize("shape", [
+    (1, 1, 1), (3, 5, 2), (30, 40, 10), (7, 100, 8), (5, 33, 17), (100, 1000, 23),
+    (70000, 3000, 100),       # L spans two staging blocks, the L / R boundary falls inside a block
+    (100, 3000000, 3),        # R: one feature is most of a block
+    (3, 70000, 150),          # R spans three blocks
+])
+def test_init_factors_on_device(gpu, shape):
+    """mfgpu_plan_init_factors (draws converted and transposed by a kernel) == the host sequence
+    mfgpu_random_fill_LR (itself checked draw for draw against the C library) + set_factors."""
+    users, items, F = shape
+    entries = np.zeros(1, dtype=ENTRY_DTYPE)
+    entries["value"] = 1.0
+    L0, R0 = gpu.random_fill_LR(users, items, F)
+    L1, R1 = np.full_like(L0, -1.0), np.full_like(R0, -1.0)
+    with gpu.Plan(users, items, F, entries, 0.001) as plan:
+        plan.init_factors()
+        plan.get_factors(L1, R1)
+        assert bits_equal(L0, L1) and bits_equal(R0, R1)
+        # ... and both buffers of the pair hold them: one iteration touches user 0 / item 0 only
+        plan.iterate(1)
+        plan.get_factors(L1, R1)
+        assert bits_equal(L0[1:], L1[1:]) and bits_equal(R0[1:], R1[1:])
+    if gpu.device_count() >= 2 and users >= 2:
+        with gpu.Plan(users, items, F, entries, 0.001, ngpus=2) as plan:
+            plan.init_factors()
+            plan.get_factors(L1, R1)
+            assert bits_equal(L0, L1) and bits_equal(R0, R1)
 
 
 @pytest.mark.parametrize("nshards", [2, 4, 8])
