@@ -167,6 +167,16 @@ _MPI_BODY = {}
 
 
 def time_reference_mpi(inst, prog, nranks, threads, budget_s, n_iters=None):
+    """_time_reference_mpi, or None (with a note on stderr) if the run fails: a baseline that cannot
+    be taken must not take the bench line with it."""
+    try:
+        return _time_reference_mpi(inst, prog, nranks, threads, budget_s, n_iters)
+    except Exception as exc:  # noqa: BLE001
+        print("bench.py: %s baseline with %d ranks not taken: %s" % (prog, nranks, exc), file=sys.stderr)
+        return None
+
+
+def _time_reference_mpi(inst, prog, nranks, threads, budget_s, n_iters=None):
     """Loop-only nonzero-updates/s of the reference's distributed program (prog 'mpi' =
     matFact-mpi.c, 'hybrid' = matFact-hybrid.c, compiled unmodified against the single-node MPI
     stand-in oracle/mpi_shim -- no MPI on this box) with `nranks` processes x `threads` OpenMP
@@ -257,8 +267,9 @@ def run_reference_arm(args, rank):
     vals, last = [], None
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        if use_mpi:
-            last = time_reference_mpi(inst, "mpi", probe["ranks"], 1, budget, n_iters=n_mpi)
+        mpi_run = time_reference_mpi(inst, "mpi", probe["ranks"], 1, budget, n_iters=n_mpi) if use_mpi else None
+        if mpi_run:
+            last = mpi_run
             last["program"] = probe["program"]
         else:
             last = time_reference(inst, "omp", budget, threads)
