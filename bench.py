@@ -203,7 +203,7 @@ def _time_reference_mpi(inst, prog, nranks, threads, budget_s, n_iters=None):
                     _MPI_BODY[key] = fh.read().split(b"\n", 1)[1]
             with open(path, "wb") as fh:
                 fh.write(b"%d\n" % n + _MPI_BODY[key])
-            return pyoracle.run_ref_mpi(path, nranks, prog, threads, timeout=600)[1]
+            return pyoracle.run_ref_mpi(path, nranks, prog, threads, timeout=300)[1]
         if n_iters is None:
             per_iter = max(run(2) / 2, 1e-6)
             n = int(max(2, min(inst.iters, budget_s / per_iter)))

@@ -7,7 +7,8 @@
  * MPISHIM_FD / MPISHIM_RANK / MPISHIM_NP in their environment and waits for them.  If a rank
  * exits with an error or dies, the rest of the job is told (abort flag) and terminated, and
  * the launcher returns that rank's status -- what a job relies on when one rank calls the
- * reference's die() (util.c:7-10).
+ * reference's die() (util.c:7-10).  Ranks also die with the launcher (PDEATHSIG), so a caller's
+ * timeout that kills the launcher leaves nothing spinning.
  */
 #define _GNU_SOURCE
 #include "shim_layout.h"
@@ -17,6 +18,7 @@
 #include <stdlib.h>
 #include <string.h>
 #include <sys/mman.h>
+#include <sys/prctl.h>
 #include <sys/wait.h>
 #include <unistd.h>
 
@@ -69,6 +71,7 @@ int main(int argc, char **argv)
 			return 1;
 		}
 		if (pid[r] == 0) {
+			prctl(PR_SET_PDEATHSIG, SIGKILL);   /* a killed launcher takes its ranks with it */
 			snprintf(rank_s, sizeof rank_s, "%d", r);
 			setenv("MPISHIM_FD", fd_s, 1);
 			setenv("MPISHIM_NP", np_s, 1);

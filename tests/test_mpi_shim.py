@@ -60,6 +60,38 @@ def test_launcher_reports_a_failing_rank(tmp_path, launcher):
     assert p.returncode == 0
 
 
+def test_ranks_die_with_a_killed_launcher(tmp_path, launcher):
+    """A caller's timeout kills the launcher with SIGKILL (subprocess.run(timeout=...)): the ranks,
+    spinning in a barrier that will never complete, must not outlive it."""
+    import signal
+    import time
+    src = tmp_path / "hang.c"
+    src.write_text('#include <mpi.h>\n#include <unistd.h>\nint main(int c, char **v) { int r; MPI_Init(&c, &v);'
+                   ' MPI_Comm_rank(MPI_COMM_WORLD, &r); if (r == 0) sleep(600); MPI_Barrier(MPI_COMM_WORLD);'
+                   ' MPI_Finalize(); return 0; }\n')
+    exe = str(tmp_path / "hang_for_shim_test")
+    subprocess.run(["gcc", "-O2", "-I", SHIM, "-o", exe, str(src), os.path.join(SHIM, "mpi_shim.c")], check=True)
+    p = subprocess.Popen([launcher, "-np", "3", exe])
+    time.sleep(1.0)
+    p.send_signal(signal.SIGKILL)
+    p.wait()
+    deadline = time.time() + 10
+    while time.time() < deadline:
+        alive = [d for d in os.listdir("/proc") if d.isdigit() and _cmdline(d).startswith(exe)]
+        if not alive:
+            break
+        time.sleep(0.2)
+    assert not alive
+
+
+def _cmdline(pid):
+    try:
+        with open("/proc/%s/cmdline" % pid, "rb") as fh:
+            return fh.read().split(b"\0")[0].decode(errors="replace")
+    except OSError:
+        return ""
+
+
 def _plain_input(sample, tmp_path):
     p = gold_path(sample + ".in")
     if not p.endswith(".gz"):
