@@ -12,6 +12,10 @@ iterations, factors + recommendations D2H), wall clock per step.
 Under torchrun (N > 1) every rank owns a contiguous user range, R is
 replicated and the partial R gradient is all-reduced each iteration; the
 problem size is fixed, so scaling is "strong".
+`cpu_baseline` (N = 1) and `--impl reference`: the reference's own CPU programs on all host
+cores, on a bounded sample of the same workload -- its OpenMP matrix_factorization in process
+(oracle/_ref/libref_omp.so) and its MPI program (oracle/_ref/matFact_mpi over the single-node MPI
+stand-in oracle/mpi_shim), the faster of the two being the figure and the other kept beside it.
 
 Workloads (BASELINE.json configs):
   inst60000  synthetic stand-in for inst60000-2000-200-10-20 (input blob missing
