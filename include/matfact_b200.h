@@ -79,6 +79,31 @@ int mfgpu_run(int users, int items, int features, int nnz,
               const mfgpu_entry *entries, int iters, double alpha,
               double *L, double *R, int *best, int ngpus);
 
+/* ---- allocation-free masked arg-max on DEVICE buffers ----------------------- */
+
+/* No counterpart in the reference: added for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  The masked arg-max of mfgpu_recommend / mfgpu_plan_recommend on the CURRENT
+ * device, enqueued on `stream` (a cudaStream_t; NULL = the default stream), with every pointer a
+ * DEVICE pointer supplied by the caller:
+ *   L (users x ld), R (items x ld) row-major doubles, rows 16-byte aligned (ld even, >= features);
+ *   mask_ptr[users+1], mask_col[mask_ptr[users]]: per user the ascending items print_output's
+ *   cursor skips (matFact.c:14-22) -- for a (row, col)-sorted duplicate-free entry list the
+ *   row pointers and columns of the entries themselves;
+ *   first_free[users]: first item not in the user's list, -1 if none (mfgpu_mask_stats gives it);
+ *   best[users]: out, as mfgpu_recommend.
+ * The call allocates nothing: the kernels' scratch lives in one built-in device array of
+ * MFGPU_NOALLOC_SCRATCH_BYTES, held by every GPU that loads the library until the process
+ * exits.  Limit: users * 16 + 64 <= MFGPU_NOALLOC_SCRATCH_BYTES (262 140 users); larger
+ * inputs return MFGPU_EINVAL.  All calls share the array: calls that overlap on one GPU (two
+ * streams, two threads) race; calls on one stream are ordered and safe.  Returns once the
+ * work is enqueued; synchronise `stream` before reading best. */
+#define MFGPU_NOALLOC_SCRATCH_BYTES (4u << 20)
+int mfgpu_recommend_noalloc(int users, int items, int features, int ld,
+                            const double *L, const double *R, const int *mask_ptr,
+                            const int *mask_col, const int *first_free, int *best,
+                            void *stream);
+
 /* ---- plan API: keep the problem resident in HBM across calls ---------------- */
 
 /* Builds the by-user / by-item groupings of `entries`, uploads them, and

@@ -34,7 +34,7 @@ EXPORTS = [
     "mfgpu_comm_unique_id", "mfgpu_comm_create", "mfgpu_comm_destroy",
     "mfgpu_split_users", "mfgpu_random_fill_LR", "mfgpu_mask_stats",
     "mfgpu_read_instance", "mfgpu_read_error", "mfgpu_free", "mfgpu_selftest_random",
-    "mfgpu_exchange_layout",
+    "mfgpu_exchange_layout", "mfgpu_recommend_noalloc",
 ]
 
 UID_BYTES = 128
@@ -111,6 +111,7 @@ def lib():
     L.mfgpu_selftest_random.restype = ctypes.c_long
     L.mfgpu_exchange_layout.argtypes = [i, i, i, vp, i, vp, vp, ctypes.POINTER(i)]
     L.mfgpu_mask_stats.argtypes = [i, i, i, vp, vp, vp]
+    L.mfgpu_recommend_noalloc.argtypes = [i, i, i, i, vp, vp, vp, vp, vp, vp, vp]
     _lib = L
     return L
 
@@ -199,6 +200,14 @@ def mask_stats(users, items, entries):
     if rc < 0:
         _check(rc)
     return cnt, ff
+
+
+def recommend_noalloc(users, items, features, ld, dL, dR, d_mask_ptr, d_mask_col, d_first_free, d_best,
+                      stream=0):
+    """mfgpu_recommend_noalloc: every pointer argument is a DEVICE address (an int); nothing is
+    allocated by the call; the work is enqueued on `stream` (a cudaStream_t as an int)."""
+    _check(lib().mfgpu_recommend_noalloc(users, items, features, ld, dL, dR, d_mask_ptr, d_mask_col,
+                                         d_first_free, d_best, stream))
 
 
 def matrix_factorization(L, R, entries, iters, alpha, ngpus=1):

@@ -924,3 +924,99 @@ extern "C" int mfgpu_run(int users, int items, int features, int nnz,
 		return mf_fail(MFGPU_EINVAL, "bad argument");
 	return run_all(users, items, features, nnz, entries, iters, alpha, L, R, best, ngpus, true, true);
 }
+
+/* ---- masked arg-max without any allocation (mfgpu_recommend_noalloc) -----------------------
+ *
+ * No counterpart in the reference; added for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  The same two kernels as mfgpu_plan_recommend, with their scratch (the
+ * per-split partial maxima part_v / part_j and the nan_first flags) in a file-scope device
+ * array instead of pool memory.  Every GPU that loads the library holds the array until the
+ * process exits; every call shares it, so calls that overlap on one GPU race.  In host code
+ * the array's name is a host-side stand-in, not a device address: the address the kernels get
+ * comes from cudaGetSymbolAddress, once per device, with that device current. */
+static __device__ __align__(256) unsigned char g_noalloc_scratch[MFGPU_NOALLOC_SCRATCH_BYTES];
+static void *g_noalloc_ptr[64];
+
+extern "C" int mfgpu_recommend_noalloc(int users, int items, int features, int ld,
+                                       const double *L, const double *R, const int *mask_ptr,
+                                       const int *mask_col, const int *first_free, int *best,
+                                       void *stream)
+{
+	if (users < 0 || items < 0 || features < 0)
+		return mf_fail(MFGPU_EINVAL, "mfgpu_recommend_noalloc: negative size");
+	if (users == 0)
+		return MFGPU_OK;
+	if (!best || !mask_ptr || !first_free)
+		return mf_fail(MFGPU_EINVAL, "mfgpu_recommend_noalloc: null pointer");
+	if (features > 0 && items > 0) {
+		if (!L || !R)
+			return mf_fail(MFGPU_EINVAL, "mfgpu_recommend_noalloc: null factor pointer");
+		if (ld < features || (ld & 1) || ((uintptr_t)L & 15) || ((uintptr_t)R & 15))
+			return mf_fail(MFGPU_EINVAL, "mfgpu_recommend_noalloc: rows must be 16-byte aligned "
+			                             "(ld even and >= features, L and R 16-byte aligned)");
+	}
+	/* scratch: nan_first[users] ints | part_j[users*splits] ints | part_v[users*splits] doubles */
+	const size_t cap = MFGPU_NOALLOC_SCRATCH_BYTES;
+	const size_t fixed = 64 + (size_t)users * sizeof(int);
+	const size_t per_split = (size_t)users * (sizeof(int) + sizeof(double));
+	if (fixed + per_split > cap)
+		return mf_fail(MFGPU_EINVAL, "mfgpu_recommend_noalloc: %d users need %zu bytes of scratch, the "
+		                             "built-in array has %zu (at most %zu users)", users, fixed + per_split,
+		               cap, (cap - 64) / (2 * sizeof(int) + sizeof(double)));
+	int dev = 0;
+	CK(cudaGetDevice(&dev));
+	if (dev < 0 || dev >= 64)
+		return mf_fail(MFGPU_ENODEV, "mfgpu_recommend_noalloc: device ordinal %d out of range", dev);
+	int major = 0;
+	CK(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+	if (major != 10)
+		return mf_fail(MFGPU_ENODEV, "mfgpu_recommend_noalloc: the current device is not an sm_100 (B200) device");
+	if (!g_noalloc_ptr[dev]) {
+		void *q = nullptr;
+		CK(cudaGetSymbolAddress(&q, g_noalloc_scratch));
+		g_noalloc_ptr[dev] = q;
+	}
+	cudaStream_t st = (cudaStream_t)stream;
+	if (features == 0 || items == 0) {
+		/* B has no columns, or is all +0.0: print_output keeps the first item its cursor does not
+		 * skip (matFact.c:17); first_free already holds it (-1 when there is none) */
+		if (items == 0)
+			CK(cudaMemsetAsync(best, 0xff, (size_t)users * sizeof(int), st));
+		else
+			CK(cudaMemcpyAsync(best, first_free, (size_t)users * sizeof(int), cudaMemcpyDeviceToDevice, st));
+		return MFGPU_OK;
+	}
+	const int tiles_y = (users + mf::AM_TI - 1) / mf::AM_TI;
+	if (tiles_y > 65535)
+		return mf_fail(MFGPU_EINVAL, "mfgpu_recommend_noalloc: too many users");
+	const int n_tiles = (items + mf::AM_TJ - 1) / mf::AM_TJ;
+	int splits = (148 * 2 * 8 + tiles_y - 1) / tiles_y;            /* as shard_create (mf_plan.cu) */
+	splits = std::max(1, std::min(splits, n_tiles));
+	splits = (int)std::min<size_t>((size_t)splits, (cap - fixed) / per_split);
+	unsigned char *base = (unsigned char *)g_noalloc_ptr[dev];
+	mf::ArgmaxArgs a;
+	a.users_lo = 0;
+	a.users_hi = users;
+	a.l_row0 = 0;
+	a.items = items;
+	a.F = features;
+	a.ld = ld;
+	a.n_splits = splits;
+	a.tiles_per_split = (n_tiles + splits - 1) / splits;
+	a.mask_ptr = mask_ptr;
+	a.mask_col = mask_col;
+	a.first_free = first_free;
+	a.nan_first = (int *)base;
+	a.part_j = a.nan_first + users;
+	a.part_v = (double *)(base + (((size_t)users * (1 + (size_t)splits) * sizeof(int) + 63) & ~(size_t)63));
+	/* the array keeps the last call's contents: the flags must start at zero, the partial
+	 * maxima are written in full by every CTA before k_argmax_final reads them */
+	CK(cudaMemsetAsync(a.nan_first, 0, (size_t)users * sizeof(int), st));
+	dim3 grid((unsigned)splits, (unsigned)tiles_y);
+	mf::k_masked_argmax<<<grid, 256, 0, st>>>(a, L, R);
+	CK(cudaGetLastError());
+	mf::k_argmax_final<<<(users + 255) / 256, 256, 0, st>>>(a, best);
+	CK(cudaGetLastError());
+	return MFGPU_OK;
+}
