@@ -20,7 +20,7 @@ import numpy as np
 from .io import ENTRY_DTYPE, Instance, format_output
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libmatfact_b200.so")
+LIB_PATH = os.environ.get("MFGPU_LIB") or os.path.join(HERE, "libmatfact_b200.so")   # MFGPU_LIB: a variant build (tools/build_variant.sh)
 
 EXPORTS = [
     "mfgpu_device_count", "mfgpu_last_error", "mfgpu_version",

@@ -79,6 +79,13 @@ struct mf_shard {
 	int r_plain;                             /* 1: R[] from cudaMalloc (exportable over CUDA IPC), 0: from the pool */
 	int borrowed;                            /* 1: G[], R[] belong to the communicator's arena */
 	int *d_chunk_row, *d_chunk_pos;          /* chunks of the long rows (k_dot) */
+	int *d_units;                            /* k_dot_units: 8 ints per unit (mf_loop.cuh) */
+	int n_units, n_mid;                      /* units of the paired launch; rows [n_long, n_mid) stay with k_update_L */
+	size_t pair_smem;
+	int pair_warps;                          /* warps per CTA of k_dot_units (4, 5, 6 or 8) */
+	int pair_nt;                             /* tiles in the ring of a k_dot_pair warp (2..6) */
+	int split;                               /* 1: dots (k_dot_pair, k_dot) and accumulations (k_acc) are separate launches */
+	unsigned long long *d_ticket;            /* k_acc: unit counter, zeroed before every launch */
 	/* factors, double buffered; L holds the shard's users only */
 	double *L[2], *R[2];
 	double *G[2];                            /* N-shard only: partial R gradient */
@@ -135,7 +142,7 @@ struct mfgpu_plan {
 	void *ipc_mapped[5 * MF_MAX_SHARDS];
 	int n_ipc_mapped;
 	/* options */
-	int opt_graph, opt_graph_iters, opt_long_row, opt_long_col, opt_ch, opt_chain_ring, opt_resident, opt_res_rows, opt_chain_ws, opt_exchange, opt_dot_stages, opt_acc_rows;
+	int opt_graph, opt_graph_iters, opt_long_row, opt_long_col, opt_ch, opt_chain_ring, opt_resident, opt_res_rows, opt_chain_ws, opt_exchange, opt_dot_stages, opt_acc_rows, opt_cs_store, opt_pair, opt_pair_stages, opt_pair_warps, opt_acc_gw;
 };
 
 /* ---- shared helpers (defined in mf_capi.cu) ----------------------------------- */
@@ -167,7 +174,7 @@ struct TraceClock {
 	}
 };
 
-int mf_kernels_prepare(int warps, size_t k1_smem, int res_ng, size_t res_smem);   /* mf_iter.cu: kernels live in that TU only */
+int mf_kernels_prepare(int warps, size_t k1_smem, int res_ng, size_t res_smem, size_t pair_smem, int pair_warps, int pair_nt);   /* mf_iter.cu: kernels live in that TU only */
 extern mf_nccl_api g_nccl;
 
 #define CK(call)                                                                        \

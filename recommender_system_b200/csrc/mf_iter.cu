@@ -314,7 +314,25 @@ static int prepare_res(size_t smem)
 	return MFGPU_OK;
 }
 
-int mf_kernels_prepare(int warps, size_t k1_smem, int res_ng, size_t res_smem)
+/* k_dot_units<W, NT> for the configured (W, NT): its function pointer */
+typedef void (*dot_units_fn)(const mf::LoopArgs, const int *, int, const double *, const double *);
+static dot_units_fn dot_units_kernel(int w, int nt)
+{
+#define MF_ROW(W) \
+	case W: switch (nt) { case 2: return mf::k_dot_units<W, 2>; case 3: return mf::k_dot_units<W, 3>; \
+	                      case 4: return mf::k_dot_units<W, 4>; case 5: return mf::k_dot_units<W, 5>; \
+	                      default: return mf::k_dot_units<W, 6>; }
+	switch (w) {
+		MF_ROW(4) MF_ROW(5) MF_ROW(6)
+	default:
+		switch (nt) { case 2: return mf::k_dot_units<8, 2>; case 3: return mf::k_dot_units<8, 3>;
+		              case 4: return mf::k_dot_units<8, 4>; case 5: return mf::k_dot_units<8, 5>;
+		              default: return mf::k_dot_units<8, 6>; }
+	}
+#undef MF_ROW
+}
+
+int mf_kernels_prepare(int warps, size_t k1_smem, int res_ng, size_t res_smem, size_t pair_smem, int pair_warps, int pair_nt)
 {
 	const auto attr = cudaFuncAttributeMaxDynamicSharedMemorySize;
 	CK(cudaFuncSetAttribute(mf::k_chain_ws, attr, mf::WS_SMEM));
@@ -328,6 +346,11 @@ int mf_kernels_prepare(int warps, size_t k1_smem, int res_ng, size_t res_smem)
 	case 7: TRY(prepare_res<7>(res_smem)); break;
 	case 8: TRY(prepare_res<8>(res_smem)); break;
 	default: break;
+	}
+	if (pair_smem) {
+		CK(cudaFuncSetAttribute(dot_units_kernel(pair_warps, pair_nt), attr, (int)pair_smem));
+		CK(cudaFuncSetAttribute(dot_units_kernel(pair_warps, pair_nt), cudaFuncAttributePreferredSharedMemoryCarveout,
+		                        (int)cudaSharedmemCarveoutMaxShared));
 	}
 	if (warps == 8) {
 		CK(cudaFuncSetAttribute(mf::k_update_L<8, 1, 2>, attr, (int)k1_smem));
@@ -392,6 +415,17 @@ enum { K_FUSED = 1, K_DOT = 2, K_BULK = 4, K_DEEP = 8, K_ALL = 15 };
 
 static int launch_fused(mfgpu_plan *pl, mf_shard *s, int c, cudaStream_t st)
 {
+	if (s->n_units > 0) {
+		/* persistent warps; as many CTAs as fit an SM (at most 16 warps: 128 registers) */
+		int n_sm = 148;
+		CK(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, s->dev));
+		const int w = s->pair_warps;
+		const int per_sm = std::max(1, std::min(16 / w, (int)(227 * 1024 / (s->pair_smem + 1024))));
+		const unsigned blocks = (unsigned)std::min((s->n_units + w - 1) / w, n_sm * per_sm);
+		dot_units_kernel(w, s->pair_nt)<<<blocks, 32 * w, s->pair_smem, st>>>(s->la, s->d_units, s->n_units, s->L[c], s->R[c]);
+		CK(cudaGetLastError());
+		pl->launches++;
+	}
 	if (s->k1_blocks <= 0)
 		return MFGPU_OK;
 #define MF_RES(NG) \
@@ -404,7 +438,9 @@ static int launch_fused(mfgpu_plan *pl, mf_shard *s, int c, cudaStream_t st)
 		}
 	} else if (s->warps == 8) {
 		const bool deep_acc = s->acc_rows > 1, deep_dot = s->la.NT > 2;
-#define MF_UPD(P, NT) mf::k_update_L<8, P, NT><<<s->k1_blocks, 256, s->k1_smem, st>>>(s->la, s->L[c], s->L[1 - c], s->R[c])
+		mf::LoopArgs la = s->la;
+		la.n_rows = s->n_mid;             /* the shorter rows went to the paired launch above */
+#define MF_UPD(P, NT) mf::k_update_L<8, P, NT><<<s->k1_blocks, 256, s->k1_smem, st>>>(la, s->L[c], s->L[1 - c], s->R[c])
 		if (deep_acc && deep_dot) MF_UPD(3, 4);
 		else if (deep_acc) MF_UPD(3, 2);
 		else if (deep_dot) MF_UPD(1, 4);
@@ -431,8 +467,47 @@ static int launch_dot(mfgpu_plan *pl, mf_shard *s, int c, cudaStream_t st)
 	return MFGPU_OK;
 }
 
+template <int GW>
+static void launch_acc_gw(const mf::ChainSide &A, const mf::ChainSide &B, long ub, long ut, int F, int ld,
+                          unsigned long long *ticket, int n_sm, cudaStream_t st)
+{
+	const long ctas = std::min<long>((ut + mf::ACC_WARPS - 1) / mf::ACC_WARPS, (long)n_sm * (GW <= 2 ? 8 : GW <= 4 ? 6 : mf::ACC_CTAS));
+	mf::k_acc<GW><<<(unsigned)ctas, mf::ACC_WARPS * 32, 0, st>>>(A, B, ub, ut, F, ld, ticket);
+}
+
+/* split mode: every accumulation that is not a deep chain, straight from L2 (k_acc) */
+static int launch_acc(mfgpu_plan *pl, mf_shard *s, int c, double *rout, cudaStream_t st)
+{
+	const mf::LoopArgs &a = s->la;
+	const mf::ChainSide A = side_L(pl, s, c, a.n_deep_rows, a.n_rows);
+	const mf::ChainSide B = side_R(pl, s, c, a.n_deep_cols, a.n_cols, rout);
+	const int ng = (a.F + 31) / 32;
+	const int gw = pl->opt_acc_gw > 0 ? std::min(pl->opt_acc_gw, std::min(ng, 8)) : std::min(ng, 8), nb = (ng + gw - 1) / gw;
+	const long ub = (long)(B.end - B.begin) * nb, ut = ub + (long)(A.end - A.begin) * nb;
+	if (ut <= 0)
+		return MFGPU_OK;
+	int n_sm = 148;
+	CK(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, s->dev));
+	CK(cudaMemsetAsync(s->d_ticket, 0, sizeof(unsigned long long), st));
+	switch (gw) {
+	case 1: launch_acc_gw<1>(A, B, ub, ut, a.F, a.ld, s->d_ticket, n_sm, st); break;
+	case 2: launch_acc_gw<2>(A, B, ub, ut, a.F, a.ld, s->d_ticket, n_sm, st); break;
+	case 3: launch_acc_gw<3>(A, B, ub, ut, a.F, a.ld, s->d_ticket, n_sm, st); break;
+	case 4: launch_acc_gw<4>(A, B, ub, ut, a.F, a.ld, s->d_ticket, n_sm, st); break;
+	case 5: launch_acc_gw<5>(A, B, ub, ut, a.F, a.ld, s->d_ticket, n_sm, st); break;
+	case 6: launch_acc_gw<6>(A, B, ub, ut, a.F, a.ld, s->d_ticket, n_sm, st); break;
+	case 7: launch_acc_gw<7>(A, B, ub, ut, a.F, a.ld, s->d_ticket, n_sm, st); break;
+	default: launch_acc_gw<8>(A, B, ub, ut, a.F, a.ld, s->d_ticket, n_sm, st); break;
+	}
+	CK(cudaGetLastError());
+	pl->launches++;
+	return MFGPU_OK;
+}
+
 static int launch_chain(mfgpu_plan *pl, mf_shard *s, int c, double *rout, bool deep, cudaStream_t st)
 {
+	if (!deep && s->split)
+		return launch_acc(pl, s, c, rout, st);
 	const mf::LoopArgs &a = s->la;
 	const mf::ChainSide A = deep ? side_L(pl, s, c, 0, a.n_deep_rows) : side_L(pl, s, c, a.n_deep_rows, a.n_long);
 	const mf::ChainSide B = deep ? side_R(pl, s, c, 0, a.n_deep_cols, rout)
@@ -651,7 +726,7 @@ static int build_graph(mfgpu_plan *pl, mf_shard *s, int c, int n)
 static long long launches_per_iteration(const mfgpu_plan *pl, const mf_shard *s)
 {
 	const mf::LoopArgs &a = s->la;
-	long long n = (s->k1_blocks > 0) + (s->dot_blocks > 0);
+	long long n = (s->k1_blocks > 0) + (s->n_units > 0) + (s->dot_blocks > 0);
 	n += (a.n_long - a.n_deep_rows > 0 || a.n_cols - a.n_deep_cols > 0);
 	n += (a.n_deep_rows > 0 || a.n_deep_cols > 0);
 	if (pl->nshards > 1 && (long)pl->n_touched * pl->F > 0)

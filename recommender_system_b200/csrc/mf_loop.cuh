@@ -117,10 +117,18 @@ __device__ __forceinline__ double dot_tile(double s, const double *l, const doub
  * small that a warp's own latency decides (rank mode with many ranks).  Loads are never
  * predicated (a predicated load is followed by a select that waits for it): rows shorter than
  * P fetch their last nonzero again instead. */
+__device__ __forceinline__ void st_row(double *p, double v, bool cs)
+{
+	if (cs)
+		__stcs(p, v);
+	else
+		*p = v;
+}
+
 template <int NG, int P>
 __device__ __forceinline__ void row_update(const double *init, double *Lout,
                                            const double *__restrict__ Rold, int j, const double *es,
-                                           int cnt, int ld, int kb, int F, int lane)
+                                           int cnt, int ld, int kb, int F, int lane, bool cs = false)
 {
 	double acc[NG], x[P][NG], xn[NG];
 	const bool last_ok = kb + (NG - 1) * 32 + lane < F;   /* only the last group can be partial */
@@ -166,7 +174,7 @@ __device__ __forceinline__ void row_update(const double *init, double *Lout,
 #pragma unroll
 	for (int g = 0; g < NG; g++)
 		if (g < NG - 1 || last_ok)
-			Lout[off[g]] = acc[g];
+			st_row(Lout + off[g], acc[g], cs);
 }
 
 /* ---- register pipelines of the sequential accumulations ------------------------------------
@@ -481,21 +489,248 @@ k_update_L(const LoopArgs p, const double *__restrict__ Lold, double *__restrict
 		__syncwarp();
 		/* L_new[i][k] chain over this chunk's nonzeros; the feature groups of a lane are
 		 * independent chains and run interleaved */
+		const bool cs = p.cs_store && c0 + CH >= m;      /* the last chunk's store is final */
 		for (int kb = 0; kb < F; kb += 256) {
 			const double *init = (c0 == 0) ? Ls : Lout;
 			switch (min(8, (F - kb + 31) >> 5)) {
-			case 1: row_update<1, P>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
-			case 2: row_update<2, P>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
-			case 3: row_update<3, P>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
-			case 4: row_update<4, P>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
-			case 5: row_update<5, P>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
-			case 6: row_update<6, P>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
-			case 7: row_update<7, P>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
-			default: row_update<8, P>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane); break;
+			case 1: row_update<1, P>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane, cs); break;
+			case 2: row_update<2, P>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane, cs); break;
+			case 3: row_update<3, P>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane, cs); break;
+			case 4: row_update<4, P>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane, cs); break;
+			case 5: row_update<5, P>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane, cs); break;
+			case 6: row_update<6, P>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane, cs); break;
+			case 7: row_update<7, P>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane, cs); break;
+			default: row_update<8, P>(init, Lout, Rold, j, es, cnt, ld, kb, F, lane, cs); break;
 			}
 		}
 		__syncwarp();                 /* es is rewritten by the next chunk */
 	}
+}
+
+/* nonzeros per register sub-block of the accumulation kernel k_acc (below) */
+#ifndef MF_ACC_SB
+#define MF_ACC_SB 4
+#endif
+constexpr int ACC_SB = MF_ACC_SB;
+#ifndef MF_ACC_CTAS
+#define MF_ACC_CTAS 5
+#endif
+constexpr int ACC_CTAS = MF_ACC_CTAS;
+#ifndef MF_ACC_PRED
+#define MF_ACC_PRED 1
+#endif
+#ifndef MF_ACC_SWITCH
+#define MF_ACC_SWITCH 0
+#endif
+
+/* a = ((a + e[0]*x[0]) + e[1]*x[1]) + ... over the first N nonzeros of a sub-block */
+template <int N>
+__device__ __forceinline__ double acc_chain_n(double a, const double (&x)[ACC_SB], const double (&e)[ACC_SB])
+{
+#pragma unroll
+	for (int n = 0; n < N; n++)
+		a = __dadd_rn(a, __dmul_rn(e[n], x[n]));
+	return a;
+}
+
+/* m (1..ACC_SB) is the same in every lane: real branches, no selects in the chains */
+__device__ __forceinline__ double acc_chain(double a, const double (&x)[ACC_SB], const double (&e)[ACC_SB], int m)
+{
+	static_assert(ACC_SB == 4 || ACC_SB == 8, "sub-blocks of 4 or 8 nonzeros");
+#if !MF_ACC_SWITCH
+	if (m == ACC_SB)
+		return acc_chain_n<ACC_SB>(a, x, e);
+#pragma unroll
+	for (int n = 0; n < ACC_SB; n++)
+		if (n < m)
+			a = __dadd_rn(a, __dmul_rn(e[n], x[n]));
+	return a;
+#endif
+	switch (m) {
+	case 1: return acc_chain_n<1>(a, x, e);
+	case 2: return acc_chain_n<2>(a, x, e);
+	case 3: return acc_chain_n<3>(a, x, e);
+	case 4: return acc_chain_n<4>(a, x, e);
+	case 5: return acc_chain_n<(ACC_SB > 4 ? 5 : 4)>(a, x, e);
+	case 6: return acc_chain_n<(ACC_SB > 4 ? 6 : 4)>(a, x, e);
+	case 7: return acc_chain_n<(ACC_SB > 4 ? 7 : 4)>(a, x, e);
+	default: return acc_chain_n<ACC_SB>(a, x, e);
+	}
+}
+
+/*
+ * k_dot_units: every dot of the by-user pass (mat2d.c:126-139, matFact.c:45) in split mode.
+ *
+ * A unit is up to 32 nonzeros that share at most two users: a chunk of a long row, one row of
+ * at most 32 nonzeros, or TWO such rows whose lengths add up to at most 32 (lanes [0, la) row
+ * A, lanes [la, la + lb) row B).  The dot costs the shared-memory pipe and the FP64 pipe one
+ * instruction per warp whatever the number of active lanes (a 16-byte shared-memory load with
+ * 15 of 32 lanes active takes as long as with 32, profiles/r02_ubench_l2_gather.txt), and the
+ * inst60000 shape has 10..20 nonzeros per user: pairing fills the lanes.
+ *
+ * What bounds the pass is the latency of the gathered R rows (~2000 cycles under load), so a
+ * warp is persistent and treats the tiles of ALL its units as one stream: the ring of NT tiles
+ * (16 features of the unit's <= 32 R rows each, 16-byte cp.async) is filled NT - 1 tiles ahead
+ * of the tile being added, across unit boundaries; the next unit's items, ratings and positions
+ * are loaded one unit ahead and its descriptor two units ahead, so no dependent global load is
+ * ever waited for.  Lane = nonzero walks k sequentially against the L row of its own user
+ * (both L rows of a unit travel with its first tile, two buffers by unit parity).
+ * Writes e_n at its by-user and by-item positions; k_acc does the accumulations.
+ * units: 8 ints per unit {ia, basea, la, ib, baseb, lb, -, -} (local user, first by-user
+ * position, length of the two parts).  Needs NT - 1 <= ceil(F / 16) (the host sees to it).
+ * Dynamic shared memory per warp: NT tiles [32][TS], L rows [2][2][ld], unit data [2][32] x
+ * (rating, position, by-item position), [2][2] lengths.
+ */
+__host__ __device__ constexpr size_t dot_units_doubles(int NT, int ld)
+{
+	return (size_t)NT * 32 * TS + 4 * (size_t)ld + 64 + 64 + 2;
+}
+
+template <int WARPS, int NT>
+__global__ void __launch_bounds__(WARPS * 32, 512 / (WARPS * 32))
+k_dot_units(const LoopArgs p, const int *__restrict__ units, int n_units,
+            const double *__restrict__ Lold, const double *__restrict__ Rold)
+{
+	extern __shared__ __align__(16) double smem[];
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	const int F = p.F, ld = p.ld;
+	constexpr int td = 32 * TS;
+	double *tiles = smem + dot_units_doubles(NT, ld) * warp;
+	double *Ls = tiles + (size_t)NT * td;          /* [parity][A, B][ld] */
+	double *m_a = Ls + 4 * (size_t)ld;             /* [parity][32] */
+	int *m_pos = (int *)(m_a + 64);                /* [parity][32] */
+	int *m_ep = m_pos + 64;                        /* [parity][32] */
+	int *m_len = m_ep + 64;                        /* [parity]{cnt, la} */
+	const int nt = (F + KT - 1) / KT;
+	const long W = (long)gridDim.x * WARPS, wid = (long)blockIdx.x * WARPS + warp;
+	if (wid >= n_units)
+		return;
+	const int n_mine = (int)((n_units - wid + W - 1) / W);
+	const long total = (long)n_mine * nt;
+
+	struct Desc { int ia, basea, la, ib, baseb, lb; };
+	struct LaneData { int pos, j, ep; double a; };
+	auto load_desc = [&](int t, Desc &d) {
+		const int *u = units + 8 * (size_t)(wid + t * W);
+		const int4 x = *reinterpret_cast<const int4 *>(u);
+		const int2 y = *reinterpret_cast<const int2 *>(u + 4);
+		d.ia = x.x; d.basea = x.y; d.la = x.z; d.ib = x.w; d.baseb = y.x; d.lb = y.y;
+	};
+	auto load_lane = [&](const Desc &d, LaneData &x) {
+		const int l = min(lane, d.la + d.lb - 1);      /* idle lanes mirror the last nonzero */
+		x.pos = l < d.la ? d.basea + l : d.baseb + l - d.la;
+		x.j = p.col_idx[x.pos];
+		x.a = p.val[x.pos];
+		x.ep = p.epos[x.pos];
+	};
+
+	Desc dI, dN;                /* unit being issued, the one after it */
+	LaneData xI, xN;
+	load_desc(0, dI);
+	load_lane(dI, xI);
+	if (n_mine > 1)
+		load_desc(1, dN);
+	/* Gathers of the unit being issued: lane l moves the 16-byte piece pc = l & 7 of the tile
+	 * rows u*4 + (l >> 3), u < 8 -- one cp.async each per tile, destinations 4 tile rows apart. */
+	const double *gsrc[8];
+	int gn = 0;                 /* pieces of this lane: u < gn */
+	const int pc2 = 2 * (lane & 7);
+	const uint32_t gdst = smem_u32(tiles) + (uint32_t)(((lane >> 3) * TS + pc2) * 8);
+	int ti = 0, ki = 0;         /* issue side: my ti-th unit, its tile ki */
+
+	auto issue = [&](int g) {
+		if (ki == 0) {
+			/* enter unit ti: plan of its gathers, its data for the adding side, its L rows */
+			const int par = ti & 1, cnt = dI.la + dI.lb;
+			gn = 0;
+#pragma unroll
+			for (int u = 0; u < 8; u++) {
+				const int row = u * 4 + (lane >> 3);
+				const int jn = __shfl_sync(FULL, xI.j, min(row, cnt - 1));
+				gsrc[u] = Rold + (size_t)jn * ld + pc2;
+				if (row < cnt)
+					gn = u + 1;
+			}
+			m_a[par * 32 + lane] = xI.a;
+			m_pos[par * 32 + lane] = xI.pos;
+			m_ep[par * 32 + lane] = xI.ep;
+			if (lane == 0) {
+				m_len[par * 2] = cnt;
+				m_len[par * 2 + 1] = dI.la;
+			}
+			const double *LrowA = Lold + (size_t)dI.ia * ld, *LrowB = Lold + (size_t)dI.ib * ld;
+			double *LsA = Ls + (size_t)par * 2 * ld, *LsB = LsA + ld;
+			for (int q = lane; q < (ld >> 1); q += 32) {
+				cp_async16(LsA + 2 * q, LrowA + 2 * q);
+				if (dI.lb)
+					cp_async16(LsB + 2 * q, LrowB + 2 * q);
+			}
+			/* the loads of the units behind it start now and have a whole unit to land */
+			if (ti + 1 < n_mine)
+				load_lane(dN, xN);
+			Desc d2 = dN;
+			if (ti + 2 < n_mine)
+				load_desc(ti + 2, d2);
+			dI = dN;
+			dN = d2;
+		}
+		{
+			const int k0 = ki * KT;
+			const bool lane_ok = k0 + pc2 < ld;
+			const uint32_t dst = gdst + (uint32_t)g * (uint32_t)(td * 8);
+#pragma unroll
+			for (int u = 0; u < 8; u++)
+				cp_async16_if(dst + (uint32_t)(u * 4 * TS * 8), gsrc[u] + k0, lane_ok && u < gn);
+		}
+		if (++ki == nt) {
+			ki = 0;
+			ti++;
+			xI = xN;
+		}
+	};
+
+	int gi = 0;                 /* ring slot of the next tile to issue */
+	for (int g = 0; g < NT - 1; g++) {
+		if (g < total) {
+			issue(gi);
+			gi = gi + 1 == NT ? 0 : gi + 1;
+		}
+		cp_async_commit();
+	}
+	int gc = 0;                 /* ring slot of the tile being added */
+	int kc = 0, par = 0, cnt = 0;
+	double s = 0.0, a = 0.0;
+	const double *Lrow = Ls;
+	for (long g = 0; g < total; g++) {
+		if (g + NT - 1 < total) {
+			issue(gi);
+			gi = gi + 1 == NT ? 0 : gi + 1;
+		}
+		cp_async_commit();
+		cp_async_wait<NT - 1>();       /* tile g (and the L rows that travel with a first tile) has landed */
+		__syncwarp();
+		if (kc == 0) {
+			cnt = m_len[par * 2];
+			const int la = m_len[par * 2 + 1];
+			a = m_a[par * 32 + lane];
+			Lrow = Ls + (size_t)par * 2 * ld + (lane < la ? 0 : ld);
+			s = 0.0;
+		}
+		if (lane < cnt)
+			s = dot_tile(s, Lrow + kc * KT, tiles + (size_t)gc * td + lane * TS, min(KT, F - kc * KT));
+		gc = gc + 1 == NT ? 0 : gc + 1;
+		if (++kc == nt) {
+			if (lane < cnt) {
+				const double e = __dmul_rn(p.alpha2, __dsub_rn(a, s));
+				p.e_csc[m_ep[par * 32 + lane]] = e;
+				p.e_csr[m_pos[par * 32 + lane]] = e;
+			}
+			kc = 0;
+			par ^= 1;
+		}
+		__syncwarp();                  /* the slot and the unit data may be rewritten by the next issue */
+	}
+	cp_async_wait<0>();
 }
 
 /*
@@ -746,9 +981,9 @@ k_update_L_res(const LoopArgs p, const double *__restrict__ Lold, double *__rest
 		if (m > 0) {
 #pragma unroll
 			for (int g = 0; g < NG - 1; g++)
-				Lout[g * 32 + lane] = acc[g];
+				st_row(Lout + g * 32 + lane, acc[g], p.cs_store);
 			if (ok_last)
-				Lout[klast] = acc[NG - 1];
+				st_row(Lout + klast, acc[NG - 1], p.cs_store);
 		}
 		r = rn;
 		i = i2;
@@ -1000,6 +1235,185 @@ k_chain_ws(const ChainSide A, const ChainSide B, long units_a, int F, int ld)
 			__syncwarp();                 /* ring entry t + WS_IDX_BLOCKS overwrites this block */
 		}
 		cp_async_wait<0>();
+	}
+}
+
+/*
+ * k_acc: the ordered accumulations (matFact.c:48-51) straight from L2 into registers.
+ *
+ * A unit is (stored row or column r, block of GW feature groups); one warp takes a unit and keeps
+ * its GW x 32 running values in registers (lane = feature).  The nonzeros of the chain come in
+ * blocks of 32 (index and e_n of nonzero 32q + l in lane l, handed to all lanes through a
+ * 384-byte shared-memory slot of the warp), and are taken in sub-blocks of ACC_SB: the
+ * sub-block's row pointers and e_n live in registers, and the groups are walked with two register
+ * sets, the ACC_SB loads of group q+1 in flight while the ACC_SB additions of group q run
+ * (16 x 256 bytes in flight per warp, ~20 warps per SM).  The loads are written as PTX with the
+ * group offset as an immediate, in program order: left to the compiler, an unrolled group loop
+ * hoists the loads of all groups and spills, and a rolled one pays two address instructions per
+ * load.  Lanes past F in the last group read the doubles that follow the row (never used; the
+ * factor buffers end with 32 spare doubles).
+ * Units are handed out by an atomic counter (*ticket, zeroed before the launch), heaviest first:
+ * side B (the columns, long chains), then side A (the rows); the next unit's position, length
+ * and first block of indices are fetched while the current one is being added.
+ */
+template <int OFF>
+__device__ __forceinline__ double ldg_imm(const double *p)
+{
+	double v;
+	asm volatile("ld.global.nc.f64 %0, [%1+%2];" : "=d"(v) : "l"(p), "n"(OFF));
+	return v;
+}
+
+/* the same under a predicate (the lanes past F of a partial last group load nothing) */
+template <int OFF>
+__device__ __forceinline__ double ldg_imm_if(const double *p, bool ok)
+{
+	double v = 0.0;
+	asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %3, 0;\n\t@q ld.global.nc.f64 %0, [%1+%2];\n\t}"
+	             : "+d"(v) : "l"(p), "n"(OFF), "r"((int)ok));
+	return v;
+}
+
+template <int Q, bool LAST>
+__device__ __forceinline__ void acc_load_q(double (&x)[ACC_SB], const double *const (&rp)[ACC_SB], bool ok_last)
+{
+#pragma unroll
+	for (int n = 0; n < ACC_SB; n++)
+		x[n] = (LAST && MF_ACC_PRED) ? ldg_imm_if<Q * 256>(rp[n], ok_last) : ldg_imm<Q * 256>(rp[n]);
+}
+
+/* all GW x ACC_SB loads of a sub-block first, then the GW chains: with ~170 registers a warp
+ * keeps up to 56 loads (14 KB) in flight and twelve warps per SM cover the L2 latency
+ * (measured: two register sets with one group fetched ahead left the additions waiting
+ * on every group, 10.6 TB/s; profiles/r02_notes.md) */
+template <int GW, int Q>
+struct AccGroups {
+	static __device__ __forceinline__ void load(double (&x)[GW][ACC_SB], const double *const (&rp)[ACC_SB], bool ok_last)
+	{
+		acc_load_q<Q, Q == GW - 1>(x[Q], rp, ok_last);
+		AccGroups<GW, Q + 1>::load(x, rp, ok_last);
+	}
+	static __device__ __forceinline__ void add(double (&acc)[GW], const double (&x)[GW][ACC_SB],
+	                                           const double (&e)[ACC_SB], int m)
+	{
+		acc[Q] = acc_chain(acc[Q], x[Q], e, m);
+		AccGroups<GW, Q + 1>::add(acc, x, e, m);
+	}
+};
+template <int GW> struct AccGroups<GW, GW> {
+	static __device__ __forceinline__ void load(double (&)[GW][ACC_SB], const double *const (&)[ACC_SB], bool) {}
+	static __device__ __forceinline__ void add(double (&)[GW], const double (&)[GW][ACC_SB], const double (&)[ACC_SB], int) {}
+};
+
+constexpr int ACC_WARPS = 4;
+
+template <int GW>
+__global__ void __launch_bounds__(ACC_WARPS * 32, GW <= 2 ? 8 : GW <= 4 ? 6 : ACC_CTAS)
+k_acc(const ChainSide A, const ChainSide B, long units_b, long units_total, int F, int ld,
+      unsigned long long *ticket)
+{
+	/* per warp: 32 indices (as doubles' worth of row offsets) and 32 e_n */
+	__shared__ __align__(16) int s_idx[ACC_WARPS][32];
+	__shared__ __align__(16) double s_e[ACC_WARPS][32];
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	const int ng = (F + 31) >> 5;
+	const int nb = (ng + GW - 1) / GW;          /* group blocks per chain */
+
+	auto take = [&]() {
+		unsigned long long t = 0;
+		if (lane == 0)
+			t = atomicAdd(ticket, 1ull);
+		return (long)__shfl_sync(FULL, t, 0);
+	};
+	/* position of unit w: side, stored row, group block */
+	struct Unit { bool is_b; int r, gb, own, beg, m; int idx0; double e0; };
+	auto describe = [&](long w, Unit &u) {
+		u.is_b = w < units_b;
+		const ChainSide &sd = u.is_b ? B : A;
+		const long v = u.is_b ? w : w - units_b;
+		u.r = sd.begin + (int)(v / nb);
+		u.gb = (int)(v % nb);
+		u.own = sd.id[u.r];
+		u.beg = sd.ptr[u.r];
+		u.m = sd.ptr[u.r + 1] - u.beg;
+	};
+	auto first_block = [&](Unit &u) {
+		const ChainSide &sd = u.is_b ? B : A;
+		const int n = min(lane, u.m - 1);
+		u.idx0 = sd.idx[u.beg + n];
+		u.e0 = sd.e[u.beg + n];
+	};
+
+	long w = take();
+	Unit cur, nxt;
+	if (w < units_total) {
+		describe(w, cur);
+		first_block(cur);
+	}
+	while (w < units_total) {
+		const long wn = take();
+		const ChainSide &sd = cur.is_b ? B : A;
+		const int g0 = cur.gb * GW;
+		const int k0 = g0 * 32 + lane;
+		double acc[GW];
+#pragma unroll
+		for (int q = 0; q < GW; q++) {
+			const int k = k0 + q * 32;
+			acc[q] = (sd.init && k < F) ? sd.init[(size_t)(cur.own - sd.own_off) * ld + k] : 0.0;
+		}
+		const double *srcb = sd.src + k0 - (size_t)sd.src_off * ld;
+		const bool ok_last = k0 + (GW - 1) * 32 < F;      /* this lane's element of the block's last group exists */
+		if (wn < units_total)
+			describe(wn, nxt);
+		int bi = cur.idx0;
+		double be = cur.e0;
+		for (int b0 = 0; b0 < cur.m; b0 += 32) {
+			const int mb = min(32, cur.m - b0);
+			__syncwarp();                      /* the slot is no longer read */
+			s_idx[warp][lane] = bi;
+			s_e[warp][lane] = be;
+			__syncwarp();
+			if (b0 + 32 < cur.m) {             /* next block of this chain */
+				const int n = min(b0 + 32 + lane, cur.m - 1);
+				bi = sd.idx[cur.beg + n];
+				be = sd.e[cur.beg + n];
+			} else if (wn < units_total) {
+				first_block(nxt);              /* first block of the next unit */
+			}
+			for (int s0 = 0; s0 < mb; s0 += ACC_SB) {
+				const int m = min(ACC_SB, mb - s0);
+				const double *rp[ACC_SB];
+				double e[ACC_SB];
+				{
+					int ii[ACC_SB];
+#pragma unroll
+					for (int n = 0; n < ACC_SB; n += 4) {
+						const int4 i4 = *reinterpret_cast<const int4 *>(&s_idx[warp][s0 + n]);
+						ii[n] = i4.x; ii[n + 1] = i4.y; ii[n + 2] = i4.z; ii[n + 3] = i4.w;
+					}
+#pragma unroll
+					for (int n = 0; n < ACC_SB; n += 2) {
+						const double2 e2 = ld2(&s_e[warp][s0 + n]);
+						e[n] = e2.x;
+						e[n + 1] = e2.y;
+					}
+#pragma unroll
+					for (int n = 0; n < ACC_SB; n++)      /* past the end: a valid row again, never added */
+						rp[n] = srcb + (size_t)ii[n] * ld;
+				}
+				double x[GW][ACC_SB];
+				AccGroups<GW, 0>::load(x, rp, ok_last);
+				AccGroups<GW, 0>::add(acc, x, e, m);
+			}
+		}
+#pragma unroll
+		for (int q = 0; q < GW; q++) {
+			const int k = k0 + q * 32;
+			if (k < F)
+				chain_store(sd, cur.own, ld, k, acc[q]);
+		}
+		w = wn;
+		cur = nxt;
 	}
 }
 

@@ -178,7 +178,27 @@ int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
 	n_sm = std::max(1, n_sm);
 	const mf_pattern &pt = s->pat;
 	const int share = (int)std::min<long>(1 << 30, (long)pt.nnz / (16L * n_sm));
-	const int long_thresh = pl->opt_long_row > 0 ? pl->opt_long_row : std::max(2 * CH, share);
+	/* split mode (option "pair", the default when eight dot warps fit): the dots of rows of at most
+	 * 32 nonzeros by k_dot_pair, of longer rows by k_dot, every accumulation by k_acc */
+	int pair_warps = pl->opt_pair_warps;
+	if (pair_warps != 4 && pair_warps != 5 && pair_warps != 6 && pair_warps != 8)
+		pair_warps = 8;
+	auto pair_bytes = [&](int nt) { return pair_warps * ((size_t)nt * 32 * TS + 4 * (size_t)pl->ld + 130) * sizeof(double); };   /* mf::dot_units_doubles */
+	/* default: where it was measured ahead (inst60000 shape: 377 against 388..400 us per iteration;
+	 * behind on the MovieLens shapes and on one eighth of inst60000): wide factors, a big shard */
+	const int want_split = pl->opt_pair >= 0 ? pl->opt_pair : (F >= 128 && pt.nnz >= 400000);
+	const bool split = warps == 8 && want_split && pair_bytes(2) <= (size_t)max_smem;
+	/* the ring of a k_dot_pair warp is what it has in flight from L2: as deep as one CTA of
+	 * eight warps per SM can hold (measured latency under load ~2000 cycles: ~100 KB in flight
+	 * per SM for 50 B/clk) */
+	int pair_nt = 2;
+	if (split) {
+		pair_nt = pl->opt_pair_stages >= 2 ? std::min(6, pl->opt_pair_stages) : 6;
+		pair_nt = std::min(pair_nt, (F + 15) / 16 + 1);      /* the ring runs at most one unit ahead */
+		while (pair_nt > 2 && pair_bytes(pair_nt) > (size_t)max_smem)
+			pair_nt--;
+	}
+	const int long_thresh = split ? 32 : pl->opt_long_row > 0 ? pl->opt_long_row : std::max(2 * CH, share);
 	const int deep_thresh = pl->opt_long_col > 0 ? pl->opt_long_col
 	                                             : std::max(64, (int)std::min<long>(1 << 30, (long)pt.nnz / (8L * n_sm)));
 	int n_long = 0, n_deep_rows = 0, n_deep_cols = 0;
@@ -199,7 +219,7 @@ int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
 	int CR = 0, RST = pl->ld + (((pl->ld / 2) & 1) ? 0 : 2);
 	s->res_ng = 0;
 	s->res_smem = 0;
-	if (warps > 1 && pl->opt_resident && F <= 256 && n_long < pt.n_rows) {
+	if (warps > 1 && pl->opt_resident && !split && F <= 256 && n_long < pt.n_rows) {
 		const int longest = pt.row_ptr[n_long + 1] - pt.row_ptr[n_long];
 		CR = std::min(32, longest);
 		if (pl->opt_res_rows > 0)
@@ -211,18 +231,56 @@ int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
 			s->res_smem = 2 * per_warp;          /* mf::RES_WARPS warps per CTA */
 		}
 	}
-	TRY(mf_kernels_prepare(warps, s->k1_smem, s->res_ng, s->res_smem));
+	/* Rows of at most 32 nonzeros two to a warp (k_update_L_pair, mf_loop.cuh): the longest
+	 * unpaired row with the shortest one while their lengths add up to at most 32.  Rows are
+	 * stored longest first, so [n_mid, n_rows) are the rows of at most 32 nonzeros. */
+	std::vector<int> units;        /* 8 ints per unit: {ia, basea, la, ib, baseb, lb, 0, 0} */
+	s->n_units = 0;
+	s->n_mid = pt.n_rows;
+	s->pair_smem = 0;
+	s->split = split;
+	if (split) {
+		s->pair_smem = pair_bytes(pair_nt);
+		s->pair_nt = pair_nt;
+		s->pair_warps = pair_warps;
+		s->n_mid = n_long;
+		auto unit = [&](int ra, int basea, int la, int rb) {
+			const int ib = rb >= 0 ? pt.row_id[rb] - s->user_lo : 0;
+			const int baseb = rb >= 0 ? pt.row_ptr[rb] : 0, lb = rb >= 0 ? pt.row_ptr[rb + 1] - baseb : 0;
+			const int d[8] = {pt.row_id[ra] - s->user_lo, basea, la, ib, baseb, lb, 0, 0};
+			units.insert(units.end(), d, d + 8);
+		};
+		/* rows longer than 32 (the rows [0, n_long), long_thresh = 32): chunks of 32 */
+		for (int r = 0; r < n_long; r++)
+			for (int pos = pt.row_ptr[r]; pos < pt.row_ptr[r + 1]; pos += 32)
+				unit(r, pos, std::min(32, pt.row_ptr[r + 1] - pos), -1);
+		/* the others two to a warp: the longest unpaired row with the shortest one while their
+		 * lengths add up to at most 32 (rows are stored longest first) */
+		int lo = n_long, hi = pt.n_rows - 1;
+		while (lo <= hi) {
+			const int la = pt.row_ptr[lo + 1] - pt.row_ptr[lo];
+			const bool two = lo < hi && la + (pt.row_ptr[hi + 1] - pt.row_ptr[hi]) <= 32;
+			unit(lo, pt.row_ptr[lo], la, two ? hi : -1);
+			lo++;
+			if (two)
+				hi--;
+		}
+		s->n_units = (int)(units.size() / 8);
+	}
+	TRY(mf_kernels_prepare(warps, s->k1_smem, s->res_ng, s->res_smem, s->pair_smem, s->pair_warps, s->pair_nt));
 
 	/* chunks of the long rows for k_dot */
 	std::vector<int> chunk_row, chunk_pos;
-	for (int r = 0; r < n_long; r++)
+	for (int r = 0; r < (split ? 0 : n_long); r++)     /* split mode: the chunks are units of k_dot_units */
 		for (int pos = pt.row_ptr[r]; pos < pt.row_ptr[r + 1]; pos += CH) {
 			chunk_row.push_back(r);
 			chunk_pos.push_back(pos);
 		}
 	dev_free(s->d_chunk_row, s->st);
 	dev_free(s->d_chunk_pos, s->st);
-	s->d_chunk_row = s->d_chunk_pos = nullptr;
+	dev_free(s->d_units, s->st);
+	s->d_chunk_row = s->d_chunk_pos = s->d_units = nullptr;
+	TRY(upload(&s->d_units, units.data(), units.size(), s->st));
 	TRY(upload(&s->d_chunk_row, chunk_row.data(), chunk_row.size(), s->st));
 	TRY(upload(&s->d_chunk_pos, chunk_pos.data(), chunk_pos.size(), s->st));
 	CK(cudaStreamSynchronize(s->st));     /* the vectors die with this scope */
@@ -241,6 +299,7 @@ int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
 	a.n_deep_cols = n_deep_cols;
 	a.n_chunks = (int)chunk_row.size();
 	a.user_lo = s->user_lo;
+	a.cs_store = pl->opt_cs_store;
 	a.alpha2 = pl->alpha * 2;     /* matFact.c:45: alpha * 2 * (...) associates left, exact */
 	a.row_id = s->d_row_id;
 	a.row_ptr = s->d_row_ptr;
@@ -255,7 +314,7 @@ int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
 	a.item_slot = pl->nshards > 1 ? s->d_item_slot : nullptr;
 	a.e_csc = s->d_e_csc;
 	a.e_csr = s->d_e_csr;
-	s->k1_blocks = (a.n_rows - n_long + warps - 1) / warps;
+	s->k1_blocks = (s->n_mid - n_long + warps - 1) / warps;      /* rows [n_mid, n_rows) go to the paired launch */
 	if (s->res_ng) {
 		/* persistent warps: as many CTAs as are resident at once, rows dealt round robin */
 		int smem_sm = 228 * 1024;
@@ -394,10 +453,12 @@ static int shard_create(mfgpu_plan *pl, mf_shard *s, int dev, const mfgpu_entry 
 	tc.lap("create: pattern upload");
 	TRY(dev_alloc((void **)&s->d_e_csc, ((size_t)p.nnz + 1) * sizeof(double), s->st));
 	TRY(dev_alloc((void **)&s->d_e_csr, ((size_t)p.nnz + 1) * sizeof(double), s->st));
+	TRY(dev_alloc((void **)&s->d_ticket, 64, s->st));
 
 	const size_t nu = (size_t)(s->user_hi - s->user_lo);
-	const size_t lbytes = (nu * pl->ld + 2) * sizeof(double);
-	const size_t rbytes = ((size_t)pl->items * pl->ld + 2) * sizeof(double);
+	/* 34 spare doubles: k_acc lets the lanes past F of the last feature group read what follows the row */
+	const size_t lbytes = (nu * pl->ld + 34) * sizeof(double);
+	const size_t rbytes = ((size_t)pl->items * pl->ld + 34) * sizeof(double);
 	/* rank mode: peers store their rows of R_new straight into this replica (push exchange), so
 	 * R must be exportable over CUDA IPC, which pool memory is not */
 	s->r_plain = pl->comm != nullptr;
@@ -495,7 +556,7 @@ static void shard_destroy(mf_shard *s)
 	void *ptrs[] = {s->d_row_id, s->d_row_ptr, s->d_col_idx, s->d_epos, s->d_col_id, s->d_col_ptr,
 	                s->d_row_idx, s->d_val, s->d_e_csc, s->d_e_csr, s->d_mask_ptr, s->d_mask_col,
 	                s->d_first_free, s->d_item_slot, s->d_touched_item, s->d_push_owner, s->d_push_row, s->d_contrib, s->part_v, s->part_j,
-	                s->nan_first, s->d_best, s->L_keep, s->R_keep, s->d_chunk_row, s->d_chunk_pos};
+	                s->nan_first, s->d_best, s->L_keep, s->R_keep, s->d_chunk_row, s->d_chunk_pos, s->d_units, s->d_ticket};
 	for (void *q : ptrs)
 		dev_free(q, s->st);
 	tc.lap("destroy: other buffers");
@@ -725,6 +786,9 @@ static int plan_create(mfgpu_plan **out, int users, int items, int features, int
 	pl->opt_resident = 1;
 	pl->opt_res_rows = 0;
 	pl->opt_chain_ws = 1;
+	pl->opt_pair = -1;           /* split mode by shape (mf_configure_shard) */
+	pl->opt_pair_warps = 4;
+	pl->opt_pair_stages = 2;
 	pl->opt_exchange = -1;       /* peer memory when it can be had */
 
 	TraceClock tc;
@@ -1084,6 +1148,11 @@ extern "C" int mfgpu_plan_set_option(mfgpu_plan *pl, const char *name, int value
 	else if (!strcmp(name, "chain_ws")) pl->opt_chain_ws = value;
 	else if (!strcmp(name, "dot_stages")) pl->opt_dot_stages = value;
 	else if (!strcmp(name, "acc_rows")) pl->opt_acc_rows = value;
+	else if (!strcmp(name, "cs_store")) pl->opt_cs_store = value;
+	else if (!strcmp(name, "pair")) pl->opt_pair = value;
+	else if (!strcmp(name, "pair_stages")) pl->opt_pair_stages = value;
+	else if (!strcmp(name, "pair_warps")) pl->opt_pair_warps = value;
+	else if (!strcmp(name, "acc_gw")) pl->opt_acc_gw = value;
 	else if (!strcmp(name, "exchange")) {
 		/* rank mode, collective: 0 = ncclAllReduce; peer memory when available: 1 / -1 = low
 		 * latency (value, tag) exchange (k_xchg_ll), 2 = pull (k_apply_R_xchg), 3 = push with

@@ -24,6 +24,7 @@ struct LoopArgs {
 	int n_cols, n_deep_cols;
 	int n_chunks;     /* chunks of the rows [0, n_long) for k_dot         */
 	int user_lo;      /* first user of this shard; L holds rows user_lo.. */
+	int cs_store;     /* 1: rows of L_new are stored evict-first (st.global.cs): they are not read again before the next iteration, L_old is (by the by-item pass) */
 	double alpha2;    /* alpha * 2, exact                                 */
 	const int *row_id, *row_ptr, *col_idx, *epos;
 	const double *val;

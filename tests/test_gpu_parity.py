@@ -92,6 +92,40 @@ def test_launch_options_do_not_change_bits(gpu, oracle, options):
     _check_against_oracle(gpu, oracle, inst, options=options)
 
 
+@pytest.mark.parametrize("case", [
+    (300, 500, 200, 0.03, 3, {"pair": 1}),            # ~15 nonzeros per row, wide factors: two rows per warp
+    (300, 500, 200, 0.03, 3, {"pair": 0}),            # the same through the fused one-row-per-warp kernel
+    (257, 300, 37, 0.05, 4, {"pair": 1}),             # odd F, odd number of rows, some rows empty
+    (100, 90, 64, 0.30, 3, {"pair": 1}),              # rows around 27: most of them stay single
+    (500, 40, 10, 0.40, 5, {"pair": 1, "pair_stages": 4}),      # one tile per unit: the ring is cut to 2
+    (64, 2000, 16, 0.01, 3, {"pair": 1, "pair_warps": 8, "pair_stages": 4, "cs_store": 1}),
+    (300, 500, 200, 0.03, 3, {"pair": 1, "pair_warps": 6, "pair_stages": 3, "long_col": 30}),
+    (300, 500, 200, 0.03, 3, {"pair": 1, "pair_warps": 5, "pair_stages": 6, "acc_gw": 3}),
+    (20, 300, 100, 0.60, 3, {"pair": 1}),             # rows of ~180 nonzeros: chunks of 32 as units
+    (10, 2000, 8, 0.90, 3, {"pair": 1}),              # very long rows, short columns
+    (2000, 10, 8, 0.90, 3, {"pair": 1, "long_col": 100}),       # very long columns: k_chain_ws beside k_acc
+    (2000, 10, 8, 0.90, 3, {"pair": 1, "long_col": 1000000}),   # the same chains through k_acc
+    (5, 6, 1000, 0.50, 2, {"pair": 1}),               # F = 1000: four blocks of eight feature groups
+    (12, 9, 200, 0.50, 3, {"pair": 1, "acc_gw": 1}),
+    (40, 130, 31, 0.20, 5, {"pair": 1, "graph": 0}),
+])
+def test_split_mode_bit_exact(gpu, oracle, case):
+    """Split mode (k_dot_units + k_acc: dots two rows to a warp, accumulations straight from L2)
+    against the oracle; it is the default only for wide factors on big shards."""
+    users, items, F, dens, iters, options = case
+    inst = synth.random_instance(users, items, F, dens, iters, 0.002, seed=users + 3 * items, values="real")
+    _check_against_oracle(gpu, oracle, inst, options=options)
+
+
+def test_split_mode_unsorted_entries(gpu, oracle):
+    inst = synth.random_instance(25, 40, 6, 0.3, 11, 0.003, seed=9, values="real")
+    rng = np.random.default_rng(3)
+    e = inst.entries.copy()
+    rng.shuffle(e)
+    e = np.concatenate([e, e[5:9]])
+    _check_against_oracle(gpu, oracle, Instance(inst.iters, inst.alpha, inst.features, 25, 40, e), options={"pair": 1})
+
+
 def test_edge_cases(gpu, oracle):
     # no nonzeros at all; a user who rated everything (prints nothing); empty matrices
     e = np.zeros(0, dtype=ENTRY_DTYPE)

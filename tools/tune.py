@@ -24,7 +24,8 @@ def main():
         inst = synth.ml_like(users=U, items=I, nnz=int(n), features=F)
     else:
         U = int(sys.argv[1])
-        inst = synth.inst60000_like(users=U, items=I, features=F)
+        inst = synth.inst60000_like(users=U, items=I, features=F, lo=int(os.environ.get('TUNE_LO', 10)),
+                                    hi=int(os.environ.get('TUNE_HI', 20)))
     L, R = api.random_fill_LR(U, I, F)
     print("U=%d I=%d F=%d nnz=%d" % (U, I, F, inst.nnz), flush=True)
     for opts in sets:
