@@ -101,25 +101,67 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
 }
 
 
-/* (value, tag) pairs of the low-latency exchange (mf_iter.cu): one 16-byte store / load, which
- * NVLink and L2 deliver whole, so a reader that sees the tag it waits for also has the value --
- * no fence, no flag of its own (the idea of NCCL's LL protocol, with 8-byte payloads) */
-__device__ __forceinline__ void st_pair(double *p, double v, unsigned long long tag)
+/* ---- waiting for another GPU ------------------------------------------------------------
+ * A wait for a peer is bounded by TIME (%globaltimer, nanoseconds), not by a poll count: under a
+ * profiler's replay, a debugger or a peer delayed by a page fault a poll count runs out long
+ * before anything is wrong.  A wait that does run out sets the error word of the rank's sync
+ * block and gives up (the kernel finishes with garbage in the affected elements); the host finds
+ * the word after its next sync and reports MFGPU_ECOMM -- no trap, no poisoned context. */
+__device__ __forceinline__ unsigned long long global_ns()
 {
-	asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(__double_as_longlong(v)), "l"(tag)
-	             : "memory");
+	unsigned long long t;
+	asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+	return t;
 }
 
-__device__ __forceinline__ double ld_pair_when(const double *p, unsigned long long tag)
+struct WaitCtl {
+	unsigned long long *err;           /* error word of this rank's sync block */
+	unsigned long long timeout_ns;
+};
+
+/* true: keep polling; false: out of time (the error word is set) */
+__device__ __forceinline__ bool wait_more(const WaitCtl &w, unsigned &spins, unsigned long long &t0, int who)
+{
+	if ((++spins & 1023u) != 0)
+		return true;
+	if (*(volatile unsigned long long *)w.err)         /* somebody here gave up already: do not wait again */
+		return false;
+	const unsigned long long now = global_ns();
+	if (t0 == 0)
+		t0 = now;
+	if (now - t0 <= w.timeout_ns)
+		return true;
+	atomicCAS(w.err, 0ull, (unsigned long long)(who + 1));
+	return false;
+}
+
+/* (value, tag) pairs of the low-latency exchange (mf_iter.cu): a pair travels as ONE 16-byte
+ * store and is read by ONE 16-byte load, so a reader that sees the tag it waits for also has the
+ * value -- no fence, no flag of its own (the idea of NCCL's LL protocol, with 8-byte payloads).
+ * "One" in the sense of the PTX memory model: the accesses use the SCALAR type .b128 (ld/st
+ * .b128, PTX ISA 8.3, sm_70+) with .relaxed.sys semantics -- one strong memory operation each
+ * (SASS: STG.E.128.STRONG.SYS / LDG.E.128.STRONG.SYS) -- and not the vector form .v2.u64 of
+ * round 1, which the model defines as two independent 8-byte operations that a reader may see
+ * one without the other.  tests/rank_mode_worker.py soaks the exchange on top of that (replicas
+ * hashed against each other every few iterations). */
+__device__ __forceinline__ void st_pair(double *p, double v, unsigned long long tag)
+{
+	asm volatile("{\n\t.reg .b128 q;\n\tmov.b128 q, {%1, %2};\n\tst.relaxed.sys.global.b128 [%0], q;\n\t}"
+	             ::"l"(p), "l"(__double_as_longlong(v)), "l"(tag) : "memory");
+}
+
+__device__ __forceinline__ double ld_pair_when(const double *p, unsigned long long tag, const WaitCtl &w, int who)
 {
 	unsigned long long v, t;
 	unsigned spins = 0;
+	unsigned long long t0 = 0;
 	for (;;) {
-		asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(v), "=l"(t) : "l"(p) : "memory");
+		asm volatile("{\n\t.reg .b128 q;\n\tld.relaxed.sys.global.b128 q, [%2];\n\tmov.b128 {%0, %1}, q;\n\t}"
+		             : "=l"(v), "=l"(t) : "l"(p) : "memory");
 		if (t == tag)
 			return __longlong_as_double((long long)v);
-		if (++spins > (1u << 24))      /* a rank that never delivers: fail instead of hanging */
-			__trap();
+		if (!wait_more(w, spins, t0, who))
+			return 0.0;
 	}
 }
 

@@ -18,12 +18,14 @@
  *   push:  [16+h] done_from[h]   rank h has stored all its contributions of the iteration here
  *          [32+h] ready_from[h]  rank h has stored its rows of R_new here
  *          [48]   epoch          iterations completed by this rank
- *          [49]   CTAs of k_reduce_bcast finished */
+ *          [49]   CTAs of k_reduce_bcast finished
+ *          [50]   error word: a wait for a peer ran out of time (host: MFGPU_ECOMM) */
 #define MF_SYNC_WORDS 64
 #define MF_SYNC_DONE 16
 #define MF_SYNC_READY 32
 #define MF_SYNC_EPOCH 48
 #define MF_SYNC_CTAS 49
+#define MF_SYNC_ERR 50      /* set by a device-side wait that ran out of time (value: 1 + the rank waited for, or 99) */
 
 /* ---- NCCL, bound at run time (only rank mode needs it) ---------------------- */
 typedef struct ncclComm *mf_ncclComm_t;
@@ -65,6 +67,8 @@ void mf_arena_reset(mfgpu_comm *c);        /* mf_plan.cu; collective over the ra
 
 struct mf_shard {
 	int dev;
+	int me;                                  /* index of this shard among the nshards of the problem (rank mode: the rank) */
+	unsigned long long *d_sync;              /* this shard's sync block (MF_SYNC_WORDS words), mapped by every peer */
 	cudaStream_t st, st2;                    /* st2: the long-row launch runs beside the short rows */
 	mf_pattern pat;
 	int user_lo, user_hi;
@@ -133,6 +137,9 @@ struct mfgpu_plan {
 	 *      one 16-byte store and the readers poll for the tag of the iteration: no fences, no
 	 *      flag words; one launch (k_xchg_ll) reduces the own block and unpacks the others' */
 	int xchg_ipc;
+	int peer_events;                               /* one process, N GPUs: 1 = the event-ordered pull exchange (k_apply_R_peer) instead of the low-latency one */
+	long ll_half;                                  /* doubles per parity half of a (value, tag) pair buffer (G[0], G[1]) */
+	unsigned long long comm_timeout_ns;            /* device-side waits for a peer give up after this long */
 	mf_xchg_arena *arena;                          /* borrowed exchange buffers, or NULL (own) */
 	int slots_per_rank;                            /* push: touched items reduced by one rank (the last may own fewer) */
 	double *peer_G[2][MF_MAX_SHARDS];              /* G[b] of rank h (own rank: the local buffer) */
@@ -142,7 +149,7 @@ struct mfgpu_plan {
 	void *ipc_mapped[5 * MF_MAX_SHARDS];
 	int n_ipc_mapped;
 	/* options */
-	int opt_graph, opt_graph_iters, opt_long_row, opt_long_col, opt_ch, opt_chain_ring, opt_resident, opt_res_rows, opt_chain_ws, opt_exchange, opt_dot_stages, opt_acc_rows, opt_cs_store, opt_pair, opt_pair_stages, opt_pair_warps, opt_acc_gw;
+	int opt_graph, opt_graph_iters, opt_long_row, opt_long_col, opt_ch, opt_chain_ring, opt_resident, opt_res_rows, opt_chain_ws, opt_exchange, opt_dot_stages, opt_acc_rows, opt_cs_store, opt_pair, opt_pair_stages, opt_pair_warps, opt_acc_gw, opt_comm_timeout_ms;
 };
 
 /* ---- shared helpers (defined in mf_capi.cu) ----------------------------------- */
@@ -152,6 +159,7 @@ int mf_usable_devices(int *ids, int cap);
 int mf_configure_shard(mfgpu_plan *pl, mf_shard *s);      /* mf_plan.cu */
 int mf_xchg_setup(mfgpu_plan *pl);                          /* mf_plan.cu: collective over the ranks */
 void mf_xchg_teardown(mfgpu_plan *pl);
+int mf_check_comm_error(mfgpu_plan *pl);                    /* mf_iter.cu: after a sync; MFGPU_ECOMM when a device-side wait timed out */
 /* MFGPU_TRACE=1: wall-clock of the host-side phases (plan creation / destruction, graph
  * builds) on stderr */
 #include <chrono>

@@ -64,6 +64,17 @@ struct PeerSync {
 	int n;
 };
 
+/* wait until the word another rank writes has reached `want`; bounded by time (mf_async.cuh) */
+__device__ __forceinline__ void spin_until(const volatile unsigned long long *w, unsigned long long want,
+                                           const WaitCtl &ctl, int who)
+{
+	unsigned spins = 0;
+	unsigned long long t0 = 0;
+	while (*w < want)
+		if (!wait_more(ctl, spins, t0, who))
+			return;
+}
+
 __global__ void k_xchg_signal(unsigned long long *done)
 {
 	__threadfence_system();              /* G[b], written by the kernels before this one */
@@ -74,17 +85,13 @@ __global__ void k_xchg_signal(unsigned long long *done)
 __global__ void __launch_bounds__(256)
 k_apply_R_xchg(int n_touched, int F, int ld, const int *__restrict__ touched_item,
                const double *__restrict__ Rold, const PeerG pg, const PeerSync ps, int b,
-               unsigned long long *sync_own, double *__restrict__ Rnew)
+               unsigned long long *sync_own, double *__restrict__ Rnew, unsigned long long timeout_ns)
 {
 	/* sync_own: done[0..1], consumed[2..3], CTAs finished [4] */
 	__shared__ bool last_cta;
 	if (threadIdx.x < ps.n) {
 		const unsigned long long want = sync_own[2 + b] + 1;
-		const volatile unsigned long long *done = ps.sync[threadIdx.x] + b;
-		unsigned spins = 0;
-		while (*done < want)
-			if (++spins > (1u << 24))    /* a rank that never arrives: fail instead of hanging */
-				__trap();
+		spin_until(ps.sync[threadIdx.x] + b, want, WaitCtl{sync_own + MF_SYNC_ERR, timeout_ns}, threadIdx.x);
 		__threadfence_system();
 	}
 	__syncthreads();
@@ -132,15 +139,8 @@ struct PushPeers {
 	double *Rnew[MF_MAX_SHARDS];
 	unsigned long long *sync[MF_MAX_SHARDS];
 	int n, me;
+	unsigned long long timeout_ns;
 };
-
-__device__ __forceinline__ void spin_until(const volatile unsigned long long *w, unsigned long long want)
-{
-	unsigned spins = 0;
-	while (*w < want)
-		if (++spins > (1u << 24))        /* a rank that never arrives: fail instead of hanging */
-			__trap();
-}
 
 __global__ void k_push_done(const PushPeers pp, const unsigned long long *sync_own)
 {
@@ -157,7 +157,7 @@ k_reduce_bcast(const PushPeers pp, int per, int cnt, int ld, const int *__restri
 	__shared__ bool last_cta;
 	const unsigned long long want = sync_own[MF_SYNC_EPOCH] + 1;
 	if ((int)threadIdx.x < pp.n) {
-		spin_until(sync_own + MF_SYNC_DONE + threadIdx.x, want);
+		spin_until(sync_own + MF_SYNC_DONE + threadIdx.x, want, WaitCtl{sync_own + MF_SYNC_ERR, pp.timeout_ns}, threadIdx.x);
 		__threadfence_system();
 	}
 	__syncthreads();
@@ -198,7 +198,7 @@ k_reduce_bcast(const PushPeers pp, int per, int cnt, int ld, const int *__restri
 			*(volatile unsigned long long *)(pp.sync[threadIdx.x] + MF_SYNC_READY + pp.me) = want;
 			/* ... and stays until everybody's rows are here: when this launch has finished,
 			 * R_new is complete in this replica */
-			spin_until(sync_own + MF_SYNC_READY + threadIdx.x, want);
+			spin_until(sync_own + MF_SYNC_READY + threadIdx.x, want, WaitCtl{sync_own + MF_SYNC_ERR, pp.timeout_ns}, threadIdx.x);
 			__threadfence_system();
 		}
 		if (threadIdx.x == 0) {
@@ -208,22 +208,25 @@ k_reduce_bcast(const PushPeers pp, int per, int cnt, int ld, const int *__restri
 	}
 }
 
-/* ---- rank mode, low-latency exchange ------------------------------------------------------
+/* ---- low-latency exchange (N shards: one process per GPU, or one process driving N GPUs) -----
  * The same data flow as the push exchange, but every element travels as a (value, tag) pair in
  * one 16-byte store (st_pair / ld_pair_when, mf_async.cuh), tag = number of the iteration, and
  * the readers poll the element itself: no fence, no flag word, no launch that only signals.
  *   chain kernels   store (gradient value, tag) into the receive buffer of the reducing rank
- *   k_xchg_ll       CTAs [0, reduce_ctas): one thread per element of the own block of items:
- *                   take the contributions in rank order as they arrive (ranks without a
- *                   nonzero in the item contribute +0.0 and are not waited for: `contrib`),
- *                   add R_old, store R_new here and as (value, tag) into every other rank;
- *                   the other CTAs: one thread per element of the other ranks' blocks: take the
- *                   pair when it arrives and store the value into R_new.
- * The reducing CTAs come first in the grid, so they are resident before any unpacking CTA:
- * they wait only for the chain kernels of the other ranks, the unpacking CTAs only for the
- * reducing CTAs of the other ranks -- no cycle.  Buffers are single: a rank stores
- * contributions of the next iteration only after its own unpacking is complete, i.e. after
- * every reducing rank has read all contributions of this one. */
+ *   k_xchg_ll       reduce part, one thread per element of the own block of items: take the
+ *                   contributions in rank order as they arrive (ranks without a nonzero in
+ *                   the item contribute +0.0 and are not waited for: `contrib`), add R_old, store
+ *                   R_new here and as (value, tag) into every other rank;
+ *                   unpack part, one thread per element of the other ranks' blocks: take the pair
+ *                   when it arrives and store the value into R_new.
+ * Progress does not depend on the order in which the hardware starts CTAs: the grid is never
+ * larger than what is resident at once and every CTA does its share of the reduce part before
+ * its share of the unpack part.  The reduce part waits only for chain kernels of other ranks
+ * (earlier in their streams), the unpack part only for reduce parts: no cycle.
+ * The pair buffers are double (ChainSide::ll_half): iteration t uses half t & 1.  A rank can
+ * be at most one iteration ahead of another (it needs everybody's rows of R_new(t) before its
+ * chain kernels of t + 1 can start), so a half is rewritten only after everyone has read it --
+ * a rank that has no nonzero in an item and therefore is not waited for included. */
 struct LLArgs {
 	double *stage[MF_MAX_SHARDS];     /* pair buffer for R_new rows of every rank (own: unused) */
 	const double *recv;               /* own pair buffer for contributions: [rank][slot in block][ld] */
@@ -232,8 +235,9 @@ struct LLArgs {
 	double *Rnew;
 	const int *touched_item, *contrib;
 	unsigned long long *sync_own;
+	unsigned long long timeout_ns;
+	long half;                        /* doubles per parity half of a pair buffer */
 	int n, me, per, n_touched, lo, cnt, F, ld;
-	unsigned reduce_ctas;
 };
 
 __global__ void __launch_bounds__(256)
@@ -241,37 +245,38 @@ k_xchg_ll(const LLArgs a)
 {
 	__shared__ bool last_cta;
 	const unsigned long long want = a.sync_own[MF_SYNC_EPOCH] + 1;
-	if (blockIdx.x < a.reduce_ctas) {
-		const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
-		if (t < (long)a.cnt * a.F) {
-			const int q = (int)(t / a.F), k = (int)(t % a.F);
-			const int slot = a.lo + q, who = a.contrib[slot];
-			const size_t blk = (size_t)a.per * a.ld;
-			const double *g = a.recv + 2 * ((size_t)q * a.ld + k);
-			double sum = (who & 1) ? ld_pair_when(g, want) : 0.0;
-			for (int h = 1; h < a.n; h++)
-				sum = __dadd_rn(sum, ((who >> h) & 1) ? ld_pair_when(g + 2 * h * blk, want) : 0.0);
-			const size_t o = (size_t)a.touched_item[slot] * a.ld + k;
-			const double v = __dadd_rn(a.Rold[o], sum);
-			a.Rnew[o] = v;
-			const size_t so = 2 * ((size_t)slot * a.ld + k);
-			for (int d = 1; d < a.n; d++) {          /* start with the neighbour: spread the links */
-				int h = a.me + d;
-				if (h >= a.n)
-					h -= a.n;
-				st_pair(a.stage[h] + so, v, want);
-			}
+	const long par = (long)(want & 1) * a.half;
+	const WaitCtl ctl{a.sync_own + MF_SYNC_ERR, a.timeout_ns};
+	const long stride = (long)gridDim.x * blockDim.x;
+	const long t0 = (long)blockIdx.x * blockDim.x + threadIdx.x;
+	const size_t blk = (size_t)a.per * a.ld;
+	const double *recv = a.recv + par;
+	for (long t = t0; t < (long)a.cnt * a.F; t += stride) {
+		const int q = (int)(t / a.F), k = (int)(t % a.F);
+		const int slot = a.lo + q, who = a.contrib[slot];
+		const double *g = recv + 2 * ((size_t)q * a.ld + k);
+		double sum = (who & 1) ? ld_pair_when(g, want, ctl, 0) : 0.0;
+		for (int h = 1; h < a.n; h++)
+			sum = __dadd_rn(sum, ((who >> h) & 1) ? ld_pair_when(g + 2 * h * blk, want, ctl, h) : 0.0);
+		const size_t o = (size_t)a.touched_item[slot] * a.ld + k;
+		const double v = __dadd_rn(a.Rold[o], sum);
+		a.Rnew[o] = v;
+		const size_t so = 2 * ((size_t)slot * a.ld + k);
+		for (int d = 1; d < a.n; d++) {              /* start with the neighbour: spread the links */
+			int h = a.me + d;
+			if (h >= a.n)
+				h -= a.n;
+			st_pair(a.stage[h] + par + so, v, want);
 		}
-	} else {
-		const long u = (long)(blockIdx.x - a.reduce_ctas) * blockDim.x + threadIdx.x;
-		if (u < (long)(a.n_touched - a.cnt) * a.F) {
-			int slot = (int)(u / a.F);
-			const int k = (int)(u % a.F);
-			if (slot >= a.lo)
-				slot += a.cnt;                        /* skip the own block */
-			const double v = ld_pair_when(a.stage_own + 2 * ((size_t)slot * a.ld + k), want);
-			a.Rnew[(size_t)a.touched_item[slot] * a.ld + k] = v;
-		}
+	}
+	const double *stage_own = a.stage_own + par;
+	for (long u = t0; u < (long)(a.n_touched - a.cnt) * a.F; u += stride) {
+		int slot = (int)(u / a.F);
+		const int k = (int)(u % a.F);
+		if (slot >= a.lo)
+			slot += a.cnt;                            /* skip the own block */
+		const double v = ld_pair_when(stage_own + 2 * ((size_t)slot * a.ld + k), want, ctl, slot / a.per);
+		a.Rnew[(size_t)a.touched_item[slot] * a.ld + k] = v;
 	}
 	/* the last CTA to get here closes the iteration */
 	__syncthreads();
@@ -292,6 +297,7 @@ __global__ void __launch_bounds__(256)
 k_ll_repush(const LLArgs a, const PeerG recv_of)
 {
 	const unsigned long long want = a.sync_own[MF_SYNC_EPOCH] + 1;
+	const long par = (long)(want & 1) * a.half;
 	const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
 	if (t >= (long)a.n_touched * a.F)
 		return;
@@ -299,7 +305,7 @@ k_ll_repush(const LLArgs a, const PeerG recv_of)
 	if (!((a.contrib[slot] >> a.me) & 1))
 		return;
 	const size_t row = (size_t)a.me * a.per + slot % a.per;
-	st_pair(const_cast<double *>(recv_of.g[slot / a.per]) + 2 * (row * a.ld + k), 0.0, want);
+	st_pair(const_cast<double *>(recv_of.g[slot / a.per]) + par + 2 * (row * a.ld + k), 0.0, want);
 }
 
 } // namespace mf
@@ -384,6 +390,7 @@ static mf::ChainSide side_L(const mfgpu_plan *, const mf_shard *s, int c, int be
 	d.out_slot = nullptr;
 	d.out_owner = nullptr;
 	d.ll_epoch = nullptr;
+	d.ll_half = 0;
 	return d;
 }
 
@@ -399,14 +406,17 @@ static mf::ChainSide side_R(const mfgpu_plan *pl, const mf_shard *s, int c, int 
 	d.out_owner = nullptr;
 	d.out_slot = pl->nshards > 1 ? s->d_item_slot : nullptr;
 	d.ll_epoch = nullptr;
+	d.ll_half = 0;
 	if (pl->xchg_ipc >= 2 && rout == nullptr) {
 		/* push / low-latency exchange: rows go to the reducing rank's receive buffer (its G[0]) */
 		d.out_slot = s->d_push_row;
 		d.out_owner = s->d_push_owner;
-		for (int h = 0; h < pl->comm->nranks; h++)
+		for (int h = 0; h < pl->nshards; h++)
 			d.peer_out[h] = pl->peer_G[0][h];
-		if (pl->xchg_ipc == 3)
-			d.ll_epoch = pl->d_sync + MF_SYNC_EPOCH;
+		if (pl->xchg_ipc == 3) {
+			d.ll_epoch = s->d_sync + MF_SYNC_EPOCH;
+			d.ll_half = pl->ll_half;
+		}
 	}
 	return d;
 }
@@ -569,15 +579,15 @@ static int enqueue_xchg(mfgpu_plan *pl, mf_shard *s, int c, int b)
 {
 	mf::PeerG pg;
 	mf::PeerSync ps;
-	pg.n = ps.n = pl->comm->nranks;
+	pg.n = ps.n = pl->nshards;
 	for (int h = 0; h < pg.n; h++) {
 		pg.g[h] = pl->peer_G[b][h];
 		ps.sync[h] = pl->peer_sync[h];
 	}
 	const long total = (long)pl->n_touched * pl->F;
-	mf::k_xchg_signal<<<1, 1, 0, s->st>>>(pl->d_sync + b);
+	mf::k_xchg_signal<<<1, 1, 0, s->st>>>(s->d_sync + b);
 	mf::k_apply_R_xchg<<<(unsigned)((total + 255) / 256), 256, 0, s->st>>>(
-	    pl->n_touched, pl->F, pl->ld, s->d_touched_item, s->R[c], pg, ps, b, pl->d_sync, s->R[1 - c]);
+	    pl->n_touched, pl->F, pl->ld, s->d_touched_item, s->R[c], pg, ps, b, s->d_sync, s->R[1 - c], pl->comm_timeout_ns);
 	CK(cudaGetLastError());
 	pl->launches += 2;
 	return MFGPU_OK;
@@ -588,8 +598,9 @@ static int enqueue_xchg(mfgpu_plan *pl, mf_shard *s, int c, int b)
 static int enqueue_push(mfgpu_plan *pl, mf_shard *s, int c)
 {
 	mf::PushPeers pp;
-	pp.n = pl->comm->nranks;
-	pp.me = pl->comm->rank;
+	pp.n = pl->nshards;
+	pp.me = s->me;
+	pp.timeout_ns = pl->comm_timeout_ns;
 	for (int h = 0; h < pp.n; h++) {
 		pp.Rnew[h] = pl->peer_R[1 - c][h];
 		pp.sync[h] = pl->peer_sync[h];
@@ -597,10 +608,10 @@ static int enqueue_push(mfgpu_plan *pl, mf_shard *s, int c)
 	const int per = pl->slots_per_rank;
 	const int lo = std::min(pl->n_touched, pp.me * per), cnt = std::min(per, pl->n_touched - lo);
 	const long pairs = (long)cnt * (pl->ld / 2);
-	mf::k_push_done<<<1, 32, 0, s->st>>>(pp, pl->d_sync);
+	mf::k_push_done<<<1, 32, 0, s->st>>>(pp, s->d_sync);
 	/* a rank without items of its own still takes part: it publishes `ready` */
 	mf::k_reduce_bcast<<<(unsigned)std::max(1L, (pairs + 255) / 256), 256, 0, s->st>>>(
-	    pp, per, cnt, pl->ld, s->d_touched_item + lo, s->R[c], s->G[0], pl->d_sync);
+	    pp, per, cnt, pl->ld, s->d_touched_item + lo, s->R[c], s->G[0], s->d_sync);
 	CK(cudaGetLastError());
 	pl->launches += 2;
 	return MFGPU_OK;
@@ -610,8 +621,10 @@ static int enqueue_push(mfgpu_plan *pl, mf_shard *s, int c)
 static mf::LLArgs ll_args(const mfgpu_plan *pl, const mf_shard *s, int c)
 {
 	mf::LLArgs a;
-	a.n = pl->comm->nranks;
-	a.me = pl->comm->rank;
+	a.n = pl->nshards;
+	a.me = s->me;
+	a.timeout_ns = pl->comm_timeout_ns;
+	a.half = pl->ll_half;
 	for (int h = 0; h < a.n; h++)
 		a.stage[h] = pl->peer_G[1][h];
 	a.recv = s->G[0];
@@ -620,22 +633,24 @@ static mf::LLArgs ll_args(const mfgpu_plan *pl, const mf_shard *s, int c)
 	a.Rnew = s->R[1 - c];
 	a.touched_item = s->d_touched_item;
 	a.contrib = s->d_contrib;
-	a.sync_own = pl->d_sync;
+	a.sync_own = s->d_sync;
 	a.per = pl->slots_per_rank;
 	a.n_touched = pl->n_touched;
 	a.lo = std::min(pl->n_touched, a.me * a.per);
 	a.cnt = std::min(a.per, pl->n_touched - a.lo);
 	a.F = pl->F;
 	a.ld = pl->ld;
-	a.reduce_ctas = (unsigned)(((long)a.cnt * a.F + 255) / 256);
 	return a;
 }
 
 static int enqueue_ll(mfgpu_plan *pl, mf_shard *s, int c)
 {
 	const mf::LLArgs a = ll_args(pl, s, c);
-	const long unpack = ((long)(a.n_touched - a.cnt) * a.F + 255) / 256;
-	mf::k_xchg_ll<<<(unsigned)std::max(1L, (long)a.reduce_ctas + unpack), 256, 0, s->st>>>(a);
+	/* never more CTAs than are resident at once (148 SMs x 8 CTAs of 256 threads): see k_xchg_ll */
+	const long work = std::max((long)a.cnt, (long)(a.n_touched - a.cnt)) * a.F;
+	int n_sm = 148;
+	CK(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, s->dev));
+	mf::k_xchg_ll<<<(unsigned)std::max(1L, std::min((work + 255) / 256, (long)n_sm * 4)), 256, 0, s->st>>>(a);
 	CK(cudaGetLastError());
 	pl->launches++;
 	return MFGPU_OK;
@@ -657,6 +672,8 @@ static int enqueue_iteration(mfgpu_plan *pl, mf_shard *s, int c)
 		return MFGPU_OK;
 	if (pl->xchg_ipc)
 		return enqueue_xchg(pl, s, c, c);
+	if (!pl->comm)
+		return mf_fail(MFGPU_EINVAL, "N shards without an exchange (internal error)");
 	/* out of place: the columns this rank never writes must stay 0.0 in G[0] */
 	NCK(g_nccl.AllReduce(s->G[0], s->G[1], count, /*ncclDouble*/ 8, /*ncclSum*/ 0, pl->comm->nccl, s->st));
 	const long total = (long)pl->n_touched * pl->F;
@@ -668,10 +685,14 @@ static int enqueue_iteration(mfgpu_plan *pl, mf_shard *s, int c)
 	return MFGPU_OK;
 }
 
-/* one iteration of a one-process N-GPU plan; `t` picks the G buffer */
-static int enqueue_iteration_peer(mfgpu_plan *pl, int c, int t)
+/* One iteration of a one-process N-GPU plan with the event-ordered pull exchange (option
+ * exchange = 2; the default is the low-latency exchange through enqueue_iteration).  The G buffer
+ * follows the factor parity c, which persists from one mfgpu_plan_iterate call to the next: G[c]
+ * is rewritten two iterations after the peers read it, and every shard's stream has by then
+ * waited for the events of the iteration in between, whatever the split into calls. */
+static int enqueue_iteration_peer(mfgpu_plan *pl, int c)
 {
-	const int gb = t & 1;
+	const int gb = c;
 	for (int g = 0; g < pl->nshards; g++) {
 		mf_shard *s = &pl->sh[g];
 		CK(cudaSetDevice(s->dev));
@@ -748,33 +769,68 @@ extern "C" int mfgpu_plan_iterate(mfgpu_plan *pl, int iters)
 	int c = pl->cur;
 	if (pl->F == 0 || pl->nnz == 0) {
 		/* nothing changes (matFact.c:41 loop is empty / rows have no columns) */
-	} else if (nl > 1) {
+	} else if (nl > 1 && pl->peer_events) {
 		for (int t = 0; t < iters; t++, c ^= 1)
-			TRY(enqueue_iteration_peer(pl, c, t));
+			TRY(enqueue_iteration_peer(pl, c));
 	} else {
-		mf_shard *s = &pl->sh[0];
-		CK(cudaSetDevice(s->dev));
+		/* one shard, one rank of a group, or one process driving N GPUs with the low-latency
+		 * exchange: every local shard replays its own graph of gi iterations.  The graphs of all
+		 * shards are built before any of them is launched: a shard's exchange waits for its peers,
+		 * which must not be held up by a graph instantiation on the host. */
 		int left = iters;
 		const int gi = pl->opt_graph_iters;
 		if (pl->opt_graph && left >= gi) {
-			if (!s->gexec[c]) {
+			for (int g = 0; g < nl; g++) {
+				mf_shard *s = &pl->sh[g];
+				if (s->gexec[c])
+					continue;
+				CK(cudaSetDevice(s->dev));
 				TraceClock tc;
 				TRY(build_graph(pl, s, c, gi));
 				tc.lap("iterate: graph build");
 			}
-			const long long per = launches_per_iteration(pl, s) * gi;
-			for (; left >= gi; left -= gi) {
-				CK(cudaGraphLaunch(s->gexec[c], s->st));
-				pl->launches += per;
-			}
+			for (; left >= gi; left -= gi)
+				for (int g = 0; g < nl; g++) {
+					mf_shard *s = &pl->sh[g];
+					CK(cudaSetDevice(s->dev));
+					CK(cudaGraphLaunch(s->gexec[c], s->st));
+					pl->launches += launches_per_iteration(pl, s) * gi;
+				}
 		}
 		for (; left > 0; left--, c ^= 1)
-			TRY(enqueue_iteration(pl, s, c));
+			for (int g = 0; g < nl; g++) {
+				CK(cudaSetDevice(pl->sh[g].dev));
+				TRY(enqueue_iteration(pl, &pl->sh[g], c));
+			}
 	}
 	pl->cur = c;
 	for (int g = 0; g < nl; g++) {
 		CK(cudaSetDevice(pl->sh[g].dev));
 		CK(cudaEventRecord(pl->sh[g].ev1, pl->sh[g].st));
+	}
+	return MFGPU_OK;
+}
+
+/* After a sync: has a device-side wait for a peer run out of time (mf_async.cuh)?  The word is
+ * cleared, so that one late peer is reported once. */
+int mf_check_comm_error(mfgpu_plan *pl)
+{
+	if (pl->nshards < 2)
+		return MFGPU_OK;
+	for (int g = 0; g < local_shards(pl); g++) {
+		mf_shard *s = &pl->sh[g];
+		if (!s->d_sync)
+			continue;
+		unsigned long long word = 0;
+		CK(cudaSetDevice(s->dev));
+		CK(cudaMemcpy(&word, s->d_sync + MF_SYNC_ERR, sizeof word, cudaMemcpyDeviceToHost));
+		if (word) {
+			CK(cudaMemset(s->d_sync + MF_SYNC_ERR, 0, sizeof word));
+			return mf_fail(MFGPU_ECOMM, "shard %d of %d waited more than %.0f ms for shard %d during the exchange "
+			                            "of the R gradient (a peer stopped, or ranks issue different calls); "
+			                            "the factors are no longer valid",
+			               s->me, pl->nshards, pl->comm_timeout_ns / 1e6, (int)word - 1);
+		}
 	}
 	return MFGPU_OK;
 }
@@ -793,7 +849,7 @@ extern "C" int mfgpu_plan_last_loop_ms(mfgpu_plan *pl, float *ms)
 		best = std::max(best, t);
 	}
 	*ms = pl->loop_ms = best;
-	return MFGPU_OK;
+	return mf_check_comm_error(pl);
 }
 
 /* Per-kernel device times for the roofline report of bench.py: each kernel `reps` times back
@@ -820,11 +876,11 @@ extern "C" int mfgpu_plan_profile_kernels(mfgpu_plan *pl, int reps, float ms[5])
 			CK(cudaMalloc((void **)&s->G_scratch, ((size_t)pl->n_touched * pl->ld + 2) * sizeof(double)));
 		rout = s->G_scratch;
 	}
-	if (pl->xchg_ipc) {
+	if (pl->xchg_ipc && pl->comm) {
 		/* the launches below write G[0] outside the exchange protocol: wait until no peer
 		 * can still be reducing it (a one-word all-reduce after everybody's last iteration) */
 		CK(cudaStreamSynchronize(s->st));
-		NCK(g_nccl.AllReduce((int *)pl->d_sync + 14, (int *)pl->d_sync + 14, 1, 2, 0, pl->comm->nccl, s->st));
+		NCK(g_nccl.AllReduce((int *)s->d_sync + 14, (int *)s->d_sync + 14, 1, 2, 0, pl->comm->nccl, s->st));
 		CK(cudaStreamSynchronize(s->st));
 	}
 	for (int phase = 0; phase < 5; phase++) {

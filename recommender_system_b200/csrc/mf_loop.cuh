@@ -1049,9 +1049,10 @@ __device__ __forceinline__ void chain_store(const ChainSide &sd, int own, int ld
 {
 	const size_t orow = sd.out_slot ? (size_t)sd.out_slot[own] : (size_t)(own - sd.own_off);
 	double *base = sd.out_owner ? sd.peer_out[sd.out_owner[own]] : sd.out;
-	if (sd.ll_epoch)
-		st_pair(base + 2 * (orow * ld + k), acc, *sd.ll_epoch + 1);
-	else
+	if (sd.ll_epoch) {
+		const unsigned long long tag = *sd.ll_epoch + 1;      /* the iteration being computed */
+		st_pair(base + (long)(tag & 1) * sd.ll_half + 2 * (orow * ld + k), acc, tag);
+	} else
 		base[orow * ld + k] = acc;
 }
 

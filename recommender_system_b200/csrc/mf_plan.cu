@@ -123,16 +123,22 @@ static int upload(T **dst, const T *src, size_t n, cudaStream_t st)
 	return MFGPU_OK;
 }
 
-/* Bytes of one G buffer.  One process: a row of ld doubles per touched item.  Rank mode: the
- * receive buffer of the push exchanges, nshards blocks (one per contributing rank) of
- * slots_per_rank rows, and twice that for the (value, tag) pairs of the low-latency exchange
- * (G[0]: contributions received, G[1]: rows of R_new received). */
-static size_t mf_g_bytes(const mfgpu_plan *pl)
+/* Doubles of one parity half of a G buffer.  One shard per row of G: a row of ld doubles per
+ * touched item.  N shards: the receive buffers of the exchanges -- nshards blocks (one per
+ * contributing shard) of slots_per_rank rows, twice that for the (value, tag) pairs of the
+ * low-latency exchange (G[0]: contributions received, G[1]: rows of R_new received). */
+static size_t mf_g_half(const mfgpu_plan *pl)
 {
 	size_t rows = (size_t)pl->n_touched;
-	if (pl->comm)
+	if (pl->nshards > 1)
 		rows = 2 * std::max(rows, (size_t)pl->nshards * pl->slots_per_rank);
-	return (rows * pl->ld + 2) * sizeof(double);
+	return rows * pl->ld;
+}
+
+/* Bytes of one G buffer: two halves, used alternately by the low-latency exchange (k_xchg_ll). */
+static size_t mf_g_bytes(const mfgpu_plan *pl)
+{
+	return (2 * mf_g_half(pl) + 2) * sizeof(double);
 }
 
 /* Launch geometry of k_update_L / k_update_R for one shard (see mf_loop.cuh). */
@@ -461,7 +467,7 @@ static int shard_create(mfgpu_plan *pl, mf_shard *s, int dev, const mfgpu_entry 
 	const size_t rbytes = ((size_t)pl->items * pl->ld + 34) * sizeof(double);
 	/* rank mode: peers store their rows of R_new straight into this replica (push exchange), so
 	 * R must be exportable over CUDA IPC, which pool memory is not */
-	s->r_plain = pl->comm != nullptr;
+	s->r_plain = pl->nshards > 1;
 	if (pl->comm && pl->nshards > 1) {
 		TRY(arena_borrow(pl->comm, mf_g_bytes(pl), rbytes, &pl->arena));
 		s->borrowed = pl->arena != nullptr;
@@ -480,11 +486,11 @@ static int shard_create(mfgpu_plan *pl, mf_shard *s, int dev, const mfgpu_entry 
 	if (pl->nshards > 1) {
 		TRY(upload(&s->d_item_slot, item_slot, (size_t)pl->items, s->st));
 		TRY(upload(&s->d_touched_item, touched_item, (size_t)pl->n_touched, s->st));
-		if (pl->comm) {
-			/* push exchange: touched item of slot t is reduced by rank t / slots_per_rank; this
-			 * rank's contribution goes to row rank * slots_per_rank + (t mod slots_per_rank) of
-			 * that rank's receive buffer */
-			const int per = pl->slots_per_rank, me = pl->comm->rank;
+		if (contrib) {
+			/* push exchange: touched item of slot t is reduced by shard t / slots_per_rank; this
+			 * shard's contribution goes to row me * slots_per_rank + (t mod slots_per_rank) of
+			 * that shard's receive buffer */
+			const int per = pl->slots_per_rank, me = s->me;
 			std::vector<int> owner((size_t)std::max(1, pl->items), 0), prow((size_t)std::max(1, pl->items), 0);
 			for (int j = 0; j < pl->items; j++)
 				if (item_slot[j] >= 0) {
@@ -528,10 +534,15 @@ static int shard_create(mfgpu_plan *pl, mf_shard *s, int dev, const mfgpu_entry 
 	return MFGPU_OK;
 }
 
-static void shard_destroy(mf_shard *s)
+static void shard_destroy(mf_shard *s, bool own_sync)
 {
 	if (s->dev >= 0)
 		cudaSetDevice(s->dev);
+	if (own_sync && s->d_sync) {
+		if (s->st) cudaStreamSynchronize(s->st);
+		cudaFree(s->d_sync);
+		s->d_sync = nullptr;
+	}
 	TraceClock tc;
 	if (s->st) cudaStreamSynchronize(s->st);
 	if (s->st2) cudaStreamSynchronize(s->st2);
@@ -603,7 +614,7 @@ static bool xchg_all_ok(mfgpu_plan *pl, mf_shard *s, int mine, int *d_scratch)
 	return total == 0;
 }
 
-int mf_xchg_setup(mfgpu_plan *pl)
+static int xchg_setup_ranks(mfgpu_plan *pl)
 {
 	pl->xchg_ipc = 0;
 	if (!pl->comm || pl->nshards < 2 || (size_t)pl->n_touched * pl->ld == 0)
@@ -721,11 +732,20 @@ int mf_xchg_setup(mfgpu_plan *pl)
 	return MFGPU_OK;
 }
 
+int mf_xchg_setup(mfgpu_plan *pl)
+{
+	const int rc = xchg_setup_ranks(pl);
+	if (pl->comm)
+		pl->sh[0].d_sync = pl->d_sync;       /* the rank's one shard waits on the rank's sync block */
+	return rc;
+}
+
 /* Collective: nobody may unmap or free while a peer's kernels can still read its G. */
 void mf_xchg_teardown(mfgpu_plan *pl)
 {
 	if (!pl->comm || !pl->d_sync)
 		return;
+	pl->sh[0].d_sync = nullptr;
 	mf_shard *s = &pl->sh[0];
 	if (s->dev >= 0)
 		cudaSetDevice(s->dev);
@@ -744,6 +764,31 @@ void mf_xchg_teardown(mfgpu_plan *pl)
 	pl->d_sync = nullptr;
 	pl->xchg_ipc = 0;
 	cudaGetLastError();
+}
+
+/* One process, N GPUs: the shards are each other's peers directly (cudaDeviceEnablePeerAccess;
+ * no IPC): every shard gets a sync block, and the peer tables of the plan point at the shards'
+ * own buffers.  Default: the low-latency exchange, exactly as between processes; option
+ * exchange = 2: the event-ordered pull (k_apply_R_peer). */
+static int mf_xchg_setup_local(mfgpu_plan *pl)
+{
+	for (int g = 0; g < pl->nshards; g++) {
+		mf_shard *s = &pl->sh[g];
+		CK(cudaSetDevice(s->dev));
+		if (!s->d_sync)
+			CK(cudaMalloc((void **)&s->d_sync, MF_SYNC_WORDS * sizeof(unsigned long long)));
+		CK(cudaMemsetAsync(s->d_sync, 0, MF_SYNC_WORDS * sizeof(unsigned long long), s->st));
+		for (int b = 0; b < 2; b++) {
+			CK(cudaMemsetAsync(s->G[b], 0, mf_g_bytes(pl), s->st));
+			pl->peer_G[b][g] = s->G[b];
+			pl->peer_R[b][g] = s->R[b];
+		}
+		pl->peer_sync[g] = s->d_sync;
+		CK(cudaStreamSynchronize(s->st));
+	}
+	pl->peer_events = pl->opt_exchange == 2;
+	pl->xchg_ipc = pl->peer_events ? 0 : 3;
+	return MFGPU_OK;
 }
 
 static int plan_create(mfgpu_plan **out, int users, int items, int features, int nnz,
@@ -812,8 +857,8 @@ static int plan_create(mfgpu_plan **out, int users, int items, int features, int
 					for (int j = 0; j < items; j++)
 						if (item_slot[j] >= 0)
 							touched[item_slot[j]] = j;
-				if (rc == MFGPU_OK && comm) {
-					/* blocks of touched items per reducing rank, contributors of every item */
+				if (rc == MFGPU_OK) {
+					/* blocks of touched items per reducing shard, contributors of every item */
 					contrib = (int *)calloc((size_t)(cnt ? cnt : 1), sizeof(int));
 					if (!contrib)
 						rc = MFGPU_ENOMEM;
@@ -832,11 +877,18 @@ static int plan_create(mfgpu_plan **out, int users, int items, int features, int
 		mf_fail(rc, rc == MFGPU_EINVAL ? "an entry lies outside the users x items matrix"
 		                               : "out of host memory");
 	tc.lap("create: user split, items");
+	pl->ll_half = (long)mf_g_half(pl);
+	{
+		const char *env = getenv("MFGPU_COMM_TIMEOUT_MS");
+		const double ms = env && atof(env) > 0 ? atof(env) : 30000.0;
+		pl->comm_timeout_ns = (unsigned long long)(ms * 1e6);
+	}
 	if (rc == MFGPU_OK) {
 		if (comm) {
 			/* rank mode: this process holds one shard, the users of its rank */
 			pl->sh[0].user_lo = pl->cut[comm->rank];
 			pl->sh[0].user_hi = pl->cut[comm->rank + 1];
+			pl->sh[0].me = comm->rank;
 			rc = shard_create(pl, &pl->sh[0], comm->device, entries, item_slot, touched, contrib);
 			if (rc == MFGPU_OK)
 				rc = mf_xchg_setup(pl);
@@ -844,7 +896,8 @@ static int plan_create(mfgpu_plan **out, int users, int items, int features, int
 			for (int g = 0; g < nshards && rc == MFGPU_OK; g++) {
 				pl->sh[g].user_lo = pl->cut[g];
 				pl->sh[g].user_hi = pl->cut[g + 1];
-				rc = shard_create(pl, &pl->sh[g], devs[g], entries, item_slot, touched, nullptr);
+				pl->sh[g].me = g;
+				rc = shard_create(pl, &pl->sh[g], devs[g], entries, item_slot, touched, contrib);
 			}
 			/* the peer exchange reads every other shard's G directly */
 			for (int g = 0; g < nshards && rc == MFGPU_OK && nshards > 1; g++) {
@@ -865,6 +918,8 @@ static int plan_create(mfgpu_plan **out, int users, int items, int features, int
 					cudaGetLastError();
 				}
 			}
+			if (rc == MFGPU_OK && nshards > 1)
+				rc = mf_xchg_setup_local(pl);
 		}
 	}
 	free(item_slot);
@@ -900,9 +955,15 @@ extern "C" void mfgpu_plan_destroy(mfgpu_plan *pl)
 		return;
 	const int n = pl->comm ? 1 : pl->nshards;
 	mf_xchg_teardown(pl);            /* rank mode: collective, see there */
+	if (!pl->comm)
+		for (int g = 0; g < n; g++)
+			if (pl->sh[g].dev >= 0 && pl->sh[g].d_sync) {
+				cudaSetDevice(pl->sh[g].dev);
+				if (pl->sh[g].st) cudaStreamSynchronize(pl->sh[g].st);
+			}
 	for (int g = 0; g < n; g++)
 		if (pl->sh[g].dev >= 0)
-			shard_destroy(&pl->sh[g]);
+			shard_destroy(&pl->sh[g], pl->comm == nullptr);
 	if (pl->arena)
 		pl->arena->in_use = 0;       /* the next plan of this communicator may borrow it */
 	delete pl;
@@ -1068,7 +1129,7 @@ extern "C" int mfgpu_plan_get_factors(mfgpu_plan *pl, double *L, double *R)
 	}
 	for (int g = 0; g < local_shards(pl); g++)
 		CK(cudaStreamSynchronize(pl->sh[g].st));
-	return MFGPU_OK;
+	return mf_check_comm_error(pl);
 }
 
 extern "C" int mfgpu_plan_sync(mfgpu_plan *pl)
@@ -1079,7 +1140,7 @@ extern "C" int mfgpu_plan_sync(mfgpu_plan *pl)
 		CK(cudaSetDevice(pl->sh[g].dev));
 		CK(cudaStreamSynchronize(pl->sh[g].st));
 	}
-	return MFGPU_OK;
+	return mf_check_comm_error(pl);
 }
 
 extern "C" int mfgpu_plan_user_range(mfgpu_plan *pl, int shard, int *lo, int *hi)
@@ -1098,7 +1159,7 @@ extern "C" int mfgpu_plan_exchange_kind(mfgpu_plan *pl)
 	if (!pl || pl->nshards < 2)
 		return 0;
 	if (!pl->comm)
-		return 3;
+		return pl->peer_events ? 3 : 5;
 	return pl->xchg_ipc == 3 ? 5 : pl->xchg_ipc == 2 ? 4 : pl->xchg_ipc ? 2 : 1;
 }
 
@@ -1153,13 +1214,22 @@ extern "C" int mfgpu_plan_set_option(mfgpu_plan *pl, const char *name, int value
 	else if (!strcmp(name, "pair_stages")) pl->opt_pair_stages = value;
 	else if (!strcmp(name, "pair_warps")) pl->opt_pair_warps = value;
 	else if (!strcmp(name, "acc_gw")) pl->opt_acc_gw = value;
+	else if (!strcmp(name, "comm_timeout_ms")) pl->comm_timeout_ns = (unsigned long long)std::max(1, value) * 1000000ull;
 	else if (!strcmp(name, "exchange")) {
 		/* rank mode, collective: 0 = ncclAllReduce; peer memory when available: 1 / -1 = low
 		 * latency (value, tag) exchange (k_xchg_ll), 2 = pull (k_apply_R_xchg), 3 = push with
 		 * fences and flags (k_reduce_bcast) */
 		pl->opt_exchange = value;
-		mf_xchg_teardown(pl);
-		TRY(mf_xchg_setup(pl));
+		if (pl->comm) {
+			mf_xchg_teardown(pl);
+			TRY(mf_xchg_setup(pl));
+		} else if (pl->nshards > 1) {
+			for (int g = 0; g < pl->nshards; g++) {
+				CK(cudaSetDevice(pl->sh[g].dev));
+				CK(cudaStreamSynchronize(pl->sh[g].st));
+			}
+			TRY(mf_xchg_setup_local(pl));
+		}
 	}
 	else
 		return mf_fail(MFGPU_EINVAL, "unknown option '%s'", name);
@@ -1233,5 +1303,5 @@ extern "C" int mfgpu_plan_timer_stop(mfgpu_plan *pl, float *ms)
 		worst = std::max(worst, t);
 	}
 	*ms = worst;
-	return MFGPU_OK;
+	return mf_check_comm_error(pl);
 }

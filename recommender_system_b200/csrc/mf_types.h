@@ -55,6 +55,7 @@ struct ChainSide {
 	/* low-latency exchange: the row is stored as (value, tag) pairs, tag = *ll_epoch + 1 (the
 	 * iteration being computed); element (row, k) lives at doubles 2*(row*ld + k).  nullptr: off */
 	const unsigned long long *ll_epoch;
+	long ll_half;             /* the pair buffers are double: iteration t uses the half (t & 1) * ll_half doubles */
 };
 
 constexpr int AM_TI = 64;      /* users per CTA           */

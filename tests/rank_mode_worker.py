@@ -22,6 +22,10 @@ def main():
     dist.broadcast_object_list(uid, src=0)
     comm = api.Comm(world, rank, uid[0], local)
     how = sys.argv[2] if len(sys.argv) > 2 else "ll"
+    if how == "timeout":
+        return timeout_case(out_path, rank, world, comm)
+    if how == "soak":
+        return soak_case(out_path, rank, world, comm, int(sys.argv[3]), int(sys.argv[4]))
 
     def set_how(p):
         if how != "ll":
@@ -69,6 +73,64 @@ def main():
         np.savez(out_path, L=L, R=R, best=best_all, replicas_equal=replicas_equal, exchange_kind=kind,
                  cut=np.array([p[0] for p in parts] + [inst.users]))
     dist.destroy_process_group()
+
+
+def timeout_case(out_path, rank, world, comm):
+    """Rank 0 runs two iterations more than the others: its exchange waits for contributions
+    that never come; after comm_timeout_ms the wait gives up and the sync reports it."""
+    inst = synth.random_instance(120, 80, 8, 0.2, 4, 0.002, seed=7)
+    L, R = api.random_fill_LR(inst.users, inst.items, inst.features)
+    code, msg = 0, ""
+    plan = api.Plan(inst.users, inst.items, inst.features, inst.entries, inst.alpha, comm=comm)
+    plan.set_option("graph", 0)
+    plan.set_option("comm_timeout_ms", 300)
+    plan.set_factors(L, R)
+    plan.iterate(2)
+    plan.sync()
+    if rank == 0:
+        plan.iterate(2)
+        try:
+            plan.sync()
+        except api.MatFactError as e:
+            code, msg = e.code, str(e)
+    dist.barrier()
+    plan.close()
+    comm.close()
+    if rank == 0:
+        np.savez(out_path, code=code, message=msg)
+    dist.destroy_process_group()
+
+
+def soak_case(out_path, rank, world, comm, total, every):
+    """The low-latency exchange for `total` iterations; every `every` iterations the replicas of R
+    are hashed against each other (a torn (value, tag) pair would leave one replica different)."""
+    import hashlib
+    import time
+    inst = synth.random_instance(400, 300, 16, 0.08, total, 1e-5, seed=11)
+    L, R = api.random_fill_LR(inst.users, inst.items, inst.features)
+    plan = api.Plan(inst.users, inst.items, inst.features, inst.entries, inst.alpha, comm=comm)
+    plan.set_factors(L, R)
+    bad, done, t0 = 0, 0, time.time()
+    while done < total:
+        plan.iterate(every)
+        done += every
+        plan.get_factors(L, R)
+        h = hashlib.sha256(R.tobytes()).hexdigest()
+        hs = [None] * world
+        dist.all_gather_object(hs, h)
+        if len(set(hs)) != 1:
+            bad += 1
+    plan.close()
+    comm.close()
+    if rank == 0:
+        line = "soak: %d ranks, %d iterations, replicas of R hashed every %d: %d mismatches, finite=%s, %.1f s" % (
+            world, done, every, bad, bool(np.isfinite(R).all()), time.time() - t0)
+        print(line, flush=True)
+        with open(out_path, "w") as fh:
+            fh.write(line + "\n")
+    dist.destroy_process_group()
+    if bad:
+        sys.exit(1)
 
 
 if __name__ == "__main__":

@@ -320,25 +320,74 @@ def test_init_factors_on_device(gpu, shape):
             assert bits_equal(L0, L1) and bits_equal(R0, R1)
 
 
+@pytest.mark.parametrize("options", [{}, {"exchange": 2}, {"pair": 1}, {"graph": 0}])
 @pytest.mark.parametrize("nshards", [2, 4, 8])
-def test_multi_gpu_matches_sharded_oracle(gpu, oracle, nshards):
-    """One process, N GPUs, peer exchange in shard order == oracle N-shard ordering, bit for bit."""
+def test_multi_gpu_matches_sharded_oracle(gpu, oracle, nshards, options):
+    """One process, N GPUs (what `MATFACT_NGPUS=N matFact file.in` runs): the low-latency
+    exchange over peer memory inside CUDA graphs by default, the event-ordered pull with
+    exchange=2; both add in shard order == the oracle's N-shard ordering, bit for bit.  The
+    iterations are split over several calls with odd counts (the buffers of the exchange
+    alternate with the iteration, across calls too)."""
     if gpu.device_count() < nshards:
         pytest.skip("needs %d GPUs" % nshards)
-    inst = synth.random_instance(300, 200, 20, 0.1, 25, 0.002, seed=33)
+    inst = synth.random_instance(300, 200, 20, 0.1, 41, 0.002, seed=33)
     cut = gpu.split_users(inst.users, inst.entries, nshards)
     L0, R0 = oracle.init_LR(inst.users, inst.items, inst.features)
     L1, R1 = L0.copy(), R0.copy()
     oracle.factorize_sharded(inst.users, inst.items, inst.features, inst.entries, inst.iters,
                              inst.alpha, L0, R0, cut)
     with gpu.Plan(inst.users, inst.items, inst.features, inst.entries, inst.alpha, ngpus=nshards) as plan:
+        for k, v in options.items():
+            plan.set_option(k, v)
+        assert plan.exchange_kind() == (3 if options.get("exchange") == 2 else 5)
         plan.set_factors(L1, R1)
-        plan.iterate(inst.iters)
+        for n in (1, 17, 3, 16, 1, 3):           # 41 iterations: graph replays and single ones, odd splits
+            plan.iterate(n)
         plan.get_factors(L1, R1)
         best = plan.recommend()
     assert bits_equal(L0, L1) and bits_equal(R0, R1)
     assert np.array_equal(best, oracle.recommend(inst.users, inst.items, inst.features,
                                                  inst.entries, L0, R0))
+
+
+def test_cli_on_several_gpus(gpu, oracle, tmp_path):
+    """The drop-in program with MATFACT_NGPUS: same stdout as on one GPU for the samples (the
+    N-shard order moves L and R by ~1e-13, never a recommendation: SURVEY.md section 4)."""
+    n = min(gpu.device_count(), 8)
+    if n < 2:
+        pytest.skip("needs 2 GPUs")
+    for sample in ("inst30-40-10-2-10", "instML100k"):
+        src = gold_path(sample + ".in")
+        if src.endswith(".gz"):
+            import gzip, shutil
+            plain = tmp_path / (sample + ".in")
+            with gzip.open(src, "rb") as fi, open(plain, "wb") as fo:
+                shutil.copyfileobj(fi, fo)
+            src = str(plain)
+        env = dict(os.environ, MATFACT_NGPUS=str(n))
+        p = subprocess.run([os.path.join(ROOT, "bin", "matFact"), src], capture_output=True, text=True, env=env, timeout=600)
+        assert p.returncode == 0, p.stderr[-2000:]
+        assert p.stdout == load_out(sample)
+
+
+def test_rank_mode_timeout_is_reported(gpu, tmp_path):
+    """A rank that stops taking part: the others' device-side waits run out of time (300 ms
+    here), the kernels finish, and the next sync returns MFGPU_ECOMM -- no trap, no hang."""
+    import sys
+    import socket
+    if gpu.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    out = tmp_path / "timeout.npz"
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+           "--master-addr", "127.0.0.1", "--master-port", str(port),
+           os.path.join(ROOT, "tests", "rank_mode_worker.py"), str(out), "timeout"]
+    p = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert p.returncode == 0, p.stderr[-3000:]
+    got = np.load(out)
+    assert int(got["code"]) == -5 and "waited more than" in str(got["message"])
 
 
 @pytest.mark.parametrize("exchange", ["ll", "push", "pull", "nccl"])
