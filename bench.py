@@ -257,6 +257,14 @@ def ncu_traffic(workload, kernel):
         return json.load(fh).get(workload, {}).get(kernel)
 
 
+def make_config(desc, inst, n_gpus):
+    """The `config` of the JSON line: the same dictionary in both arms (the driver compares them)."""
+    return {"workload": desc, "iters": inst.iters, "nnz": int(inst.nnz), "alpha": inst.alpha,
+            "sharding": "users" if n_gpus > 1 else "none",
+            "l2": "factor buffers %.0f MB vs 126 MB L2; no flush (the loop re-reads its own output by "
+                  "construction)" % (32e-6 * inst.features * (inst.users + inst.items))}
+
+
 def run_reference_arm(args, rank):
     if rank != 0:
         return
@@ -291,66 +299,105 @@ def run_reference_arm(args, rank):
             "ms_per_step": 1e3 * inst.nnz * inst.iters / v, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic"
             if args.workload != "ml100k" else "reference sample file",
-            "config": {"workload": desc, "iters": inst.iters, "nnz": inst.nnz,
-                       "note": "reference CPU implementation, all host threads: the faster of its OpenMP "
-                               "and MPI programs (cpu_baseline.program); ms_per_step extrapolated to the "
-                               "full iteration count"},
+            "config": make_config(desc, inst, args.gpus),
+            "note": "reference CPU implementation, all host threads: the faster of its OpenMP and MPI "
+                    "programs (cpu_baseline.program); ms_per_step extrapolated to the full iteration count",
             "cpu_baseline": last,
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
-    ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="inst60000", choices=["inst60000", "ml1m", "ml100k"])
-    ap.add_argument("--iters", type=int, default=None, help="override the workload's iteration count")
-    ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--option", action="append", default=[], help="plan option name=value")
-    args = ap.parse_args()
-    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+EXCHANGE = {0: "none", 1: "nccl allreduce of the R gradient + apply",
+            2: "fused reduce+apply kernel over NVLink peer memory (CUDA IPC), rank order",
+            3: "event-ordered reduce+apply kernel over NVLink peer memory, shard order (one process)",
+            4: "chain kernels store gradient rows into the owning rank over NVLink peer memory; owner reduces in "
+               "rank order, applies, stores R_new rows into every replica (fences + flag words)",
+            5: "accumulation kernels store gradient elements as 16-byte (value, tag) pairs into the owning rank "
+               "over NVLink peer memory; one kernel reduces the own items in rank order as pairs arrive, applies, "
+               "stores R_new pairs into every replica and unpacks the others' (no fences, no flags)"}
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if args.impl == "reference":
-        run_reference_arm(args, rank)
-        return
+# measured on this pool's B200 by tools/ubench_l2_gather.cu (profiles/r02_ubench_l2_gather.txt): rows of
+# 1536 B gathered at random from a 3.2 MB table, 64 warps per SM -- what the L2 -> SM path delivers when
+# enough loads are in flight (the loop kernels are bound by how many they can keep in flight)
+L2_GATHER_PEAK_GBS = 27500.0
 
-    import torch
-    import torch.distributed as dist
-    from recommender_system_b200 import api
 
-    if api.device_count() < 1:
-        raise SystemExit("bench.py: no B200 visible and there is no CPU path")
-    inst, desc = load_workload(args.workload, args.iters)
-    U, I, F, T = inst.users, inst.items, inst.features, inst.iters
-    torch.cuda.set_device(local)
-    comm = None
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-        uid = torch.zeros(api.UID_BYTES, dtype=torch.uint8, device="cuda")
-        if rank == 0:
-            uid.copy_(torch.frombuffer(bytearray(api.Comm.unique_id()), dtype=torch.uint8))
-        dist.broadcast(uid, 0)
-        comm = api.Comm(world, rank, bytes(uid.cpu().numpy().tobytes()), local)
-    n_gpus = world if world > 1 else args.gpus
+def expected_hash(workload, n_gpus, iters):
+    """sha256 of the oracle's final L||R for this workload, iteration count and shard count, or None."""
+    try:
+        if workload == "ml100k":
+            with open(os.path.join(ROOT, "tests", "golden", "expected.json")) as fh:
+                rec = json.load(fh)["instML100k"]
+            return rec["lr_sha256"] if n_gpus == 1 and iters == rec["iters"] else None
+        with open(os.path.join(ROOT, "tests", "golden", "expected_shapes.json")) as fh:
+            rec = json.load(fh)[workload]
+        return rec["shards"].get(str(n_gpus)) if iters == rec["iters"] else None
+    except (OSError, KeyError, ValueError):
+        return None
 
-    def barrier():
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
 
-    def max_over_ranks(x):
-        if world == 1:
+class Ctx:
+    """What every workload of one bench run shares: the process group, the communicator, the options."""
+
+    def __init__(self, args):
+        import torch
+        import torch.distributed as dist
+        from recommender_system_b200 import api
+        self.torch, self.dist, self.api, self.args = torch, dist, api, args
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        if api.device_count() < 1:
+            raise SystemExit("bench.py: no B200 visible and there is no CPU path")
+        torch.cuda.set_device(self.local)
+        self.comm = None
+        if self.world > 1:
+            dist.init_process_group("nccl", device_id=torch.device("cuda", self.local))
+            uid = torch.zeros(api.UID_BYTES, dtype=torch.uint8, device="cuda")
+            if self.rank == 0:
+                uid.copy_(torch.frombuffer(bytearray(api.Comm.unique_id()), dtype=torch.uint8))
+            dist.broadcast(uid, 0)
+            self.comm = api.Comm(self.world, self.rank, bytes(uid.cpu().numpy().tobytes()), self.local)
+        self.n_gpus = self.world if self.world > 1 else args.gpus
+
+    def barrier(self):
+        self.torch.cuda.synchronize()
+        if self.world > 1:
+            self.dist.barrier()
+
+    def max_over_ranks(self, x):
+        if self.world == 1:
             return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        t = self.torch.tensor([x], dtype=self.torch.float64, device="cuda")
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
         return float(t.item())
+
+    def gather(self, obj):
+        """obj of every rank, on every rank (pickled through the process group)."""
+        if self.world == 1:
+            return [obj]
+        out = [None] * self.world
+        self.dist.all_gather_object(out, obj)
+        return out
+
+    def close(self):
+        if self.comm:
+            self.comm.close()
+        if self.world > 1:
+            self.dist.barrier()
+            self.dist.destroy_process_group()
+
+
+def bench_workload(cx, name, steps, warmup, e2e_steps, headline):
+    """One workload: the device-resident leg (`value`), the parity check of its factors against the
+    oracle's hash on record, the per-kernel times, and the end-to-end leg.  Returns a dict (all
+    ranks; rank 0's is printed)."""
+    import hashlib
+    torch, api, args = cx.torch, cx.api, cx.args
+    inst, desc = load_workload(name, args.iters if headline else None)
+    U, I, F, T = inst.users, inst.items, inst.features, inst.iters
+    n_gpus, comm, rank = cx.n_gpus, cx.comm, cx.rank
 
     # the reference's host-side initialisation, kept in pinned memory for the e2e legs
     L0, R0 = api.random_fill_LR(U, I, F)
@@ -360,6 +407,7 @@ def main():
     Ro = torch.empty((I, F), dtype=torch.float64, pin_memory=True).numpy()
     Lp[...] = L0
     Rp[...] = R0
+    del L0, R0
 
     def make_plan():
         pl = api.Plan(U, I, F, inst.entries, inst.alpha, ngpus=(1 if comm else args.gpus), comm=comm)
@@ -373,31 +421,56 @@ def main():
     xkind = plan.exchange_kind()
     plan.set_factors(Lp, Rp)
     plan.save_factors()
-    for _ in range(args.warmup):
+    for _ in range(warmup):
         plan.restore_factors()
         plan.iterate(T)
     plan.sync()
-    barrier()
-    sampler = ClockSampler(local)
+    cx.barrier()
+    sampler = ClockSampler(cx.local)
     sampler.start()
     launches0 = plan.launch_count()
     plan.timer_start()
-    for _ in range(args.steps):
+    for _ in range(steps):
         plan.restore_factors()
         plan.iterate(T)
     region_ms = plan.timer_stop()
-    barrier()
+    cx.barrier()
     clocks = sampler.result()
-    region_ms = max_over_ranks(region_ms)
+    region_ms = cx.max_over_ranks(region_ms)
     launches = plan.launch_count() - launches0
-    value = inst.nnz * T * args.steps / (region_ms * 1e-3)
+    value = inst.nnz * T * steps / (region_ms * 1e-3)
+
+    # ---- parity of what was just timed: the factors of the last step against the oracle's hash --
+    lo, hi = plan.user_range(0)
+    single_process_multi = (not comm) and args.gpus > 1
+    if single_process_multi:
+        lo, hi = 0, U
+    plan.get_factors(Lo, Ro)
+    parts = cx.gather((lo, hi, Lo[lo:hi].copy() if comm else None, hashlib.sha256(Ro.tobytes()).hexdigest()))
+    parity = None
+    if rank == 0:
+        if comm:
+            for (a, b, rows, _) in parts:
+                Lo[a:b] = rows
+        h = hashlib.sha256()
+        h.update(Lo.tobytes())
+        h.update(Ro.tobytes())
+        want = expected_hash(name, n_gpus, T)      # plan options never change a bit of the result
+        parity = {"lr_sha256": h.hexdigest(), "expected": want,
+                  "replicas_of_R_identical": len({p[3] for p in parts}) == 1,
+                  "source": "oracle (tools/make_golden_shapes.py -> tests/golden/expected_shapes.json; "
+                            "ml100k: tests/golden/expected.json), same cut, same order of the sum"}
+        parity["checked"] = want is not None
+        parity["ok"] = (h.hexdigest() == want) if want is not None else None
+    del parts
 
     # per-kernel device times for the roofline (all ranks: the exchange is collective)
     k_ms = plan.profile_kernels(20)
     k_bytes = plan.kernel_bytes()
-    lo, hi = plan.user_range(0)
+    g_bytes = plan.kernel_gather_bytes()
+    lo0, hi0 = plan.user_range(0)
     e = inst.entries
-    mine = e[(e["row"] >= lo) & (e["row"] < hi)]      # shard 0 (= this rank): the kernels timed above
+    mine = e[(e["row"] >= lo0) & (e["row"] < hi0)]      # shard 0 (= this rank): the kernels timed above
     U_t, I_t = len(np.unique(mine["row"])), len(np.unique(mine["col"]))
     _, _, b_it = kernel_bytes(F, U_t, I_t, len(mine))
     peak, peak_src = peaks()
@@ -405,19 +478,21 @@ def main():
     dom_name = max(loop_kernels, key=lambda k: k_ms[k])
     dom_bytes = k_bytes[dom_name]
     ach = dom_bytes / (k_ms[dom_name] * 1e-3) / 1e9 if k_ms[dom_name] > 0 else 0.0
-    it_ms = region_ms / (args.steps * T)
-    # what actually binds the loop: the rows gathered from L2 per nonzero and pass;
-    # peak = L2 slice throughput of B200, ~6300 B/clk (B300_MICROARCH.md) at the max SM clock
-    g_bytes = plan.kernel_gather_bytes()
-    l2_peak = 6300.0 * 1.965
+    it_ms = region_ms / (steps * T)
     l2_ach = g_bytes[dom_name] / (k_ms[dom_name] * 1e-3) / 1e9 if k_ms[dom_name] > 0 else 0.0
     roofline = {"bound": "hbm", "kernel": dom_name, "achieved": ach, "peak": peak, "unit": "GB/s",
-                "frac": ach / peak, "traffic": ncu_traffic(args.workload, dom_name),
+                "frac": ach / peak, "traffic": ncu_traffic(name, dom_name),
                 "peak_source": peak_src, "algorithmic_bytes_per_launch": dom_bytes,
                 "kernel_ms": k_ms, "kernel_algorithmic_bytes": k_bytes,
+                "kernel_names": "k_update_L = by-user pass (fused k_update_L[_res], or k_dot_units in split "
+                                "mode); k_dot = dots of the long rows; k_chain_bulk = ordered accumulations "
+                                "(k_chain, or k_acc in split mode); k_chain_deep = k_chain_ws",
+                "what_binds": "the bytes a kernel keeps in flight from L2 (gathered factor rows, ~2000 cycles "
+                              "under load), not HBM: see l2_gather and DESIGN.md section 4",
                 "l2_gather": {"kernel": dom_name, "bytes_per_launch": g_bytes[dom_name], "achieved": l2_ach,
-                              "peak": l2_peak, "unit": "GB/s", "frac": l2_ach / l2_peak,
-                              "peak_source": "6300 B/clk L2 slice cap (B300_MICROARCH.md) x 1.965 GHz",
+                              "peak": L2_GATHER_PEAK_GBS, "unit": "GB/s", "frac": l2_ach / L2_GATHER_PEAK_GBS,
+                              "peak_source": "measured: tools/ubench_l2_gather.cu on this pool's B200, rows of 1536 B "
+                                             "gathered from a 3.2 MB table (profiles/r02_ubench_l2_gather.txt)",
                               "kernel_gather_bytes": g_bytes},
                 "iteration": {"algorithmic_bytes": b_it, "ms": it_ms,
                               "achieved": b_it / (it_ms * 1e-3) / 1e9,
@@ -428,12 +503,11 @@ def main():
         # exchange is what is left of it beside the loop kernels (the longer of each concurrent pair)
         beside = max(k_ms["k_update_L"], k_ms["k_dot"]) + max(k_ms["k_chain_bulk"], k_ms["k_chain_deep"])
         roofline["iteration"]["exchange_in_situ_ms"] = max(0.0, it_ms - beside)
-    # determinism check outside the timed region: the K-th factorization equals the first
     best = plan.recommend()
+    rec_ms = plan.last_recommend_ms()
     plan.close()
 
     # ---- end-to-end leg: host buffers in, host buffers out, every step ------------------
-    e2e_steps = max(3, min(args.steps, 10))
     best2 = np.full(U, -2, dtype=np.int32)
 
     def e2e_step():
@@ -450,23 +524,105 @@ def main():
                                                         for n, a, b in zip(names, t, t[1:])), file=sys.stderr)
 
     e2e_step()
-    barrier()
+    cx.barrier()
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
         e2e_step()
-    barrier()
-    e2e_s = max_over_ranks(time.perf_counter() - t0)
+    cx.barrier()
+    e2e_s = cx.max_over_ranks(time.perf_counter() - t0)
     e2e_value = inst.nnz * T * e2e_steps / e2e_s
-    single_process_multi = (not comm) and args.gpus > 1
-    nu = U if single_process_multi else hi - lo
+    nu = U if single_process_multi else hi0 - lo0
     nloc = inst.nnz if single_process_multi else len(mine)
     h2d = nloc * (4 + 8 + 4 + 4) + nloc * 4 + 4 * (2 * U + 2 + U_t + I_t) * 2 + 8 * F * (nu + I)
     d2h = 8 * F * (nu + I) + 4 * nu
-    if not np.array_equal(best[lo:hi] if comm else best, best2[lo:hi] if comm else best2):
+    if not np.array_equal(best[lo0:hi0] if comm else best, best2[lo0:hi0] if comm else best2):
         raise SystemExit("bench.py: device-resident and end-to-end legs disagree")
+    return {"inst": inst, "desc": desc, "value": value, "region_ms": region_ms, "steps": steps, "launches": launches,
+            "clocks": clocks, "roofline": roofline, "parity": parity, "xkind": xkind,
+            "argmax_ms": rec_ms,
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+                    "d2h_bytes_per_step": int(d2h), "steps": e2e_steps, "ms_per_step": 1e3 * e2e_s / e2e_steps}}
+
+
+def bench_argmax_1e6(cx):
+    """BASELINE.json configs[4]: samples/inst1000-1e6-1000-1-3.in as it is -- its loop is 2e4
+    nonzero-updates, its run time is the masked arg-max over L.R^T (2e12 separately rounded flops).
+    One GPU (R is 8 GB per buffer and is generated on the device); reports the arg-max time."""
+    import hashlib
+    from recommender_system_b200.io import format_output, read_instance
+    api = cx.api
+    path = os.path.join(ROOT, "tests", "golden", "inst1000-1e6-1000-1-3.in")
+    if not os.path.exists(path):
+        path += ".gz"
+    inst = read_instance(path)
+    t0 = time.perf_counter()
+    with api.Plan(inst.users, inst.items, inst.features, inst.entries, inst.alpha, ngpus=1) as plan:
+        t1 = time.perf_counter()
+        plan.init_factors()
+        t2 = time.perf_counter()
+        plan.iterate(inst.iters)
+        loop_ms = plan.last_loop_ms()
+        best = plan.recommend()
+        ms = plan.last_recommend_ms()
+        best = plan.recommend()
+        ms = min(ms, plan.last_recommend_ms())
+    flops = 2.0 * inst.users * inst.items * inst.features
+    out = format_output(best)
+    return {"workload": "samples/inst1000-1e6-1000-1-3.in: U=1000 I=1000000 F=1000 nnz=%d" % inst.nnz,
+            "argmax_ms": ms, "tflops_separately_rounded": flops / (ms * 1e-3) / 1e12,
+            "frac_of_fp64_issue_roof": flops / (ms * 1e-3) / 18.6e12,
+            "fp64_issue_roof": "64 FP64 lanes/clk/SM x 148 SMs x 1.965 GHz = 18.6e12 multiplies or adds per second "
+                               "(no FMA: the reference rounds the product and the sum separately)",
+            "loop_ms": loop_ms, "plan_create_s": t1 - t0, "init_factors_s": t2 - t1,
+            "stdout_md5": hashlib.md5(out.encode()).hexdigest(),
+            "stdout_md5_serial_reference": "cbb0f9797c19e495f70281dfbba2862d"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="inst60000", choices=["inst60000", "ml1m", "ml100k"])
+    ap.add_argument("--iters", type=int, default=None, help="override the workload's iteration count")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extra", action="store_true", help="only the headline workload")
+    ap.add_argument("--option", action="append", default=[], help="plan option name=value")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+
+    rank = int(os.environ.get("RANK", "0"))
+    if args.impl == "reference":
+        run_reference_arm(args, rank)
+        return
+
+    cx = Ctx(args)
+    r = bench_workload(cx, args.workload, args.steps, args.warmup, max(3, min(args.steps, 10)), True)
+    inst = r["inst"]
+
+    # the other named configurations, measured in the same run (BASELINE.json configs[1..4])
+    extra = {}
+    if not args.no_extra and not args.option:
+        for name in ("ml1m", "ml100k", "inst60000"):
+            if name == args.workload:
+                continue
+            x = bench_workload(cx, name, 3, 3, 3, False)
+            xi = x["inst"]
+            extra[name] = {"workload": x["desc"], "iters": xi.iters, "nnz": int(xi.nnz),
+                           "value": x["value"], "unit": UNIT, "ms_per_step": x["region_ms"] / x["steps"],
+                           "us_per_iteration": 1e3 * x["region_ms"] / (x["steps"] * xi.iters),
+                           "e2e": x["e2e"], "argmax_ms": x["argmax_ms"], "clocks": x["clocks"],
+                           "parity": x["parity"],
+                           "roofline": {k: x["roofline"][k] for k in ("kernel", "achieved", "frac", "kernel_ms", "iteration", "l2_gather")}}
+        if cx.n_gpus == 1 and rank == 0:
+            try:
+                extra["inst1e6_argmax"] = bench_argmax_1e6(cx)
+            except Exception as exc:  # noqa: BLE001  (e.g. not enough host memory on the box)
+                extra["inst1e6_argmax"] = {"skipped": str(exc)}
 
     cpu = None
-    if rank == 0 and n_gpus == 1 and not args.no_cpu_baseline:
+    if rank == 0 and cx.n_gpus == 1 and not args.no_cpu_baseline:
         cpu = time_best_reference(inst, 10.0, cpu_threads())
         if args.workload == "ml100k":
             # the reference's serial and OpenMP programs over the thread counts of its own report
@@ -477,52 +633,38 @@ def main():
             while t <= cpu_threads():
                 sweep["omp_%d" % t] = time_reference(inst, "omp", 2.5, t)["value"]
                 t *= 2
-            # ... and its MPI and hybrid programs over the rank counts of deliverables/report-mpi.pdf
-            # that fit this box, through the MPI stand-in
             t = 1
             while t <= min(cpu_threads(), 64):
-                r = time_reference_mpi(inst, "mpi", t, 1, 2.5)
-                if r:
-                    sweep["mpi_%d" % t] = r["value"]
+                rr = time_reference_mpi(inst, "mpi", t, 1, 2.5)
+                if rr:
+                    sweep["mpi_%d" % t] = rr["value"]
                 t *= 2
             if cpu_threads() >= 4:
                 half = 1
                 while half * 2 * 2 <= min(cpu_threads(), 64):
                     half *= 2
-                r = time_reference_mpi(inst, "hybrid", half, 2, 2.5)
-                if r:
-                    sweep["hybrid_%dx2" % half] = r["value"]
+                rr = time_reference_mpi(inst, "hybrid", half, 2, 2.5)
+                if rr:
+                    sweep["hybrid_%dx2" % half] = rr["value"]
             cpu["by_threads"] = sweep
-    if comm:
-        comm.close()
-    if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
+    n_gpus = cx.n_gpus
+    cx.close()
     if rank != 0:
         return
-    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": region_ms / args.steps, "higher_is_better": True,
+    parity = r["parity"] or {}
+    line = {"metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": n_gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": r["region_ms"] / args.steps, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic" if args.workload != "ml100k" else "reference sample file",
-            "config": {"workload": desc, "iters": T, "nnz": inst.nnz, "alpha": inst.alpha,
-                       "sharding": "users" if n_gpus > 1 else "none",
-                       "exchange": {0: "none", 1: "nccl allreduce of the R gradient + apply",
-                                    2: "fused reduce+apply kernel over NVLink peer memory (CUDA IPC), rank order",
-                                    3: "fused reduce+apply kernel over NVLink peer memory, shard order",
-                                    4: "chain kernels store gradient rows into the owning rank over NVLink peer "
-                                       "memory (CUDA IPC); owner reduces in rank order, applies, stores R_new "
-                                       "rows into every replica (fences + flag words)",
-                                    5: "chain kernels store gradient elements as (value, tag) pairs into the owning "
-                                       "rank over NVLink peer memory (CUDA IPC); one kernel reduces the own items "
-                                       "in rank order as pairs arrive, applies, stores R_new pairs into every "
-                                       "replica and unpacks the others' (no fences, no flags)"}[xkind],
-                       "l2": "factor buffers %.0f MB vs 126 MB L2; no flush (the loop re-reads "
-                             "its own output by construction)" % (32e-6 * F * (U + I))},
-            "roofline": roofline, "cpu_baseline": cpu,
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
-                    "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
-                    "ms_per_step": 1e3 * e2e_s / e2e_steps},
-            "gpu_launches": int(launches), "clocks": clocks}
+            "config": make_config(r["desc"], inst, n_gpus),
+            "exchange": EXCHANGE[r["xkind"]],
+            "parity_checked": bool(parity.get("checked") and parity.get("ok")), "parity": parity,
+            "roofline": r["roofline"], "cpu_baseline": cpu, "e2e": r["e2e"],
+            "gpu_launches": int(r["launches"]), "clocks": r["clocks"], "argmax_ms": r["argmax_ms"],
+            "workloads": extra}
+    if parity.get("checked") and not parity.get("ok"):
+        print(json.dumps(line), flush=True)
+        raise SystemExit("bench.py: the factors of the timed leg differ from the oracle's hash on record")
     print(json.dumps(line), flush=True)
 
 

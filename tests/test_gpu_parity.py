@@ -196,18 +196,68 @@ def test_diverging_run_matches(gpu, oracle):
                           gpu.recommend(L1, R1, inst.entries))
 
 
-def test_full_size_inst60000_shape(gpu, oracle):
-    """BASELINE.json configs[3] shape (synthetic stand-in, input blob missing):
-    two iterations bit-exact against the oracle; L is 96 MB."""
+def _shape_record(name):
+    import json
+    with open(os.path.join(ROOT, "tests", "golden", "expected_shapes.json")) as fh:
+        return json.load(fh)[name]
+
+
+@pytest.mark.parametrize("options", [{}, {"pair": 0}, {"pair": 1, "cs_store": 1}], ids=["default", "fused", "split"])
+def test_full_size_inst60000_shape(gpu, oracle, options):
+    """BASELINE.json configs[3] shape (synthetic stand-in, input blob missing), L is 96 MB: two
+    iterations bit-exact against the oracle, then the bench's full 100 iterations (graph replays,
+    both buffer parities) against the oracle's recorded L||R (tools/make_golden_shapes.py)."""
     inst = synth.inst60000_like(iters=2)
-    _check_against_oracle(gpu, oracle, inst)
+    _check_against_oracle(gpu, oracle, inst, options=options)
+    rec = _shape_record("inst60000")
+    inst = synth.inst60000_like()
+    assert (inst.iters, inst.nnz) == (rec["iters"], rec["nnz"])
+    L, R = gpu.random_fill_LR(inst.users, inst.items, inst.features)
+    with gpu.Plan(inst.users, inst.items, inst.features, inst.entries, inst.alpha) as plan:
+        for k, v in options.items():
+            plan.set_option(k, v)
+        plan.set_factors(L, R)
+        plan.iterate(inst.iters)
+        plan.get_factors(L, R)
+    assert lr_sha256(L, R) == rec["shards"]["1"]
 
 
-def test_full_size_ml1m_shape(gpu, oracle):
-    """BASELINE.json configs[2] shape (synthetic stand-in): heavy-tailed rows and
-    columns (max 2314 / ~3400 nonzeros) exercise the whole-CTA path."""
+@pytest.mark.parametrize("options", [{}, {"pair": 1}], ids=["default", "split"])
+def test_full_size_ml1m_shape(gpu, oracle, options):
+    """BASELINE.json configs[2] shape (synthetic stand-in): heavy-tailed rows and columns (max
+    2314 / ~3400 nonzeros) exercise the long-chain kernels; 2 iterations against the oracle and
+    the full 100 against its recorded L||R."""
     inst = synth.ml_like(iters=2)
-    _check_against_oracle(gpu, oracle, inst)
+    _check_against_oracle(gpu, oracle, inst, options=options)
+    rec = _shape_record("ml1m")
+    inst = synth.ml_like()
+    assert (inst.iters, inst.nnz) == (rec["iters"], rec["nnz"])
+    L, R = gpu.random_fill_LR(inst.users, inst.items, inst.features)
+    with gpu.Plan(inst.users, inst.items, inst.features, inst.entries, inst.alpha) as plan:
+        for k, v in options.items():
+            plan.set_option(k, v)
+        plan.set_factors(L, R)
+        plan.iterate(inst.iters)
+        plan.get_factors(L, R)
+    assert lr_sha256(L, R) == rec["shards"]["1"]
+
+
+@pytest.mark.parametrize("nshards", [2, 4, 8])
+@pytest.mark.parametrize("name", ["inst60000", "ml1m"])
+def test_full_size_shapes_on_several_gpus(gpu, name, nshards):
+    """The two headline shapes at their full size and iteration count on N GPUs of one process
+    (low-latency exchange in CUDA graphs) against the oracle's N-shard L||R on record."""
+    if gpu.device_count() < nshards:
+        pytest.skip("needs %d GPUs" % nshards)
+    rec = _shape_record(name)
+    inst = synth.inst60000_like() if name == "inst60000" else synth.ml_like()
+    assert list(gpu.split_users(inst.users, inst.entries, nshards)) == rec["cut"][str(nshards)]
+    L, R = gpu.random_fill_LR(inst.users, inst.items, inst.features)
+    with gpu.Plan(inst.users, inst.items, inst.features, inst.entries, inst.alpha, ngpus=nshards) as plan:
+        plan.set_factors(L, R)
+        plan.iterate(inst.iters)
+        plan.get_factors(L, R)
+    assert lr_sha256(L, R) == rec["shards"][str(nshards)]
 
 
 # Shapes of the reference's remaining published instances (report-mpi.pdf p.4; inputs missing
