@@ -46,9 +46,8 @@ k_masked_argmax(const ArgmaxArgs p, const double *__restrict__ L, const double *
 	const int tx = tid & 15, ty = tid >> 4;          /* items / users */
 	const int u0 = p.users_lo + (int)blockIdx.y * AM_TI;
 	const int split = blockIdx.x;
-	const int n_tiles = (p.items + AM_TJ - 1) / AM_TJ;
-	const int t_begin = split * p.tiles_per_split;
-	const int t_end = min(n_tiles, t_begin + p.tiles_per_split);
+	const int t_begin = p.tile_begin + split * p.tiles_per_split;
+	const int t_end = min(p.tile_end, t_begin + p.tiles_per_split);
 	const int F = p.F, ld = p.ld;
 
 	/* per-user cursor into the ascending mask list, positioned at the split start */
@@ -242,6 +241,30 @@ k_argmax_final(const ArgmaxArgs p, int *__restrict__ best)
 	if (ff >= 0 && p.nan_first[ul])
 		j = ff;
 	best[ul] = j;
+}
+
+/* The same fold without the last word: (value, item) of the launch's item block per user, for
+ * the merge over the GPUs of an item-sharded arg-max (mfgpu_plan_recommend): the blocks are
+ * folded in ascending item order with better(), and the NaN-at-the-first-unrated-item rule is
+ * applied once, after the last block. */
+__global__ void __launch_bounds__(256)
+k_argmax_block(const ArgmaxArgs p, double *__restrict__ out_v, int *__restrict__ out_j)
+{
+	const int ul = blockIdx.x * blockDim.x + threadIdx.x;
+	if (ul >= p.users_hi - p.users_lo)
+		return;
+	double v = 0.0;
+	int j = -1;
+	for (int s = 0; s < p.n_splits; s++) {
+		const size_t o = (size_t)ul * p.n_splits + s;
+		const int cj = p.part_j[o];
+		if (cj >= 0 && better(p.part_v[o], cj, v, j)) {
+			v = p.part_v[o];
+			j = cj;
+		}
+	}
+	out_v[ul] = v;
+	out_j[ul] = j;
 }
 
 } // namespace mf

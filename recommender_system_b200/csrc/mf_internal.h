@@ -111,6 +111,12 @@ struct mf_shard {
 	double *part_v;
 	int *part_j, *nan_first, *d_best;
 	int am_splits;
+	/* item-sharded arg-max (one process, N GPUs, users << items): this GPU's item block against ALL users */
+	double *am_L;                            /* users x ld: the L rows of every shard */
+	int *am_mask_ptr, *am_mask_col, *am_first_free;   /* rated-item mask of all users */
+	double *am_part_v, *am_out_v;
+	int *am_part_j, *am_nan, *am_out_j;
+	int am2_splits, am_tile0, am_tile1;
 };
 
 struct mfgpu_plan {
@@ -149,7 +155,7 @@ struct mfgpu_plan {
 	void *ipc_mapped[5 * MF_MAX_SHARDS];
 	int n_ipc_mapped;
 	/* options */
-	int opt_graph, opt_graph_iters, opt_long_row, opt_long_col, opt_ch, opt_chain_ring, opt_resident, opt_res_rows, opt_chain_ws, opt_exchange, opt_dot_stages, opt_acc_rows, opt_cs_store, opt_pair, opt_pair_stages, opt_pair_warps, opt_acc_gw, opt_comm_timeout_ms;
+	int opt_graph, opt_graph_iters, opt_long_row, opt_long_col, opt_ch, opt_chain_ring, opt_resident, opt_res_rows, opt_chain_ws, opt_exchange, opt_dot_stages, opt_acc_rows, opt_cs_store, opt_pair, opt_pair_stages, opt_pair_warps, opt_acc_gw, opt_comm_timeout_ms, opt_argmax_items;
 };
 
 /* ---- shared helpers (defined in mf_capi.cu) ----------------------------------- */

@@ -23,6 +23,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <vector>
 
 namespace mf {
 
@@ -929,6 +930,130 @@ extern "C" int mfgpu_plan_profile_kernels(mfgpu_plan *pl, int reps, float ms[5])
 
 /* ---- masked arg-max -------------------------------------------------------------- */
 
+/* host twin of mf::better (mf_argmax.cuh): NaN never wins; ties go to the lower item */
+static bool better_host(double v, int j, double bv, int bj)
+{
+	return (v == v) && (bj < 0 || v > bv || (v == bv && j < bj));
+}
+
+/* Item-sharded masked arg-max (one process, N GPUs; few users, many items -- the shape of
+ * samples/inst1000-1e6-1000-1-3.in, where the arg-max is the whole run time): GPU g scans ITS
+ * block of items for ALL users and the per-user results of the blocks are merged with
+ * "(value greater) else (index lower)", the serial tie rule of matFact.c:13-25 -- the reference's
+ * own distributed version does the same with MPI_Reduce and max_cmp (matFact-mpi.c:23-28,76-98),
+ * except that its strict > keeps the incoming entry, so it is not the serial rule on ties.
+ * Every GPU needs all of L for that (users x ld doubles, small by assumption): the rows are
+ * copied from their owners over NVLink.  Blocks are whole 64-item tiles. */
+static int recommend_by_items(mfgpu_plan *pl, int *best)
+{
+	const int N = pl->nshards, U = pl->users, c = pl->cur;
+	const int n_tiles = (pl->items + mf::AM_TJ - 1) / mf::AM_TJ;
+	const int tiles_y = (U + mf::AM_TI - 1) / mf::AM_TI;
+	for (int g = 0; g < N; g++) {                 /* everything enqueued so far, L rows included, is done */
+		CK(cudaSetDevice(pl->sh[g].dev));
+		CK(cudaStreamSynchronize(pl->sh[g].st));
+	}
+	/* the rated-item mask of all users: the shards hold consecutive user ranges */
+	std::vector<int> mptr((size_t)U + 1, 0), mcol, ff((size_t)U, -1);
+	for (int g = 0; g < N; g++) {
+		const mf_shard *s = &pl->sh[g];
+		for (int i = s->user_lo; i < s->user_hi; i++) {
+			const int a = s->pat.mask_ptr[i], b = s->pat.mask_ptr[i + 1];
+			mcol.insert(mcol.end(), s->pat.mask_col + a, s->pat.mask_col + b);
+			mptr[(size_t)i + 1] = (int)mcol.size();
+			ff[(size_t)i] = s->pat.first_free[i];
+		}
+	}
+	std::vector<double> hv((size_t)N * U);
+	std::vector<int> hj((size_t)N * U), hn((size_t)N * U);
+	for (int g = 0; g < N; g++) {
+		mf_shard *s = &pl->sh[g];
+		CK(cudaSetDevice(s->dev));
+		CK(cudaEventRecord(s->ev0, s->st));
+		if (!s->am_L) {
+			s->am_tile0 = (int)((long)n_tiles * g / N);
+			s->am_tile1 = (int)((long)n_tiles * (g + 1) / N);
+			const int tiles = s->am_tile1 - s->am_tile0;
+			s->am2_splits = std::max(1, std::min(std::max(1, tiles), (148 * 2 * 8 + tiles_y - 1) / std::max(1, tiles_y)));
+			CK(cudaMallocAsync((void **)&s->am_L, ((size_t)U * pl->ld + 34) * sizeof(double), s->st));
+			CK(cudaMallocAsync((void **)&s->am_mask_ptr, ((size_t)U + 1) * sizeof(int), s->st));
+			CK(cudaMallocAsync((void **)&s->am_mask_col, (mcol.size() + 1) * sizeof(int), s->st));
+			CK(cudaMallocAsync((void **)&s->am_first_free, ((size_t)U + 1) * sizeof(int), s->st));
+			CK(cudaMallocAsync((void **)&s->am_part_v, ((size_t)U * s->am2_splits + 1) * sizeof(double), s->st));
+			CK(cudaMallocAsync((void **)&s->am_part_j, ((size_t)U * s->am2_splits + 1) * sizeof(int), s->st));
+			CK(cudaMallocAsync((void **)&s->am_nan, ((size_t)U + 1) * sizeof(int), s->st));
+			CK(cudaMallocAsync((void **)&s->am_out_v, ((size_t)U + 1) * sizeof(double), s->st));
+			CK(cudaMallocAsync((void **)&s->am_out_j, ((size_t)U + 1) * sizeof(int), s->st));
+			CK(cudaMemcpyAsync(s->am_mask_ptr, mptr.data(), mptr.size() * sizeof(int), cudaMemcpyHostToDevice, s->st));
+			if (!mcol.empty())
+				CK(cudaMemcpyAsync(s->am_mask_col, mcol.data(), mcol.size() * sizeof(int), cudaMemcpyHostToDevice, s->st));
+			CK(cudaMemcpyAsync(s->am_first_free, ff.data(), ff.size() * sizeof(int), cudaMemcpyHostToDevice, s->st));
+		}
+		for (int h = 0; h < N; h++) {
+			const mf_shard *o = &pl->sh[h];
+			const size_t rows = (size_t)(o->user_hi - o->user_lo);
+			if (rows)
+				CK(cudaMemcpyPeerAsync(s->am_L + (size_t)o->user_lo * pl->ld, s->dev, o->L[c], o->dev,
+				                       rows * pl->ld * sizeof(double), s->st));
+		}
+		CK(cudaMemsetAsync(s->am_nan, 0, (size_t)U * sizeof(int), s->st));
+		mf::ArgmaxArgs a;
+		a.users_lo = 0;
+		a.users_hi = U;
+		a.l_row0 = 0;
+		a.items = pl->items;
+		a.F = pl->F;
+		a.ld = pl->ld;
+		a.n_splits = s->am2_splits;
+		a.tile_begin = s->am_tile0;
+		a.tile_end = s->am_tile1;
+		a.tiles_per_split = (s->am_tile1 - s->am_tile0 + s->am2_splits - 1) / s->am2_splits;
+		a.mask_ptr = s->am_mask_ptr;
+		a.mask_col = s->am_mask_col;
+		a.first_free = s->am_first_free;
+		a.part_v = s->am_part_v;
+		a.part_j = s->am_part_j;
+		a.nan_first = s->am_nan;
+		dim3 grid((unsigned)s->am2_splits, (unsigned)tiles_y);
+		mf::k_masked_argmax<<<grid, 256, 0, s->st>>>(a, s->am_L, s->R[c]);
+		CK(cudaGetLastError());
+		mf::k_argmax_block<<<(U + 255) / 256, 256, 0, s->st>>>(a, s->am_out_v, s->am_out_j);
+		CK(cudaGetLastError());
+		pl->launches += 2;
+		CK(cudaMemcpyAsync(hv.data() + (size_t)g * U, s->am_out_v, (size_t)U * sizeof(double), cudaMemcpyDeviceToHost, s->st));
+		CK(cudaMemcpyAsync(hj.data() + (size_t)g * U, s->am_out_j, (size_t)U * sizeof(int), cudaMemcpyDeviceToHost, s->st));
+		CK(cudaMemcpyAsync(hn.data() + (size_t)g * U, s->am_nan, (size_t)U * sizeof(int), cudaMemcpyDeviceToHost, s->st));
+		CK(cudaEventRecord(s->ev1, s->st));
+	}
+	float worst = 0.f;
+	for (int g = 0; g < N; g++) {
+		mf_shard *s = &pl->sh[g];
+		CK(cudaSetDevice(s->dev));
+		CK(cudaStreamSynchronize(s->st));
+		float t = 0.f;
+		CK(cudaEventElapsedTime(&t, s->ev0, s->ev1));
+		worst = std::max(worst, t);
+	}
+	pl->rec_ms = worst;
+	/* merge: blocks in ascending item order; a NaN at the first unrated item is never displaced */
+	for (int i = 0; i < U; i++) {
+		double v = 0.0;
+		int j = -1, nan_first = 0;
+		for (int g = 0; g < N; g++) {
+			const size_t o = (size_t)g * U + i;
+			if (hj[o] >= 0 && better_host(hv[o], hj[o], v, j)) {
+				v = hv[o];
+				j = hj[o];
+			}
+			nan_first |= hn[o];
+		}
+		if (ff[(size_t)i] >= 0 && nan_first)
+			j = ff[(size_t)i];
+		best[i] = j;
+	}
+	return MFGPU_OK;
+}
+
 extern "C" int mfgpu_plan_recommend(mfgpu_plan *pl, int *best)
 {
 	if (!pl || !best)
@@ -938,6 +1063,9 @@ extern "C" int mfgpu_plan_recommend(mfgpu_plan *pl, int *best)
 	const int nl = local_shards(pl);
 	const int c = pl->cur;
 	const bool on_device = pl->F > 0 && pl->items > 0;
+	if (nl > 1 && on_device && pl->users > 0 &&
+	    (pl->opt_argmax_items > 0 || (pl->opt_argmax_items < 0 && (long)pl->items >= 8L * pl->users)))
+		return recommend_by_items(pl, best);
 	for (int g = 0; g < nl; g++) {
 		mf_shard *s = &pl->sh[g];
 		const int nu = s->user_hi - s->user_lo;
@@ -953,6 +1081,8 @@ extern "C" int mfgpu_plan_recommend(mfgpu_plan *pl, int *best)
 			a.ld = pl->ld;
 			a.n_splits = s->am_splits;
 			a.tiles_per_split = (n_tiles + s->am_splits - 1) / s->am_splits;
+			a.tile_begin = 0;
+			a.tile_end = n_tiles;
 			a.mask_ptr = s->d_mask_ptr;
 			a.mask_col = s->d_mask_col;
 			a.first_free = s->d_first_free;
@@ -1135,6 +1265,8 @@ extern "C" int mfgpu_recommend_noalloc(int users, int items, int features, int l
 	a.ld = ld;
 	a.n_splits = splits;
 	a.tiles_per_split = (n_tiles + splits - 1) / splits;
+	a.tile_begin = 0;
+	a.tile_end = n_tiles;
 	a.mask_ptr = mask_ptr;
 	a.mask_col = mask_col;
 	a.first_free = first_free;

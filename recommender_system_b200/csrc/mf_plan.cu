@@ -567,7 +567,8 @@ static void shard_destroy(mf_shard *s, bool own_sync)
 	void *ptrs[] = {s->d_row_id, s->d_row_ptr, s->d_col_idx, s->d_epos, s->d_col_id, s->d_col_ptr,
 	                s->d_row_idx, s->d_val, s->d_e_csc, s->d_e_csr, s->d_mask_ptr, s->d_mask_col,
 	                s->d_first_free, s->d_item_slot, s->d_touched_item, s->d_push_owner, s->d_push_row, s->d_contrib, s->part_v, s->part_j,
-	                s->nan_first, s->d_best, s->L_keep, s->R_keep, s->d_chunk_row, s->d_chunk_pos, s->d_units, s->d_ticket};
+	                s->nan_first, s->d_best, s->L_keep, s->R_keep, s->d_chunk_row, s->d_chunk_pos, s->d_units, s->d_ticket,
+	                s->am_L, s->am_mask_ptr, s->am_mask_col, s->am_first_free, s->am_part_v, s->am_out_v, s->am_part_j, s->am_nan, s->am_out_j};
 	for (void *q : ptrs)
 		dev_free(q, s->st);
 	tc.lap("destroy: other buffers");
@@ -831,6 +832,7 @@ static int plan_create(mfgpu_plan **out, int users, int items, int features, int
 	pl->opt_resident = 1;
 	pl->opt_res_rows = 0;
 	pl->opt_chain_ws = 1;
+	pl->opt_argmax_items = -1;   /* item-sharded arg-max when users << items (mfgpu_plan_recommend) */
 	pl->opt_pair = -1;           /* split mode by shape (mf_configure_shard) */
 	pl->opt_pair_warps = 4;
 	pl->opt_pair_stages = 2;
@@ -1214,6 +1216,7 @@ extern "C" int mfgpu_plan_set_option(mfgpu_plan *pl, const char *name, int value
 	else if (!strcmp(name, "pair_stages")) pl->opt_pair_stages = value;
 	else if (!strcmp(name, "pair_warps")) pl->opt_pair_warps = value;
 	else if (!strcmp(name, "acc_gw")) pl->opt_acc_gw = value;
+	else if (!strcmp(name, "argmax_items")) pl->opt_argmax_items = value;
 	else if (!strcmp(name, "comm_timeout_ms")) pl->comm_timeout_ns = (unsigned long long)std::max(1, value) * 1000000ull;
 	else if (!strcmp(name, "exchange")) {
 		/* rank mode, collective: 0 = ncclAllReduce; peer memory when available: 1 / -1 = low

@@ -68,6 +68,7 @@ struct ArgmaxArgs {
 	int l_row0;
 	int items, F, ld;
 	int tiles_per_split, n_splits;
+	int tile_begin, tile_end; /* item tiles handled by this launch: [tile_begin, tile_end) (an item block of one GPU, or all) */
 	const int *mask_ptr;      /* [users+1] global user index */
 	const int *mask_col;
 	const int *first_free;    /* [users] */

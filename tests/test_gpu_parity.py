@@ -400,6 +400,43 @@ def test_multi_gpu_matches_sharded_oracle(gpu, oracle, nshards, options):
                                                  inst.entries, L0, R0))
 
 
+@pytest.mark.parametrize("nshards", [2, 4, 8])
+def test_item_sharded_argmax(gpu, oracle, nshards):
+    """Few users, many items on N GPUs of one process: every GPU scans its block of items for all
+    users, the blocks are merged with (value greater, else index lower) -- the serial rule of
+    matFact.c:13-25, incl. ties across blocks, NaN never displacing, a NaN at the first unrated
+    item never displaced, a user who rated everything printing nothing."""
+    if gpu.device_count() < nshards:
+        pytest.skip("needs %d GPUs" % nshards)
+    users, items, F = 24, 2500, 5
+    inst = synth.random_instance(users, items, F, 0.02, 0, 0.0, seed=8)
+    rng = np.random.default_rng(1)
+    L = rng.standard_normal((users, F))
+    R = rng.standard_normal((items, F))
+    R[1700] = R[300]; R[2400] = R[300]; R[900] = R[300]    # exact ties in different blocks
+    L[1] = 0.0                                   # a row of +0.0: the first unrated item wins
+    L[2, 0] = np.nan                             # a NaN row: the first unrated item stays
+    R[5, 1] = np.nan
+    R[2000, 2] = np.inf
+    L[3] = np.abs(L[3]); L[4] = -np.abs(L[4])
+    for forced in (1, 0):                        # by items, and (same answer) by users
+        for first_nan in (False, True):
+            if first_nan:
+                R[0, :] = np.nan
+            ref = oracle.recommend(users, items, F, inst.entries, L, R)
+            with gpu.Plan(users, items, F, inst.entries, 0.0, ngpus=nshards) as plan:
+                plan.set_option("argmax_items", forced)
+                plan.set_factors(L, R)
+                got = plan.recommend()
+            assert np.array_equal(ref, got), (forced, first_nan)
+            R[0, :] = rng.standard_normal(F)
+    full = synth.random_instance(6, 700, 4, 1.0, 0, 0.0, seed=3)      # everything rated: -1 everywhere
+    with gpu.Plan(6, 700, 4, full.entries, 0.0, ngpus=nshards) as plan:
+        plan.set_option("argmax_items", 1)
+        plan.set_factors(rng.standard_normal((6, 4)), rng.standard_normal((700, 4)))
+        assert np.all(plan.recommend() == -1)
+
+
 def test_cli_on_several_gpus(gpu, oracle, tmp_path):
     """The drop-in program with MATFACT_NGPUS: same stdout as on one GPU for the samples (the
     N-shard order moves L and R by ~1e-13, never a recommendation: SURVEY.md section 4)."""
