@@ -353,18 +353,27 @@ class Ctx:
         torch.cuda.set_device(self.local)
         self.comm = None
         if self.world > 1:
+            if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+                os.environ["NCCL_DEBUG"] = "WARN"       # the version banner goes to stdout: one JSON line only
             dist.init_process_group("nccl", device_id=torch.device("cuda", self.local))
             uid = torch.zeros(api.UID_BYTES, dtype=torch.uint8, device="cuda")
             if self.rank == 0:
                 uid.copy_(torch.frombuffer(bytearray(api.Comm.unique_id()), dtype=torch.uint8))
             dist.broadcast(uid, 0)
             self.comm = api.Comm(self.world, self.rank, bytes(uid.cpu().numpy().tobytes()), self.local)
+            self.cpu_group = dist.new_group(backend="gloo")     # waits that must not occupy a GPU
         self.n_gpus = self.world if self.world > 1 else args.gpus
 
     def barrier(self):
         self.torch.cuda.synchronize()
         if self.world > 1:
             self.dist.barrier()
+
+    def host_barrier(self):
+        """A barrier that waits on the host: no kernel spins on any GPU meanwhile."""
+        self.torch.cuda.synchronize()
+        if self.world > 1:
+            self.dist.barrier(group=self.cpu_group)
 
     def max_over_ranks(self, x):
         if self.world == 1:
@@ -544,10 +553,12 @@ def bench_workload(cx, name, steps, warmup, e2e_steps, headline):
                     "d2h_bytes_per_step": int(d2h), "steps": e2e_steps, "ms_per_step": 1e3 * e2e_s / e2e_steps}}
 
 
-def bench_argmax_1e6(cx):
+def bench_argmax_1e6(cx, ngpus=1):
     """BASELINE.json configs[4]: samples/inst1000-1e6-1000-1-3.in as it is -- its loop is 2e4
     nonzero-updates, its run time is the masked arg-max over L.R^T (2e12 separately rounded flops).
-    One GPU (R is 8 GB per buffer and is generated on the device); reports the arg-max time."""
+    R is 8 GB per buffer and is generated on the device(s).  On N GPUs it runs as ONE process
+    driving the N GPUs (rank 0 of the bench; what `MATFACT_NGPUS=N matFact` does): the arg-max is
+    sharded by ITEMS, every GPU scanning its block for all 1000 users.  Reports the arg-max time."""
     import hashlib
     from recommender_system_b200.io import format_output, read_instance
     api = cx.api
@@ -556,7 +567,7 @@ def bench_argmax_1e6(cx):
         path += ".gz"
     inst = read_instance(path)
     t0 = time.perf_counter()
-    with api.Plan(inst.users, inst.items, inst.features, inst.entries, inst.alpha, ngpus=1) as plan:
+    with api.Plan(inst.users, inst.items, inst.features, inst.entries, inst.alpha, ngpus=ngpus) as plan:
         t1 = time.perf_counter()
         plan.init_factors()
         t2 = time.perf_counter()
@@ -569,8 +580,9 @@ def bench_argmax_1e6(cx):
     flops = 2.0 * inst.users * inst.items * inst.features
     out = format_output(best)
     return {"workload": "samples/inst1000-1e6-1000-1-3.in: U=1000 I=1000000 F=1000 nnz=%d" % inst.nnz,
+            "n_gpus": ngpus, "sharding": "items (one process, N GPUs)" if ngpus > 1 else "none",
             "argmax_ms": ms, "tflops_separately_rounded": flops / (ms * 1e-3) / 1e12,
-            "frac_of_fp64_issue_roof": flops / (ms * 1e-3) / 18.6e12,
+            "frac_of_fp64_issue_roof": flops / (ms * 1e-3) / 18.6e12 / ngpus,
             "fp64_issue_roof": "64 FP64 lanes/clk/SM x 148 SMs x 1.965 GHz = 18.6e12 multiplies or adds per second "
                                "(no FMA: the reference rounds the product and the sum separately)",
             "loop_ms": loop_ms, "plan_create_s": t1 - t0, "init_factors_s": t2 - t1,
@@ -615,11 +627,14 @@ def main():
                            "e2e": x["e2e"], "argmax_ms": x["argmax_ms"], "clocks": x["clocks"],
                            "parity": x["parity"],
                            "roofline": {k: x["roofline"][k] for k in ("kernel", "achieved", "frac", "kernel_ms", "iteration", "l2_gather")}}
-        if cx.n_gpus == 1 and rank == 0:
+        # rank 0 alone drives all N GPUs for this one; the other ranks wait on the host, GPUs idle
+        cx.host_barrier()
+        if rank == 0:
             try:
-                extra["inst1e6_argmax"] = bench_argmax_1e6(cx)
+                extra["inst1e6_argmax"] = bench_argmax_1e6(cx, cx.n_gpus)
             except Exception as exc:  # noqa: BLE001  (e.g. not enough host memory on the box)
                 extra["inst1e6_argmax"] = {"skipped": str(exc)}
+        cx.host_barrier()
 
     cpu = None
     if rank == 0 and cx.n_gpus == 1 and not args.no_cpu_baseline:
