@@ -524,11 +524,10 @@ def bench_workload(cx, name, steps, warmup, e2e_steps, headline):
         pl = make_plan(); t.append(time.perf_counter())
         pl.set_factors(Lp, Rp); t.append(time.perf_counter())
         pl.iterate(T); t.append(time.perf_counter())
-        pl.get_factors(Lo, Ro); t.append(time.perf_counter())
-        pl.recommend(best2); t.append(time.perf_counter())
+        pl.get_results(Lo, Ro, best2); t.append(time.perf_counter())
         pl.close(); t.append(time.perf_counter())
         if os.environ.get("MFGPU_TRACE"):       # host-side view; iterate returns before the device is done
-            names = ["create", "set_factors", "iterate (enqueue)", "get_factors (+wait)", "recommend", "close"]
+            names = ["create", "set_factors", "iterate (enqueue)", "get_results: factors D2H beside the arg-max (+wait)", "close"]
             print("[bench rank %d] " % rank + ", ".join("%s %.1f ms" % (n, (b - a) * 1e3)
                                                         for n, a, b in zip(names, t, t[1:])), file=sys.stderr)
 

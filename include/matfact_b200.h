@@ -129,6 +129,9 @@ int mfgpu_plan_init_factors(mfgpu_plan *plan);
 /* Device -> host.  In rank mode only the rows of L owned by this rank are
  * written (the others are left untouched); R is complete on every rank. */
 int mfgpu_plan_get_factors(mfgpu_plan *plan, double *L, double *R);
+/* mfgpu_plan_get_factors and mfgpu_plan_recommend in one call: the copies of the factors run on
+ * the copy engine beside the arg-max kernels.  L and R may be NULL (not copied). */
+int mfgpu_plan_get_results(mfgpu_plan *plan, double *L, double *R, int *best);
 /* Enqueue `iters` iterations; returns once they are enqueued. */
 int mfgpu_plan_iterate(mfgpu_plan *plan, int iters);
 /* Wait for everything enqueued on the plan. */

@@ -26,7 +26,7 @@ EXPORTS = [
     "mfgpu_device_count", "mfgpu_last_error", "mfgpu_version",
     "mfgpu_factorize", "mfgpu_recommend", "mfgpu_run",
     "mfgpu_plan_create", "mfgpu_plan_create_rank", "mfgpu_plan_destroy",
-    "mfgpu_plan_set_factors", "mfgpu_plan_init_factors", "mfgpu_plan_get_factors", "mfgpu_plan_iterate", "mfgpu_plan_sync",
+    "mfgpu_plan_set_factors", "mfgpu_plan_init_factors", "mfgpu_plan_get_factors", "mfgpu_plan_get_results", "mfgpu_plan_iterate", "mfgpu_plan_sync",
     "mfgpu_plan_last_loop_ms", "mfgpu_plan_recommend", "mfgpu_plan_last_recommend_ms",
     "mfgpu_plan_user_range", "mfgpu_plan_launch_count", "mfgpu_plan_exchange_kind", "mfgpu_plan_bytes_per_iter",
     "mfgpu_plan_set_option", "mfgpu_plan_save_factors", "mfgpu_plan_restore_factors",
@@ -73,6 +73,7 @@ def lib():
     L.mfgpu_plan_set_factors.argtypes = [vp, vp, vp]
     L.mfgpu_plan_init_factors.argtypes = [vp]
     L.mfgpu_plan_get_factors.argtypes = [vp, vp, vp]
+    L.mfgpu_plan_get_results.argtypes = [vp, vp, vp, vp]
     L.mfgpu_plan_iterate.argtypes = [vp, i]
     L.mfgpu_plan_sync.argtypes = [vp]
     L.mfgpu_plan_last_loop_ms.argtypes = [vp, ctypes.POINTER(ctypes.c_float)]
@@ -303,6 +304,14 @@ class Plan:
     def get_factors(self, L, R):
         _f64(L, (self.users, self.features)); _f64(R, (self.items, self.features))
         _check(lib().mfgpu_plan_get_factors(self._h, L.ctypes.data, R.ctypes.data))
+
+    def get_results(self, L, R, best=None):
+        """get_factors + recommend in one call (the copies run beside the arg-max)."""
+        if best is None:
+            best = np.full(self.users, -2, dtype=np.int32)
+        _f64(L, (self.users, self.features)); _f64(R, (self.items, self.features))
+        _check(lib().mfgpu_plan_get_results(self._h, L.ctypes.data, R.ctypes.data, best.ctypes.data))
+        return best
 
     def iterate(self, iters):
         _check(lib().mfgpu_plan_iterate(self._h, iters))

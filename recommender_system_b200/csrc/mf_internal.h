@@ -126,6 +126,7 @@ struct mfgpu_plan {
 	int cut[MF_MAX_SHARDS + 1];
 	mf_shard sh[MF_MAX_SHARDS];
 	mfgpu_comm *comm;            /* rank mode, else NULL   */
+	const mf_scan *scan;         /* during plan creation: what the pass over the entries found */
 	int n_touched;               /* items with >=1 nonzero */
 	int cur;                     /* buffer holding the current factors */
 	int have_factors;

@@ -1146,9 +1146,11 @@ static int run_all(int users, int items, int features, int nnz, const mfgpu_entr
 	int rc = mfgpu_plan_set_factors(pl, L, R);
 	if (rc == MFGPU_OK && factorize)
 		rc = mfgpu_plan_iterate(pl, iters);
-	if (rc == MFGPU_OK && writeback)
+	if (rc == MFGPU_OK && writeback && best)
+		rc = mfgpu_plan_get_results(pl, L, R, best);
+	else if (rc == MFGPU_OK && writeback)
 		rc = mfgpu_plan_get_factors(pl, L, R);
-	if (rc == MFGPU_OK && best)
+	else if (rc == MFGPU_OK && best)
 		rc = mfgpu_plan_recommend(pl, best);
 	if (rc == MFGPU_OK)
 		rc = mfgpu_plan_sync(pl);

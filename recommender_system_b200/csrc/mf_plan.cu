@@ -438,8 +438,8 @@ static int shard_create(mfgpu_plan *pl, mf_shard *s, int dev, const mfgpu_entry 
 	s->host_ws = ws_acquire(mf_pattern_ws_bytes(pl->users, pl->items, pl->nnz, s->user_lo, s->user_hi),
 	                        &s->host_ws_bytes);
 	tc.lap("create: host workspace");
-	int rc = mf_pattern_build_ws(&s->pat, pl->users, pl->items, pl->nnz, entries, s->user_lo, s->user_hi,
-	                             s->host_ws, s->host_ws_bytes);
+	int rc = mf_pattern_build_scan(&s->pat, pl->users, pl->items, pl->nnz, entries, s->user_lo, s->user_hi,
+	                               s->host_ws, s->host_ws_bytes, pl->scan);
 	tc.lap("create: pattern build (host)");
 	if (rc != MFGPU_OK)
 		return mf_fail(rc, rc == MFGPU_EINVAL ? "an entry lies outside the users x items matrix"
@@ -839,42 +839,39 @@ static int plan_create(mfgpu_plan **out, int users, int items, int features, int
 	pl->opt_exchange = -1;       /* peer memory when it can be had */
 
 	TraceClock tc;
-	int rc = mf_split_users(users, nnz, entries, nshards, pl->cut);
-	int *item_slot = nullptr, *touched = nullptr, *contrib = nullptr;
-	if (rc == MFGPU_OK && nshards > 1) {
-		item_slot = (int *)malloc(sizeof(int) * (size_t)(items ? items : 1));
-		if (!item_slot)
-			rc = MFGPU_ENOMEM;
-		else {
-			int cnt = mf_touched_items(items, nnz, entries, item_slot);
-			if (cnt < 0)
-				rc = cnt;
-			else {
-				pl->n_touched = cnt;
-				pl->slots_per_rank = std::max(1, (cnt + nshards - 1) / nshards);
-				touched = (int *)malloc(sizeof(int) * (size_t)(cnt ? cnt : 1));
-				if (!touched)
-					rc = MFGPU_ENOMEM;
-				else
-					for (int j = 0; j < items; j++)
-						if (item_slot[j] >= 0)
-							touched[item_slot[j]] = j;
-				if (rc == MFGPU_OK) {
-					/* blocks of touched items per reducing shard, contributors of every item */
-					contrib = (int *)calloc((size_t)(cnt ? cnt : 1), sizeof(int));
-					if (!contrib)
-						rc = MFGPU_ENOMEM;
-					else {
-						const int per = mf_exchange_layout(users, nnz, entries, nshards, pl->cut, item_slot, cnt, contrib);
-						if (per < 0)
-							rc = per;
-						else
-							pl->slots_per_rank = per;
-					}
-				}
-			}
+	/* one pass over the whole entry list (host/mf_prep.c: mf_scan_entries): the cut, the touched
+	 * items, the contributors of every item, and -- when the rows never decrease, as in every
+	 * file of the reference -- where each user's entries start, so that a shard builds its
+	 * pattern from its own entries only */
+	int rc = MFGPU_OK;
+	int *item_slot = (int *)malloc(sizeof(int) * (size_t)(items ? items : 1));
+	int *row_first = (int *)malloc(sizeof(int) * ((size_t)users + 1));
+	int *touched = nullptr, *contrib = nullptr;
+	mf_scan scan;
+	memset(&scan, 0, sizeof scan);
+	if (nshards > 1)
+		contrib = (int *)calloc((size_t)(items ? items : 1), sizeof(int));
+	if (!item_slot || !row_first || (nshards > 1 && !contrib))
+		rc = MFGPU_ENOMEM;
+	else {
+		int per = 1;
+		const int cnt = mf_scan_entries(users, items, nnz, entries, nshards, pl->cut, item_slot, row_first, &scan,
+		                                contrib, &per);
+		if (cnt < 0)
+			rc = cnt;
+		else if (nshards > 1) {
+			pl->n_touched = cnt;
+			pl->slots_per_rank = per;
+			touched = (int *)malloc(sizeof(int) * (size_t)(cnt ? cnt : 1));
+			if (!touched)
+				rc = MFGPU_ENOMEM;
+			else
+				for (int j = 0; j < items; j++)
+					if (item_slot[j] >= 0)
+						touched[item_slot[j]] = j;
 		}
 	}
+	pl->scan = &scan;
 	if (rc != MFGPU_OK)
 		mf_fail(rc, rc == MFGPU_EINVAL ? "an entry lies outside the users x items matrix"
 		                               : "out of host memory");
@@ -924,7 +921,9 @@ static int plan_create(mfgpu_plan **out, int users, int items, int features, int
 				rc = mf_xchg_setup_local(pl);
 		}
 	}
+	pl->scan = nullptr;
 	free(item_slot);
+	free(row_first);
 	free(touched);
 	free(contrib);
 	if (rc != MFGPU_OK) {
@@ -1114,23 +1113,51 @@ extern "C" int mfgpu_plan_init_factors(mfgpu_plan *pl)
 	return MFGPU_OK;
 }
 
-extern "C" int mfgpu_plan_get_factors(mfgpu_plan *pl, double *L, double *R)
+/* device -> host copies of the current factors; side = true: on the shard's second stream,
+ * behind everything enqueued on the first so far, so that they run beside what is enqueued on
+ * the first stream next (the arg-max) */
+static int enqueue_get_factors(mfgpu_plan *pl, double *L, double *R, bool side)
 {
-	if (!pl)
-		return mf_fail(MFGPU_EINVAL, "null plan");
 	const size_t F = (size_t)pl->F, ld = (size_t)pl->ld;
 	const int c = pl->cur;
 	for (int g = 0; g < local_shards(pl); g++) {
 		mf_shard *s = &pl->sh[g];
 		CK(cudaSetDevice(s->dev));
+		cudaStream_t st = s->st;
+		if (side) {
+			CK(cudaEventRecord(s->ev_a, s->st));
+			CK(cudaStreamWaitEvent(s->st2, s->ev_a, 0));
+			st = s->st2;
+		}
 		const size_t nu = (size_t)(s->user_hi - s->user_lo);
 		if (L && F && nu)
-			TRY(copy_rows(L + (size_t)s->user_lo * F, F, s->L[c], ld, F, nu, cudaMemcpyDeviceToHost, s->st));
+			TRY(copy_rows(L + (size_t)s->user_lo * F, F, s->L[c], ld, F, nu, cudaMemcpyDeviceToHost, st));
 		if (R && g == 0 && F && pl->items)
-			TRY(copy_rows(R, F, s->R[c], ld, F, (size_t)pl->items, cudaMemcpyDeviceToHost, s->st));
+			TRY(copy_rows(R, F, s->R[c], ld, F, (size_t)pl->items, cudaMemcpyDeviceToHost, st));
 	}
+	return MFGPU_OK;
+}
+
+extern "C" int mfgpu_plan_get_factors(mfgpu_plan *pl, double *L, double *R)
+{
+	if (!pl)
+		return mf_fail(MFGPU_EINVAL, "null plan");
+	TRY(enqueue_get_factors(pl, L, R, false));
 	for (int g = 0; g < local_shards(pl); g++)
 		CK(cudaStreamSynchronize(pl->sh[g].st));
+	return mf_check_comm_error(pl);
+}
+
+extern "C" int mfgpu_plan_get_results(mfgpu_plan *pl, double *L, double *R, int *best)
+{
+	if (!pl || !best)
+		return mf_fail(MFGPU_EINVAL, "null argument");
+	TRY(enqueue_get_factors(pl, L, R, true));        /* copy engine ... */
+	TRY(mfgpu_plan_recommend(pl, best));             /* ... beside the arg-max kernels */
+	for (int g = 0; g < local_shards(pl); g++) {
+		CK(cudaSetDevice(pl->sh[g].dev));
+		CK(cudaStreamSynchronize(pl->sh[g].st2));
+	}
 	return mf_check_comm_error(pl);
 }
 

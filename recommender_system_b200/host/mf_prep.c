@@ -180,6 +180,13 @@ int mf_pattern_build_ws(mf_pattern *p, int users, int items, int nnz,
                         const mfgpu_entry *entries, int user_lo, int user_hi,
                         void *ws, size_t ws_bytes)
 {
+	return mf_pattern_build_scan(p, users, items, nnz, entries, user_lo, user_hi, ws, ws_bytes, NULL);
+}
+
+int mf_pattern_build_scan(mf_pattern *p, int users, int items, int nnz,
+                          const mfgpu_entry *entries, int user_lo, int user_hi,
+                          void *ws, size_t ws_bytes, const mf_scan *scan)
+{
 	memset(p, 0, sizeof *p);
 	p->ws = (char *)ws;
 	p->ws_bytes = ws ? ws_bytes : 0;
@@ -192,7 +199,14 @@ int mf_pattern_build_ws(mf_pattern *p, int users, int items, int nnz,
 	p->user_lo = user_lo;
 	p->user_hi = user_hi;
 
-	const int T = prep_threads(nnz);
+	/* the entries that can belong to this shard: all of them, or -- rows known never to decrease
+	 * (mf_scan_entries) -- the slice of its users */
+	int n_lo = 0, n_hi = nnz;
+	if (scan && scan->by_row && scan->row_first) {
+		n_lo = scan->row_first[user_lo];
+		n_hi = scan->row_first[user_hi];
+	}
+	const int T = prep_threads(n_hi - n_lo);
 	prep_slice sl[MF_PREP_MAX_THREADS];
 	int *cur = NULL;            /* threads 1..T-1: their per-row / per-column arrays */
 	int *row_count = xcalloc((size_t)users, sizeof *row_count);
@@ -209,8 +223,8 @@ int mf_pattern_build_ws(mf_pattern *p, int users, int items, int nnz,
 	}
 	for (int t = 0; t < T; t++) {
 		sl[t].entries = entries;
-		sl[t].n0 = (int)((long)nnz * t / T);
-		sl[t].n1 = (int)((long)nnz * (t + 1) / T);
+		sl[t].n0 = n_lo + (int)((long)(n_hi - n_lo) * t / T);
+		sl[t].n1 = n_lo + (int)((long)(n_hi - n_lo) * (t + 1) / T);
 		sl[t].users = users;
 		sl[t].items = items;
 		sl[t].user_lo = user_lo;
@@ -236,6 +250,8 @@ int mf_pattern_build_ws(mf_pattern *p, int users, int items, int nnz,
 	for (int t = T - 1; t >= 0; t--)
 		if (sl[t].first_unsorted < sl[t].n1)
 			matched = sl[t].first_unsorted;
+	if (scan)
+		matched = scan->matched;         /* of the whole list, not of the slice */
 	for (int i = user_lo; i < user_hi; i++) {
 		int c = 0;
 		for (int t = 0; t < T; t++)
@@ -304,7 +320,7 @@ int mf_pattern_build_ws(mf_pattern *p, int users, int items, int nnz,
 		for (int i = user_lo; i < user_hi; i++)
 			p->mask_ptr[i + 1] = row_count[i];
 	} else {
-		for (int n = 0; n < matched; n++) {
+		for (int n = n_lo; n < matched && n < n_hi; n++) {
 			int r = entries[n].row;
 			if (r >= user_lo && r < user_hi)
 				p->mask_ptr[r + 1]++;
@@ -359,6 +375,174 @@ void mf_pattern_free(mf_pattern *p)
 	free(p->col_id); free(p->col_ptr); free(p->row_idx);
 	free(p->mask_ptr); free(p->mask_col); free(p->first_free);
 	memset(p, 0, sizeof *p);
+}
+
+/* ---- mf_scan_entries: one pass for the whole list ------------------------------------------ */
+typedef struct {
+	const mfgpu_entry *entries;
+	int n0, n1, users, items;
+	int *row_cnt;               /* [users] of this thread   */
+	unsigned char *col_seen;    /* [items] of this thread   */
+	int bad, row_desc, first_unsorted;
+	/* second pass */
+	const int *cut, *item_slot;
+	int nshards;
+	int *contrib;               /* [n_touched] of this thread */
+} scan_slice;
+
+static void *scan_count(void *arg)
+{
+	scan_slice *s = arg;
+	long prev_r = -1, prev_c = -1;
+	if (s->n0 > 0) {
+		prev_r = s->entries[s->n0 - 1].row;
+		prev_c = s->entries[s->n0 - 1].col;
+	}
+	s->first_unsorted = s->n1;
+	for (int n = s->n0; n < s->n1; n++) {
+		const int r = s->entries[n].row, c = s->entries[n].col;
+		if (r < 0 || r >= s->users || c < 0 || c >= s->items) {
+			s->bad = 1;
+			return NULL;
+		}
+		if (r < prev_r)
+			s->row_desc = 1;
+		if (!(r > prev_r || (r == prev_r && c > prev_c)) && s->first_unsorted == s->n1)
+			s->first_unsorted = n;
+		prev_r = r;
+		prev_c = c;
+		s->row_cnt[r]++;
+		s->col_seen[c] = 1;
+	}
+	return NULL;
+}
+
+static void *scan_contrib(void *arg)
+{
+	scan_slice *s = arg;
+	int r = 0;
+	for (int n = s->n0; n < s->n1; n++) {
+		const int u = s->entries[n].row;
+		while (r + 1 < s->nshards && u >= s->cut[r + 1])
+			r++;
+		while (r > 0 && u < s->cut[r])
+			r--;
+		s->contrib[s->item_slot[s->entries[n].col]] |= 1 << r;
+	}
+	return NULL;
+}
+
+static void run_scan(scan_slice *sl, int T, void *(*fn)(void *))
+{
+	pthread_t th[MF_PREP_MAX_THREADS];
+	int started[MF_PREP_MAX_THREADS] = {0};
+	for (int t = 1; t < T; t++)
+		started[t] = pthread_create(&th[t], NULL, fn, &sl[t]) == 0;
+	fn(&sl[0]);
+	for (int t = 1; t < T; t++) {
+		if (started[t])
+			pthread_join(th[t], NULL);
+		else
+			fn(&sl[t]);
+	}
+}
+
+int mf_scan_entries(int users, int items, int nnz, const mfgpu_entry *entries, int nshards,
+                    int *cut, int *item_slot, int *row_first, mf_scan *scan,
+                    int *contrib, int *slots_per_rank)
+{
+	if (users < 0 || items < 0 || nnz < 0 || nshards < 1 || nshards > 31 || !cut || !item_slot || !row_first || !scan)
+		return MFGPU_EINVAL;
+	if (nnz > 0 && !entries)
+		return MFGPU_EINVAL;
+	const int T = prep_threads(nnz);
+	scan_slice sl[MF_PREP_MAX_THREADS];
+	int *cnt = xcalloc((size_t)T * (size_t)users, sizeof *cnt);
+	unsigned char *seen = xcalloc((size_t)T * (size_t)items, 1);
+	int *ctr = NULL;
+	int rc = MFGPU_ENOMEM, n_touched = 0;
+	if (!cnt || !seen)
+		goto done;
+	memset(sl, 0, sizeof sl);
+	for (int t = 0; t < T; t++) {
+		sl[t].entries = entries;
+		sl[t].n0 = (int)((long)nnz * t / T);
+		sl[t].n1 = (int)((long)nnz * (t + 1) / T);
+		sl[t].users = users;
+		sl[t].items = items;
+		sl[t].row_cnt = cnt + (size_t)t * users;
+		sl[t].col_seen = seen + (size_t)t * items;
+	}
+	run_scan(sl, T, scan_count);
+	int by_row = 1, matched = nnz;
+	for (int t = T - 1; t >= 0; t--) {
+		if (sl[t].bad) {
+			rc = MFGPU_EINVAL;
+			goto done;
+		}
+		if (sl[t].row_desc)
+			by_row = 0;
+		if (sl[t].first_unsorted < sl[t].n1)
+			matched = sl[t].first_unsorted;
+	}
+	/* nonzeros per user -> where each user's entries start (by_row) and the balanced cut */
+	long run = 0;
+	int s = 1;
+	cut[0] = 0;
+	for (int i = 0; i < users; i++) {
+		row_first[i] = (int)run;
+		/* smallest i with (nonzeros before i) >= s*nnz/nshards, as mf_split_users */
+		while (s < nshards && run >= (long)((double)nnz * s / nshards + 0.5))
+		{
+			cut[s] = nnz ? i : (int)((long)s * users / nshards);
+			s++;
+		}
+		for (int t = 0; t < T; t++)
+			run += sl[t].row_cnt[i];
+	}
+	row_first[users] = (int)run;
+	while (s < nshards) {
+		cut[s] = nnz ? users : (int)((long)s * users / nshards);
+		s++;
+	}
+	cut[nshards] = users;
+	for (int j = 0; j < items; j++) {
+		int any = 0;
+		for (int t = 0; t < T; t++)
+			any |= sl[t].col_seen[j];
+		item_slot[j] = any ? n_touched++ : -1;
+	}
+	scan->by_row = by_row;
+	scan->matched = matched;
+	scan->row_first = row_first;
+	if (contrib) {
+		ctr = xcalloc((size_t)T * (size_t)(n_touched ? n_touched : 1), sizeof *ctr);
+		if (!ctr)
+			goto done;
+		for (int t = 0; t < T; t++) {
+			sl[t].cut = cut;
+			sl[t].item_slot = item_slot;
+			sl[t].nshards = nshards;
+			sl[t].contrib = ctr + (size_t)t * n_touched;
+		}
+		run_scan(sl, T, scan_contrib);
+		for (int k = 0; k < n_touched; k++) {
+			int m = 0;
+			for (int t = 0; t < T; t++)
+				m |= sl[t].contrib[k];
+			contrib[k] = m;
+		}
+		if (slots_per_rank) {
+			const int per = (n_touched + nshards - 1) / nshards;
+			*slots_per_rank = per > 0 ? per : 1;
+		}
+	}
+	rc = n_touched;
+done:
+	free(cnt);
+	free(seen);
+	free(ctr);
+	return rc;
 }
 
 int mf_split_users(int users, int nnz, const mfgpu_entry *entries, int nshards, int *cut)

@@ -65,6 +65,33 @@ int mf_pattern_build_ws(mf_pattern *p, int users, int items, int nnz,
                         const mfgpu_entry *entries, int user_lo, int user_hi,
                         void *ws, size_t ws_bytes);
 
+/* What one pass over the whole entry list learns (mf_scan_entries): enough for a shard to build
+ * its pattern from ITS entries only.  by_row: rows never decrease, so the entries of the users
+ * [lo, hi) are the contiguous slice [first_of_row(lo), first_of_row(hi)) (row_first has users+1
+ * ints; valid only when by_row).  matched: mf_mask_prefix of the whole list. */
+typedef struct {
+	int by_row;
+	int matched;
+	const int *row_first;       /* [users+1] first entry of each user's rows, when by_row */
+} mf_scan;
+
+/* The same build from the knowledge of a scan: only the entries of the slice are read. */
+int mf_pattern_build_scan(mf_pattern *p, int users, int items, int nnz,
+                          const mfgpu_entry *entries, int user_lo, int user_hi,
+                          void *ws, size_t ws_bytes, const mf_scan *scan);
+
+/* One threaded pass over the entries for everything plan creation needs from the WHOLE list
+ * (each used to be a pass of its own): validation, nonzeros per user -> cut[nshards+1]
+ * (mf_split_users), items with a nonzero -> item_slot[items] and their number (mf_touched_items),
+ * whether the rows never decrease and where each user's entries start (row_first[users+1],
+ * caller-provided), the matched prefix of print_output (mf_mask_prefix); and a second pass, only
+ * when contrib != NULL (nshards > 1), for the contributors of every touched item
+ * (mf_exchange_layout; contrib has room for `items` ints, *slots_per_rank is returned).
+ * Returns the number of touched items or an MFGPU_E* code (< 0). */
+int mf_scan_entries(int users, int items, int nnz, const mfgpu_entry *entries, int nshards,
+                    int *cut, int *item_slot, int *row_first, mf_scan *scan,
+                    int *contrib, int *slots_per_rank);
+
 /* Number of leading entries the cursor of print_output (matFact.c:14-22) ever
  * matches: the longest prefix that is strictly increasing in (row, col).  For
  * the (row, col)-sorted, duplicate-free files of the reference this is nnz. */

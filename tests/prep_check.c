@@ -86,6 +86,34 @@ int main(void)
 			mf_pattern_free(&got);
 		}
 		if (mf_mask_prefix(users, items, nnz, e) < nnz && trial % 3 == 0) { printf("unexpected disorder\n"); fails++; }
+		/* the one-pass scan (mf_scan_entries) against the passes it replaces, and the build from
+		 * its knowledge (only the slice of the shard's users is read) against the full build */
+		for (int T = 1; T <= 8; T += 7) {
+			char buf[8];
+			snprintf(buf, sizeof buf, "%d", T);
+			setenv("MFGPU_PREP_THREADS", buf, 1);
+			for (int ns = 1; ns <= 8; ns += 7) {
+				int cut[9], cut2[9], per = 0;
+				int *slot = malloc(sizeof(int) * items), *slot2 = malloc(sizeof(int) * items);
+				int *ctr = malloc(sizeof(int) * items), *ctr2 = malloc(sizeof(int) * items);
+				int *first = malloc(sizeof(int) * (users + 1));
+				mf_scan sc;
+				const int nt = mf_scan_entries(users, items, nnz, e, ns, cut, slot, first, &sc, ctr, &per);
+				const int nt2 = mf_touched_items(items, nnz, e, slot2);
+				mf_split_users(users, nnz, e, ns, cut2);
+				const int per2 = mf_exchange_layout(users, nnz, e, ns, cut2, slot2, nt2, ctr2);
+				int ok = nt == nt2 && per == per2 && !memcmp(cut, cut2, sizeof(int) * (ns + 1)) &&
+				         !memcmp(slot, slot2, sizeof(int) * items) && !memcmp(ctr, ctr2, sizeof(int) * (nt2 > 0 ? nt2 : 0)) &&
+				         sc.matched == mf_mask_prefix(users, items, nnz, e);
+				if (!ok) { printf("MISMATCH in mf_scan_entries (trial %d, %d threads, %d shards)\n", trial, T, ns); fails++; }
+				size_t wsb = mf_pattern_ws_bytes(users, items, nnz, lo, hi);
+				void *ws = malloc(wsb);
+				if (mf_pattern_build_scan(&got, users, items, nnz, e, lo, hi, ws, wsb, &sc)) { printf("scan build failed\n"); return 2; }
+				if (!compare(&ref, &got, users)) { printf("  (trial %d, %d threads, from the scan, by_row %d)\n", trial, T, sc.by_row); fails++; }
+				mf_pattern_free(&got);
+				free(ws); free(slot); free(slot2); free(ctr); free(ctr2); free(first);
+			}
+		}
 		mf_pattern_free(&ref);
 		free(e);
 	}
