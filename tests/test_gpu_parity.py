@@ -457,6 +457,30 @@ def test_cli_on_several_gpus(gpu, oracle, tmp_path):
         assert p.stdout == load_out(sample)
 
 
+@pytest.mark.parametrize("sample", ["inst0", "inst1", "inst2", "inst30-40-10-2-10", "inst500-500-20-2-100", "instML100k"])
+def test_reference_main_with_the_patch(gpu, tmp_path, sample):
+    """The boundary on the reference's OWN main program: /root/reference/matFact.c with the patch of
+    INTEGRATION.md section 1 (oracle/integration_patch.sed: the two calls at the seam replaced by
+    mfgpu_run), built in the build container into oracle/_ref/matFact_patched together with its
+    own parser, mat2d_random_fill_LR and transpose.  Its stdout = the golden .out followed by the
+    "time : ..." line the top-level program prints (benchmark.h)."""
+    exe = os.path.join(ROOT, "oracle", "_ref", "matFact_patched")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/matFact_patched not built (needs the reference checkout at build time)")
+    src = gold_path(sample + ".in")
+    if src.endswith(".gz"):
+        import gzip, shutil
+        plain = tmp_path / (sample + ".in")
+        with gzip.open(src, "rb") as fi, open(plain, "wb") as fo:
+            shutil.copyfileobj(fi, fo)
+        src = str(plain)
+    p = subprocess.run([exe, src], capture_output=True, text=True, timeout=600)
+    assert p.returncode == 0, p.stderr[-2000:]
+    lines = p.stdout.splitlines(keepends=True)
+    assert lines and lines[-1].startswith("time : ")
+    assert "".join(lines[:-1]) == load_out(sample)
+
+
 def test_rank_mode_timeout_is_reported(gpu, tmp_path):
     """A rank that stops taking part: the others' device-side waits run out of time (300 ms
     here), the kernels finish, and the next sync returns MFGPU_ECOMM -- no trap, no hang."""

@@ -229,3 +229,18 @@ def test_library_parser_reads_the_samples_and_reports_reference_errors(built_lib
     with pytest.raises(api.MatFactError, match="Unable to open input file"):
         api.read_instance(str(tmp_path / "missing.in"))
     assert api.selftest_random(0, 200000) == -1 and api.selftest_random(7, 1000) == -1
+
+
+def test_reference_main_with_the_patch_has_no_cpu_path():
+    """oracle/_ref/matFact_patched = the reference's own main with the two calls at the seam
+    replaced by mfgpu_run (oracle/integration_patch.sed).  Without a B200 it must stop the way the
+    reference stops on an error (util.c:7-10: "Error: ...", exit status 255), not compute on the CPU."""
+    import subprocess
+    exe = os.path.join(ROOT, "oracle", "_ref", "matFact_patched")
+    if not os.path.exists(exe):
+        pytest.skip("not built (no reference checkout at build time)")
+    from recommender_system_b200 import api
+    if api.device_count() > 0:
+        pytest.skip("a B200 is visible: covered by the gpu test of the same program")
+    p = subprocess.run([exe, os.path.join(ROOT, "tests", "golden", "inst0.in")], capture_output=True, text=True)
+    assert p.returncode == 255 and p.stderr.startswith("Error: ") and p.stdout == ""
