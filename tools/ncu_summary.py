@@ -47,8 +47,10 @@ STALL_NAMES = ["long_scoreboard", "short_scoreboard", "wait", "barrier", "math_p
 
 def label(kernel):
     """bench.py's name of the launch (recommender_system_b200/api.py KERNELS)."""
-    if "k_update_L" in kernel:
+    if "k_update_L" in kernel or "k_dot_units" in kernel:      # slot 0: the by-user pass (split mode: its dots)
         return "k_update_L"
+    if "k_acc" in kernel:                                        # split mode: every accumulation that is not a deep chain
+        return "k_chain_bulk"
     if "k_dot" in kernel:
         return "k_dot"
     if "k_chain_ws" in kernel:
