@@ -36,7 +36,11 @@ __global__ void __launch_bounds__(256)
 k_masked_argmax(const ArgmaxArgs p, const double *__restrict__ L, const double *__restrict__ R)
 {
 	__shared__ __align__(16) double Ls[AM_KC][AM_LDS];
-	__shared__ __align__(16) double Rs[AM_KC][AM_LDS];
+	/* item c of the tile sits at column c + 2*(c >> 4): 16 bytes of padding after every four
+	 * threads' items, so that the 16-byte reads of a quarter-warp (8 threads x 32-byte stride)
+	 * fall in 8 distinct bank groups (ncu on the unpadded layout: 41 % of the shared-memory
+	 * wavefronts of this kernel were bank conflicts, profiles/r02_notes.md) */
+	__shared__ __align__(16) double Rs[AM_KC][AM_LDS + 8];
 	__shared__ unsigned long long mbits[AM_TI];
 	__shared__ int mcur[AM_TI];
 	__shared__ double red_v[AM_TI][16];
@@ -144,7 +148,7 @@ k_masked_argmax(const ArgmaxArgs p, const double *__restrict__ L, const double *
 #pragma unroll
 			for (int q = 0; q < 4; q++) {
 				Ls[lk + q][lrow] = lv[q];
-				Rs[lk + q][lrow] = rv[q];
+				Rs[lk + q][lrow + 2 * (lrow >> 4)] = rv[q];
 			}
 			__syncthreads();
 			if (k0 + AM_KC < F)
@@ -156,8 +160,8 @@ k_masked_argmax(const ArgmaxArgs p, const double *__restrict__ L, const double *
 				for (int kk = 0; kk < AM_KC; kk++) {
 					const double2 a01 = *reinterpret_cast<const double2 *>(&Ls[kk][ty * 4]);
 					const double2 a23 = *reinterpret_cast<const double2 *>(&Ls[kk][ty * 4 + 2]);
-					const double2 b01 = *reinterpret_cast<const double2 *>(&Rs[kk][tx * 4]);
-					const double2 b23 = *reinterpret_cast<const double2 *>(&Rs[kk][tx * 4 + 2]);
+					const double2 b01 = *reinterpret_cast<const double2 *>(&Rs[kk][tx * 4 + 2 * (tx >> 2)]);
+					const double2 b23 = *reinterpret_cast<const double2 *>(&Rs[kk][tx * 4 + 2 * (tx >> 2) + 2]);
 					const double av[4] = {a01.x, a01.y, a23.x, a23.y};
 					const double bw[4] = {b01.x, b01.y, b23.x, b23.y};
 #pragma unroll
@@ -173,7 +177,7 @@ k_masked_argmax(const ArgmaxArgs p, const double *__restrict__ L, const double *
 #pragma unroll
 						for (int b = 0; b < 4; b++)
 							acc[a][b] = __dadd_rn(acc[a][b],
-							                      __dmul_rn(Ls[kk][ty * 4 + a], Rs[kk][tx * 4 + b]));
+							                      __dmul_rn(Ls[kk][ty * 4 + a], Rs[kk][tx * 4 + 2 * (tx >> 2) + b]));
 				}
 			}
 		}

@@ -130,6 +130,7 @@ struct mfgpu_plan {
 	int n_touched;               /* items with >=1 nonzero */
 	int cur;                     /* buffer holding the current factors */
 	int have_factors;
+	int graph_len;               /* iterations per captured graph once one exists (0: none yet) */
 	long long launches;
 	float loop_ms, rec_ms;
 	/* Rank mode over peer memory (mf_xchg_setup): every rank maps the G and R buffers and the

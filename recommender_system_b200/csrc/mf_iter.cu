@@ -23,6 +23,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <thread>
 #include <vector>
 
 namespace mf {
@@ -378,6 +379,15 @@ int mf_kernels_prepare(int warps, size_t k1_smem, int res_ng, size_t res_smem, s
 
 static int local_shards(const mfgpu_plan *pl) { return pl->comm ? 1 : pl->nshards; }
 
+/* launches issued so far (mfgpu_plan_launch_count); launches recorded into a graph under capture
+ * are not counted here but when the graph is launched (several threads may be capturing) */
+static thread_local bool t_capturing = false;
+static inline void count_launches(mfgpu_plan *pl, int n = 1)
+{
+	if (!t_capturing)
+		pl->launches += n;
+}
+
 /* ---- launches ------------------------------------------------------------------ */
 
 static mf::ChainSide side_L(const mfgpu_plan *, const mf_shard *s, int c, int begin, int end)
@@ -435,7 +445,7 @@ static int launch_fused(mfgpu_plan *pl, mf_shard *s, int c, cudaStream_t st)
 		const unsigned blocks = (unsigned)std::min((s->n_units + w - 1) / w, n_sm * per_sm);
 		dot_units_kernel(w, s->pair_nt)<<<blocks, 32 * w, s->pair_smem, st>>>(s->la, s->d_units, s->n_units, s->L[c], s->R[c]);
 		CK(cudaGetLastError());
-		pl->launches++;
+		count_launches(pl);
 	}
 	if (s->k1_blocks <= 0)
 		return MFGPU_OK;
@@ -461,7 +471,7 @@ static int launch_fused(mfgpu_plan *pl, mf_shard *s, int c, cudaStream_t st)
 		mf::k_update_L<1, 1, 2><<<s->k1_blocks, 32, s->k1_smem, st>>>(s->la, s->L[c], s->L[1 - c], s->R[c]);
 #undef MF_RES
 	CK(cudaGetLastError());
-	pl->launches++;
+	count_launches(pl);
 	return MFGPU_OK;
 }
 
@@ -474,7 +484,7 @@ static int launch_dot(mfgpu_plan *pl, mf_shard *s, int c, cudaStream_t st)
 	else
 		mf::k_dot<8, 2><<<s->dot_blocks, 256, s->k1_smem, st>>>(s->la, s->L[c], s->R[c]);
 	CK(cudaGetLastError());
-	pl->launches++;
+	count_launches(pl);
 	return MFGPU_OK;
 }
 
@@ -511,7 +521,7 @@ static int launch_acc(mfgpu_plan *pl, mf_shard *s, int c, double *rout, cudaStre
 	default: launch_acc_gw<8>(A, B, ub, ut, a.F, a.ld, s->d_ticket, n_sm, st); break;
 	}
 	CK(cudaGetLastError());
-	pl->launches++;
+	count_launches(pl);
 	return MFGPU_OK;
 }
 
@@ -542,7 +552,7 @@ static int launch_chain(mfgpu_plan *pl, mf_shard *s, int c, double *rout, bool d
 	else
 		mf::k_chain<8, mf::CHAIN_BULK_REGS><<<(unsigned)blocks, 256, 0, st>>>(A, B, wa, a.F, a.ld);
 	CK(cudaGetLastError());
-	pl->launches++;
+	count_launches(pl);
 	return MFGPU_OK;
 }
 
@@ -590,7 +600,7 @@ static int enqueue_xchg(mfgpu_plan *pl, mf_shard *s, int c, int b)
 	mf::k_apply_R_xchg<<<(unsigned)((total + 255) / 256), 256, 0, s->st>>>(
 	    pl->n_touched, pl->F, pl->ld, s->d_touched_item, s->R[c], pg, ps, b, s->d_sync, s->R[1 - c], pl->comm_timeout_ns);
 	CK(cudaGetLastError());
-	pl->launches += 2;
+	count_launches(pl, 2);
 	return MFGPU_OK;
 }
 
@@ -614,7 +624,7 @@ static int enqueue_push(mfgpu_plan *pl, mf_shard *s, int c)
 	mf::k_reduce_bcast<<<(unsigned)std::max(1L, (pairs + 255) / 256), 256, 0, s->st>>>(
 	    pp, per, cnt, pl->ld, s->d_touched_item + lo, s->R[c], s->G[0], s->d_sync);
 	CK(cudaGetLastError());
-	pl->launches += 2;
+	count_launches(pl, 2);
 	return MFGPU_OK;
 }
 
@@ -653,7 +663,7 @@ static int enqueue_ll(mfgpu_plan *pl, mf_shard *s, int c)
 	CK(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, s->dev));
 	mf::k_xchg_ll<<<(unsigned)std::max(1L, std::min((work + 255) / 256, (long)n_sm * 4)), 256, 0, s->st>>>(a);
 	CK(cudaGetLastError());
-	pl->launches++;
+	count_launches(pl);
 	return MFGPU_OK;
 }
 
@@ -682,7 +692,7 @@ static int enqueue_iteration(mfgpu_plan *pl, mf_shard *s, int c)
 	                                                                 s->d_touched_item, s->R[c], s->G[1],
 	                                                                 s->R[1 - c]);
 	CK(cudaGetLastError());
-	pl->launches++;
+	count_launches(pl);
 	return MFGPU_OK;
 }
 
@@ -716,7 +726,7 @@ static int enqueue_iteration_peer(mfgpu_plan *pl, int c)
 		mf::k_apply_R_peer<<<(unsigned)((total + 255) / 256), 256, 0, s->st>>>(
 		    pl->n_touched, pl->F, pl->ld, s->d_touched_item, s->R[c], pg, s->R[1 - c]);
 		CK(cudaGetLastError());
-		pl->launches++;
+		count_launches(pl);
 	}
 	return MFGPU_OK;
 }
@@ -725,13 +735,13 @@ static int enqueue_iteration_peer(mfgpu_plan *pl, int c)
 static int build_graph(mfgpu_plan *pl, mf_shard *s, int c, int n)
 {
 	cudaGraph_t graph = nullptr;
-	const long long before = pl->launches;
 	CK(cudaStreamBeginCapture(s->st, cudaStreamCaptureModeThreadLocal));
 	int rc = MFGPU_OK;
+	t_capturing = true;          /* captured, not launched */
 	for (int it = 0; it < n && rc == MFGPU_OK; it++)
 		rc = enqueue_iteration(pl, s, (c + it) & 1);
+	t_capturing = false;
 	cudaError_t e = cudaStreamEndCapture(s->st, &graph);
-	pl->launches = before;       /* captured, not launched */
 	if (rc != MFGPU_OK) {
 		if (graph) cudaGraphDestroy(graph);
 		return rc;
@@ -779,17 +789,45 @@ extern "C" int mfgpu_plan_iterate(mfgpu_plan *pl, int iters)
 		 * shards are built before any of them is launched: a shard's exchange waits for its peers,
 		 * which must not be held up by a graph instantiation on the host. */
 		int left = iters;
-		const int gi = pl->opt_graph_iters;
+		/* iterations per graph: the option's (16) -- or, for the first graph of a plan, the even
+		 * length between that and twice that which leaves the fewest iterations of this call to be
+		 * enqueued one by one (100 iterations: 5 graphs of 20 instead of 6 of 16 + 4 single) */
+		int gi = pl->graph_len ? pl->graph_len : pl->opt_graph_iters;
+		if (!pl->graph_len && pl->opt_graph && iters >= gi) {
+			int best = gi;
+			for (int g = gi; g <= 2 * pl->opt_graph_iters && g <= iters; g += 2)
+				if (iters % g < iters % best || (iters % g == iters % best && g > best))
+					best = g;
+			gi = best;
+		}
 		if (pl->opt_graph && left >= gi) {
+			pl->graph_len = gi;
+			/* one host thread per shard that still lacks its graph: capture and instantiation
+			 * take ~0.3 ms each, and the program that runs once (the CLI) pays them inside its loop */
+			TraceClock tc;
+			int rcs[MF_MAX_SHARDS] = {0};
+			char msgs[MF_MAX_SHARDS][256];
+			std::vector<std::thread> th;
 			for (int g = 0; g < nl; g++) {
 				mf_shard *s = &pl->sh[g];
 				if (s->gexec[c])
 					continue;
-				CK(cudaSetDevice(s->dev));
-				TraceClock tc;
-				TRY(build_graph(pl, s, c, gi));
-				tc.lap("iterate: graph build");
+				auto work = [pl, s, c, gi, g, &rcs, &msgs]() {
+					rcs[g] = cudaSetDevice(s->dev) == cudaSuccess ? build_graph(pl, s, c, gi)
+					                                              : mf_fail(MFGPU_ECUDA, "cudaSetDevice failed");
+					snprintf(msgs[g], sizeof msgs[g], "%s", rcs[g] ? mfgpu_last_error() : "");
+				};
+				if (nl > 1)
+					th.emplace_back(work);
+				else
+					work();
 			}
+			for (auto &t : th)
+				t.join();
+			for (int g = 0; g < nl; g++)
+				if (rcs[g] != MFGPU_OK)
+					return mf_fail(rcs[g], "%s", msgs[g]);
+			tc.lap("iterate: graph build");
 			for (; left >= gi; left -= gi)
 				for (int g = 0; g < nl; g++) {
 					mf_shard *s = &pl->sh[g];
@@ -1019,7 +1057,7 @@ static int recommend_by_items(mfgpu_plan *pl, int *best)
 		CK(cudaGetLastError());
 		mf::k_argmax_block<<<(U + 255) / 256, 256, 0, s->st>>>(a, s->am_out_v, s->am_out_j);
 		CK(cudaGetLastError());
-		pl->launches += 2;
+		count_launches(pl, 2);
 		CK(cudaMemcpyAsync(hv.data() + (size_t)g * U, s->am_out_v, (size_t)U * sizeof(double), cudaMemcpyDeviceToHost, s->st));
 		CK(cudaMemcpyAsync(hj.data() + (size_t)g * U, s->am_out_j, (size_t)U * sizeof(int), cudaMemcpyDeviceToHost, s->st));
 		CK(cudaMemcpyAsync(hn.data() + (size_t)g * U, s->am_nan, (size_t)U * sizeof(int), cudaMemcpyDeviceToHost, s->st));
@@ -1100,7 +1138,7 @@ extern "C" int mfgpu_plan_recommend(mfgpu_plan *pl, int *best)
 				CK(cudaGetLastError());
 				mf::k_argmax_final<<<(cnt + 255) / 256, 256, 0, s->st>>>(a, s->d_best + off);
 				CK(cudaGetLastError());
-				pl->launches += 2;
+				count_launches(pl, 2);
 			}
 			CK(cudaMemcpyAsync(best + s->user_lo, s->d_best, (size_t)nu * sizeof(int),
 			                   cudaMemcpyDeviceToHost, s->st));

@@ -363,6 +363,7 @@ int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
 			cudaGraphExecDestroy(s->gexec[g]);
 			s->gexec[g] = nullptr;
 		}
+	pl->graph_len = 0;               /* the next graph may choose its length again */
 	return MFGPU_OK;
 }
 
