@@ -343,12 +343,11 @@ int mf_pattern_build_scan(mf_pattern *p, int users, int items, int nnz,
 		if (i >= user_lo && i < user_hi) {
 			const int *m = p->mask_col + p->mask_ptr[i];
 			int cnt = p->mask_ptr[i + 1] - p->mask_ptr[i];
-			/* first j with m[j] != j (m ascending, distinct) */
-			int a = 0, b = cnt;
-			while (a < b) {
-				int mid = a + (b - a) / 2;
-				if (m[mid] == mid) a = mid + 1; else b = mid;
-			}
+			/* first j with m[j] != j (m ascending, distinct): almost always j = 0 or 1, so a
+			 * forward scan beats a bisection (one predictable branch, one cache line) */
+			int a = 0;
+			while (a < cnt && m[a] == a)
+				a++;
 			f = (a < items) ? a : -1;
 		}
 		p->first_free[i] = f;
