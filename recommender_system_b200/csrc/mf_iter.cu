@@ -441,7 +441,7 @@ static int launch_fused(mfgpu_plan *pl, mf_shard *s, int c, cudaStream_t st)
 		int n_sm = 148;
 		CK(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, s->dev));
 		const int w = s->pair_warps;
-		const int per_sm = std::max(1, std::min(16 / w, (int)(227 * 1024 / (s->pair_smem + 1024))));
+		const int per_sm = std::max(1, std::min((w == 4 ? 4 * MF_DOT_MINB : 16) / w, (int)(227 * 1024 / (s->pair_smem + 1024))));
 		const unsigned blocks = (unsigned)std::min((s->n_units + w - 1) / w, n_sm * per_sm);
 		dot_units_kernel(w, s->pair_nt)<<<blocks, 32 * w, s->pair_smem, st>>>(s->la, s->d_units, s->n_units, s->L[c], s->R[c]);
 		CK(cudaGetLastError());

@@ -574,30 +574,36 @@ __device__ __forceinline__ double acc_chain(double a, const double (&x)[ACC_SB],
  * of the tile being added, across unit boundaries; the next unit's items, ratings and positions
  * are loaded one unit ahead and its descriptor two units ahead, so no dependent global load is
  * ever waited for.  Lane = nonzero walks k sequentially against the L row of its own user
- * (both L rows of a unit travel with its first tile, two buffers by unit parity).
+ * (whose 16 features of the tile travel in the tile itself).
  * Writes e_n at its by-user and by-item positions; k_acc does the accumulations.
  * units: 8 ints per unit {ia, basea, la, ib, baseb, lb, -, -} (local user, first by-user
  * position, length of the two parts).  Needs NT - 1 <= ceil(F / 16) (the host sees to it).
- * Dynamic shared memory per warp: NT tiles [32][TS], L rows [2][2][ld], unit data [2][32] x
- * (rating, position, by-item position), [2][2] lengths.
+ * Dynamic shared memory per warp: NT tiles [34][TS] (the R rows and, as rows 32 and 33, the same 16
+ * features of the two L rows: no L buffer of its own, 10.8 KB per warp at NT = 2), unit data
+ * [2][32] x (rating, position, by-item position), [2][2] lengths.
  */
+constexpr int DOT_ROWS = 34;   /* rows of a tile: the <= 32 gathered R rows, then the L rows of user A and user B */
+
 __host__ __device__ constexpr size_t dot_units_doubles(int NT, int ld)
 {
-	return (size_t)NT * 32 * TS + 4 * (size_t)ld + 64 + 64 + 2;
+	(void)ld;
+	return (size_t)NT * DOT_ROWS * TS + 64 + 64 + 2;
 }
 
+#ifndef MF_DOT_MINB
+#define MF_DOT_MINB 4
+#endif
 template <int WARPS, int NT>
-__global__ void __launch_bounds__(WARPS * 32, 512 / (WARPS * 32))
+__global__ void __launch_bounds__(WARPS * 32, WARPS == 4 ? MF_DOT_MINB : 512 / (WARPS * 32))
 k_dot_units(const LoopArgs p, const int *__restrict__ units, int n_units,
             const double *__restrict__ Lold, const double *__restrict__ Rold)
 {
 	extern __shared__ __align__(16) double smem[];
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 	const int F = p.F, ld = p.ld;
-	constexpr int td = 32 * TS;
+	constexpr int td = DOT_ROWS * TS;
 	double *tiles = smem + dot_units_doubles(NT, ld) * warp;
-	double *Ls = tiles + (size_t)NT * td;          /* [parity][A, B][ld] */
-	double *m_a = Ls + 4 * (size_t)ld;             /* [parity][32] */
+	double *m_a = tiles + (size_t)NT * td;         /* [parity][32] */
 	int *m_pos = (int *)(m_a + 64);                /* [parity][32] */
 	int *m_ep = m_pos + 64;                        /* [parity][32] */
 	int *m_len = m_ep + 64;                        /* [parity]{cnt, la} */
@@ -633,6 +639,8 @@ k_dot_units(const LoopArgs p, const int *__restrict__ units, int n_units,
 	/* Gathers of the unit being issued: lane l moves the 16-byte piece pc = l & 7 of the tile
 	 * rows u*4 + (l >> 3), u < 8 -- one cp.async each per tile, destinations 4 tile rows apart. */
 	const double *gsrc[8];
+	const double *lsrc = Lold;  /* lanes 0..7: pieces of the L row of user A, lanes 8..15: of user B */
+	bool l_ok = false;
 	int gn = 0;                 /* pieces of this lane: u < gn */
 	const int pc2 = 2 * (lane & 7);
 	const uint32_t gdst = smem_u32(tiles) + (uint32_t)(((lane >> 3) * TS + pc2) * 8);
@@ -658,13 +666,9 @@ k_dot_units(const LoopArgs p, const int *__restrict__ units, int n_units,
 				m_len[par * 2] = cnt;
 				m_len[par * 2 + 1] = dI.la;
 			}
-			const double *LrowA = Lold + (size_t)dI.ia * ld, *LrowB = Lold + (size_t)dI.ib * ld;
-			double *LsA = Ls + (size_t)par * 2 * ld, *LsB = LsA + ld;
-			for (int q = lane; q < (ld >> 1); q += 32) {
-				cp_async16(LsA + 2 * q, LrowA + 2 * q);
-				if (dI.lb)
-					cp_async16(LsB + 2 * q, LrowB + 2 * q);
-			}
+			/* the 16 features of the two L rows travel in every tile, as its rows 32 and 33 */
+			lsrc = Lold + (size_t)(lane < 8 ? dI.ia : dI.ib) * ld + pc2;
+			l_ok = lane < 8 || (lane < 16 && dI.lb > 0);
 			/* the loads of the units behind it start now and have a whole unit to land */
 			if (ti + 1 < n_mine)
 				load_lane(dN, xN);
@@ -681,6 +685,7 @@ k_dot_units(const LoopArgs p, const int *__restrict__ units, int n_units,
 #pragma unroll
 			for (int u = 0; u < 8; u++)
 				cp_async16_if(dst + (uint32_t)(u * 4 * TS * 8), gsrc[u] + k0, lane_ok && u < gn);
+			cp_async16_if(dst + (uint32_t)(8 * 4 * TS * 8), lsrc + k0, lane_ok && l_ok);
 		}
 		if (++ki == nt) {
 			ki = 0;
@@ -700,7 +705,7 @@ k_dot_units(const LoopArgs p, const int *__restrict__ units, int n_units,
 	int gc = 0;                 /* ring slot of the tile being added */
 	int kc = 0, par = 0, cnt = 0;
 	double s = 0.0, a = 0.0;
-	const double *Lrow = Ls;
+	int lrow = 32 * TS;         /* offset of this lane's L row in a tile */
 	for (long g = 0; g < total; g++) {
 		if (g + NT - 1 < total) {
 			issue(gi);
@@ -713,11 +718,11 @@ k_dot_units(const LoopArgs p, const int *__restrict__ units, int n_units,
 			cnt = m_len[par * 2];
 			const int la = m_len[par * 2 + 1];
 			a = m_a[par * 32 + lane];
-			Lrow = Ls + (size_t)par * 2 * ld + (lane < la ? 0 : ld);
+			lrow = (lane < la ? 32 : 33) * TS;
 			s = 0.0;
 		}
 		if (lane < cnt)
-			s = dot_tile(s, Lrow + kc * KT, tiles + (size_t)gc * td + lane * TS, min(KT, F - kc * KT));
+			s = dot_tile(s, tiles + (size_t)gc * td + lrow, tiles + (size_t)gc * td + lane * TS, min(KT, F - kc * KT));
 		gc = gc + 1 == NT ? 0 : gc + 1;
 		if (++kc == nt) {
 			if (lane < cnt) {

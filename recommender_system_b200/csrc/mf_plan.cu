@@ -103,14 +103,51 @@ void ws_release(void *p, size_t bytes)
 }
 } // namespace
 
-/* rows of `width` doubles between matrices of row strides dld / sld doubles */
-static int copy_rows(double *dst, size_t dld, const double *src, size_t sld, size_t width, size_t rows,
-                     cudaMemcpyKind kind, cudaStream_t st)
+/* rows of `width` doubles from a matrix of row stride sld to one of row stride dld (device) */
+__global__ void __launch_bounds__(256)
+k_pack_rows(double *__restrict__ dst, size_t dld, const double *__restrict__ src, size_t sld, size_t width, size_t total)
 {
-	if (dld == width && sld == width)
-		CK(cudaMemcpyAsync(dst, src, rows * width * sizeof(double), kind, st));
-	else
-		CK(cudaMemcpy2DAsync(dst, dld * 8, src, sld * 8, width * 8, rows, kind, st));
+	for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (size_t)gridDim.x * blockDim.x) {
+		const size_t r = t / width, k = t - r * width;
+		dst[r * dld + k] = src[r * sld + k];
+	}
+}
+
+static int pack_rows(double *dst, size_t dld, const double *src, size_t sld, size_t width, size_t rows, cudaStream_t st)
+{
+	const size_t total = width * rows;
+	if (!total)
+		return MFGPU_OK;
+	k_pack_rows<<<(unsigned)std::min<size_t>((total + 255) / 256, 148 * 32), 256, 0, st>>>(dst, dld, src, sld, width, total);
+	CK(cudaGetLastError());
+	return MFGPU_OK;
+}
+
+/* Host rows of F doubles -> device rows of stride ld, through `scratch` (a device buffer of the
+ * same size, whose content is dead): one contiguous copy + a kernel instead of a strided copy
+ * (cudaMemcpy2DAsync of 1600-byte rows runs at a third of the contiguous rate). */
+static int upload_rows(double *dst, double *scratch, size_t ld, const double *host, size_t F, size_t rows, cudaStream_t st)
+{
+	if (ld == F) {
+		CK(cudaMemcpyAsync(dst, host, rows * F * sizeof(double), cudaMemcpyHostToDevice, st));
+		return MFGPU_OK;
+	}
+	CK(cudaMemcpyAsync(scratch, host, rows * F * sizeof(double), cudaMemcpyHostToDevice, st));
+	return pack_rows(dst, ld, scratch, F, F, rows, st);
+}
+
+/* ... and back: packed into `scratch`, one contiguous copy to the host, and `scratch` restored as
+ * a copy of `src` (it is the other buffer of the pair: rows that are never rewritten must be
+ * equal in both, and any valid content will do for the rest). */
+static int download_rows(double *host, const double *src, double *scratch, size_t ld, size_t F, size_t rows, cudaStream_t st)
+{
+	if (ld == F) {
+		CK(cudaMemcpyAsync(host, src, rows * F * sizeof(double), cudaMemcpyDeviceToHost, st));
+		return MFGPU_OK;
+	}
+	TRY(pack_rows(scratch, F, src, ld, F, rows, st));
+	CK(cudaMemcpyAsync(host, scratch, rows * F * sizeof(double), cudaMemcpyDeviceToHost, st));
+	CK(cudaMemcpyAsync(scratch, src, rows * ld * sizeof(double), cudaMemcpyDeviceToDevice, st));
 	return MFGPU_OK;
 }
 
@@ -189,7 +226,7 @@ int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
 	int pair_warps = pl->opt_pair_warps;
 	if (pair_warps != 4 && pair_warps != 5 && pair_warps != 6 && pair_warps != 8)
 		pair_warps = 8;
-	auto pair_bytes = [&](int nt) { return pair_warps * ((size_t)nt * 32 * TS + 4 * (size_t)pl->ld + 130) * sizeof(double); };   /* mf::dot_units_doubles */
+	auto pair_bytes = [&](int nt) { return pair_warps * ((size_t)nt * 34 * TS + 130) * sizeof(double); };   /* mf::dot_units_doubles */
 	/* default: where it was measured ahead (inst60000 shape: 377 against 388..400 us per iteration;
 	 * behind on the MovieLens shapes and on one eighth of inst60000): wide factors, a big shard */
 	const int want_split = pl->opt_pair >= 0 ? pl->opt_pair : (F >= 128 && pt.nnz >= 400000);
@@ -823,6 +860,18 @@ static int plan_create(mfgpu_plan **out, int users, int items, int features, int
 	pl->items = items;
 	pl->F = features;
 	pl->ld = std::max(2, (features + 1) & ~1);
+	{
+		/* Rows on whole 128-byte lines when that costs at most 1/16 more bytes (F = 200 -> 208,
+		 * 1000 -> 1008; not 100 -> 112): a 16-feature tile of a gathered row is then one line
+		 * instead of the halves of two (ncu: the dot kernel pulled 2.2 GB through L2 -> SM for the
+		 * 1.45 GB it needed; 169 -> 154 us per iteration on the inst60000 shape).  The host copies
+		 * stay contiguous: rows are packed / padded by a kernel on the device (pack_rows). */
+		const char *env = getenv("MFGPU_LD_ALIGN");      /* 0 / 1: never; default 16 doubles */
+		const int al = env ? atoi(env) : 16;
+		const int padded = al > 1 ? (features + al - 1) / al * al : pl->ld;
+		if (features >= 64 && padded - features <= features / 16)
+			pl->ld = padded;
+	}
 	pl->nnz = nnz;
 	pl->alpha = alpha;
 	pl->nshards = nshards;
@@ -983,9 +1032,9 @@ extern "C" int mfgpu_plan_set_factors(mfgpu_plan *pl, const double *L, const dou
 		CK(cudaSetDevice(s->dev));
 		const size_t nu = (size_t)(s->user_hi - s->user_lo);
 		if (F && nu)
-			TRY(copy_rows(s->L[0], ld, L + (size_t)s->user_lo * F, F, F, nu, cudaMemcpyHostToDevice, s->st));
+			TRY(upload_rows(s->L[0], s->L[1], ld, L + (size_t)s->user_lo * F, F, nu, s->st));
 		if (F && pl->items)
-			TRY(copy_rows(s->R[0], ld, R, F, F, (size_t)pl->items, cudaMemcpyHostToDevice, s->st));
+			TRY(upload_rows(s->R[0], s->R[1], ld, R, F, (size_t)pl->items, s->st));
 		/* rows without a nonzero are never rewritten, so both buffers start equal */
 		CK(cudaMemcpyAsync(s->L[1], s->L[0], nu * ld * 8, cudaMemcpyDeviceToDevice, s->st));
 		CK(cudaMemcpyAsync(s->R[1], s->R[0], (size_t)pl->items * ld * 8, cudaMemcpyDeviceToDevice, s->st));
@@ -1132,9 +1181,9 @@ static int enqueue_get_factors(mfgpu_plan *pl, double *L, double *R, bool side)
 		}
 		const size_t nu = (size_t)(s->user_hi - s->user_lo);
 		if (L && F && nu)
-			TRY(copy_rows(L + (size_t)s->user_lo * F, F, s->L[c], ld, F, nu, cudaMemcpyDeviceToHost, st));
+			TRY(download_rows(L + (size_t)s->user_lo * F, s->L[c], s->L[1 - c], ld, F, nu, st));
 		if (R && g == 0 && F && pl->items)
-			TRY(copy_rows(R, F, s->R[c], ld, F, (size_t)pl->items, cudaMemcpyDeviceToHost, st));
+			TRY(download_rows(R, s->R[c], s->R[1 - c], ld, F, (size_t)pl->items, st));
 	}
 	return MFGPU_OK;
 }
