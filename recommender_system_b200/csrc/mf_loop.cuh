@@ -578,8 +578,8 @@ __device__ __forceinline__ double acc_chain(double a, const double (&x)[ACC_SB],
  * Writes e_n at its by-user and by-item positions; k_acc does the accumulations.
  * units: 8 ints per unit {ia, basea, la, ib, baseb, lb, -, -} (local user, first by-user
  * position, length of the two parts).  Needs NT - 1 <= ceil(F / 16) (the host sees to it).
- * Dynamic shared memory per warp: NT tiles [34][TS] (the R rows and, as rows 32 and 33, the same 16
- * features of the two L rows: no L buffer of its own, 10.8 KB per warp at NT = 2), unit data
+ * Dynamic shared memory per warp: NT tiles [34][16] (the R rows and, as rows 32 and 33, the same 16
+ * features of the two L rows: no L buffer of its own, 9.9 KB per warp at NT = 2), unit data
  * [2][32] x (rating, position, by-item position), [2][2] lengths.
  */
 constexpr int DOT_ROWS = 34;   /* rows of a tile: the <= 32 gathered R rows, then the L rows of user A and user B */
@@ -587,7 +587,33 @@ constexpr int DOT_ROWS = 34;   /* rows of a tile: the <= 32 gathered R rows, the
 __host__ __device__ constexpr size_t dot_units_doubles(int NT, int ld)
 {
 	(void)ld;
-	return (size_t)NT * DOT_ROWS * TS + 64 + 64 + 2;
+	return (size_t)NT * DOT_ROWS * KT + 144;       /* 144: the unit data, rounded to whole 128-byte lines */
+}
+
+/* Tile rows of k_dot_units are 128 bytes (16 features) on 128-byte boundaries, the 16-byte piece p
+ * of row r stored at position p ^ (r & 7).  Why not the padded rows of the older kernels (TS = 18):
+ * a cp.async whose 8 lanes' destination straddles two 128-byte lines of shared memory is split in
+ * two, and each half fetches its sectors of the SOURCE line on its own -- ncu counted 6 sectors
+ * per gathered 128-byte segment instead of 4 (77 M sectors per launch for the 50 M needed, the
+ * L2 at 73 % of its sector throughput).  With aligned rows a segment is one request of four
+ * sectors, and the swizzle keeps the transposed read (lane = row, all lanes the same p) free of
+ * bank conflicts: eight consecutive rows hit eight different 16-byte bank groups. */
+__device__ __forceinline__ double dot_tile_swz(double s, const double *l, int lsw, const double *r, int rsw, int kc)
+{
+	if (kc == KT) {
+#pragma unroll
+		for (int p = 0; p < KT / 2; p++) {
+			const double2 a = ld2(l + 2 * (p ^ lsw)), b = ld2(r + 2 * (p ^ rsw));
+			s = __dadd_rn(s, __dmul_rn(a.x, b.x));
+			s = __dadd_rn(s, __dmul_rn(a.y, b.y));
+		}
+	} else {
+		for (int k = 0; k < kc; k++) {
+			const int p = k >> 1, h = k & 1;
+			s = __dadd_rn(s, __dmul_rn(l[2 * (p ^ lsw) + h], r[2 * (p ^ rsw) + h]));
+		}
+	}
+	return s;
 }
 
 #ifndef MF_DOT_MINB
@@ -601,8 +627,9 @@ k_dot_units(const LoopArgs p, const int *__restrict__ units, int n_units,
 	extern __shared__ __align__(16) double smem[];
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 	const int F = p.F, ld = p.ld;
-	constexpr int td = DOT_ROWS * TS;
-	double *tiles = smem + dot_units_doubles(NT, ld) * warp;
+	constexpr int td = DOT_ROWS * KT;
+	/* tile rows on 128-byte lines of shared memory (the launch adds 128 bytes of slack) */
+	double *tiles = smem + ((128u - (smem_u32(smem) & 127u)) & 127u) / 8 + dot_units_doubles(NT, ld) * warp;
 	double *m_a = tiles + (size_t)NT * td;         /* [parity][32] */
 	int *m_pos = (int *)(m_a + 64);                /* [parity][32] */
 	int *m_ep = m_pos + 64;                        /* [parity][32] */
@@ -643,7 +670,9 @@ k_dot_units(const LoopArgs p, const int *__restrict__ units, int n_units,
 	bool l_ok = false;
 	int gn = 0;                 /* pieces of this lane: u < gn */
 	const int pc2 = 2 * (lane & 7);
-	const uint32_t gdst = smem_u32(tiles) + (uint32_t)(((lane >> 3) * TS + pc2) * 8);
+	/* destination of this lane's piece in tile rows u*4 + (lane >> 3): row & 7 = (u & 1)*4 + (lane >> 3) */
+	const uint32_t gdst_e = smem_u32(tiles) + (uint32_t)((lane >> 3) * 128 + (((lane & 7) ^ (lane >> 3)) << 4));
+	const uint32_t gdst_o = smem_u32(tiles) + (uint32_t)((lane >> 3) * 128 + (((lane & 7) ^ (4 + (lane >> 3))) << 4));
 	int ti = 0, ki = 0;         /* issue side: my ti-th unit, its tile ki */
 
 	auto issue = [&](int g) {
@@ -681,11 +710,11 @@ k_dot_units(const LoopArgs p, const int *__restrict__ units, int n_units,
 		{
 			const int k0 = ki * KT;
 			const bool lane_ok = k0 + pc2 < ld;
-			const uint32_t dst = gdst + (uint32_t)g * (uint32_t)(td * 8);
+			const uint32_t tile = (uint32_t)g * (uint32_t)(td * 8);
 #pragma unroll
 			for (int u = 0; u < 8; u++)
-				cp_async16_if(dst + (uint32_t)(u * 4 * TS * 8), gsrc[u] + k0, lane_ok && u < gn);
-			cp_async16_if(dst + (uint32_t)(8 * 4 * TS * 8), lsrc + k0, lane_ok && l_ok);
+				cp_async16_if(((u & 1) ? gdst_o : gdst_e) + tile + (uint32_t)(u * 4 * 128), gsrc[u] + k0, lane_ok && u < gn);
+			cp_async16_if(gdst_e + tile + (uint32_t)(8 * 4 * 128), lsrc + k0, lane_ok && l_ok);
 		}
 		if (++ki == nt) {
 			ki = 0;
@@ -705,7 +734,7 @@ k_dot_units(const LoopArgs p, const int *__restrict__ units, int n_units,
 	int gc = 0;                 /* ring slot of the tile being added */
 	int kc = 0, par = 0, cnt = 0;
 	double s = 0.0, a = 0.0;
-	int lrow = 32 * TS;         /* offset of this lane's L row in a tile */
+	int lrow = 32;              /* tile row of this lane's L row */
 	for (long g = 0; g < total; g++) {
 		if (g + NT - 1 < total) {
 			issue(gi);
@@ -718,11 +747,12 @@ k_dot_units(const LoopArgs p, const int *__restrict__ units, int n_units,
 			cnt = m_len[par * 2];
 			const int la = m_len[par * 2 + 1];
 			a = m_a[par * 32 + lane];
-			lrow = (lane < la ? 32 : 33) * TS;
+			lrow = lane < la ? 32 : 33;
 			s = 0.0;
 		}
 		if (lane < cnt)
-			s = dot_tile(s, tiles + (size_t)gc * td + lrow, tiles + (size_t)gc * td + lane * TS, min(KT, F - kc * KT));
+			s = dot_tile_swz(s, tiles + (size_t)gc * td + lrow * KT, lrow & 7, tiles + (size_t)gc * td + lane * KT, lane & 7,
+			                 min(KT, F - kc * KT));
 		gc = gc + 1 == NT ? 0 : gc + 1;
 		if (++kc == nt) {
 			if (lane < cnt) {

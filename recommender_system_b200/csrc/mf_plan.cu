@@ -226,7 +226,7 @@ int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
 	int pair_warps = pl->opt_pair_warps;
 	if (pair_warps != 4 && pair_warps != 5 && pair_warps != 6 && pair_warps != 8)
 		pair_warps = 8;
-	auto pair_bytes = [&](int nt) { return pair_warps * ((size_t)nt * 34 * TS + 130) * sizeof(double); };   /* mf::dot_units_doubles */
+	auto pair_bytes = [&](int nt) { return pair_warps * ((size_t)nt * 34 * 16 + 144) * sizeof(double) + 128; };   /* mf::dot_units_doubles + alignment slack */
 	/* default: where it was measured ahead (inst60000 shape: 377 against 388..400 us per iteration;
 	 * behind on the MovieLens shapes and on one eighth of inst60000): wide factors, a big shard */
 	const int want_split = pl->opt_pair >= 0 ? pl->opt_pair : (F >= 128 && pt.nnz >= 400000);

@@ -246,7 +246,7 @@ int main()
 		CK(cudaFuncSetAttribute(k_cpa128<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, WARPS * S * 4096)); \
 		float ms = time_best(run_cpa128<S>, &c); double bytes = (double)c.blocks * WARPS * iters * 4096.0; \
 		printf("cpa128 (4 rows x 128 B per instruction), %d stages, %d x %d warps/SM: %8.1f GB/s  (%.1f B/clk/SM)\n", S, PERSM, WARPS, bytes / ms / 1e6, bytes / ms / 1e6 / sms / (khz / 1e6)); } while (0)
-	CPA128(2, 8, 2); CPA128(2, 8, 1); CPA128(4, 8, 1); CPA128(4, 8, 2); CPA128(8, 8, 1); CPA128(8, 4, 1);
+	CPA128(2, 8, 2); CPA128(2, 8, 1); CPA128(4, 8, 1); CPA128(4, 8, 2);
 	LDG64(4, 64); LDG64(4, 32); LDG64(8, 16); LDG64(8, 12); LDG64(8, 24); LDG64(2, 64);
 	{
 		/* the same gathers from a 96 MB table (L of the inst60000 shape): L2 + HBM */
