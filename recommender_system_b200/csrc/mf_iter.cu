@@ -368,9 +368,9 @@ int mf_kernels_prepare(int warps, size_t k1_smem, int res_ng, size_t res_smem, s
 		CK(cudaFuncSetAttribute(mf::k_dot<8, 2>, attr, (int)k1_smem));
 		CK(cudaFuncSetAttribute(mf::k_dot<8, 4>, attr, (int)k1_smem));
 		CK(cudaFuncSetAttribute(mf::k_chain<8, mf::CHAIN_DEEP_RING>, attr,
-		                        8 * mf::ring_doubles(mf::RING_DEEP_ROWS, mf::RING_DEEP_STAGES) * (int)sizeof(double)));
+		                        8 * mf::ring_doubles(mf::RING_DEEP_ROWS, mf::RING_DEEP_STAGES) * (int)sizeof(double) + 128));
 		CK(cudaFuncSetAttribute(mf::k_chain<8, mf::CHAIN_BULK_RING>, attr,
-		                        8 * mf::ring_doubles(mf::RING_BULK_ROWS, mf::RING_BULK_STAGES) * (int)sizeof(double)));
+		                        8 * mf::ring_doubles(mf::RING_BULK_ROWS, mf::RING_BULK_STAGES) * (int)sizeof(double) + 128));
 	} else {
 		CK(cudaFuncSetAttribute(mf::k_update_L<1, 1, 2>, attr, (int)k1_smem));
 	}
@@ -538,8 +538,8 @@ static int launch_chain(mfgpu_plan *pl, mf_shard *s, int c, double *rout, bool d
 	const long blocks = (wa + wb + 7) / 8;
 	if (blocks <= 0)
 		return MFGPU_OK;
-	const size_t ring_deep = (size_t)8 * mf::ring_doubles(mf::RING_DEEP_ROWS, mf::RING_DEEP_STAGES) * sizeof(double);
-	const size_t ring_bulk = (size_t)8 * mf::ring_doubles(mf::RING_BULK_ROWS, mf::RING_BULK_STAGES) * sizeof(double);
+	const size_t ring_deep = (size_t)8 * mf::ring_doubles(mf::RING_DEEP_ROWS, mf::RING_DEEP_STAGES) * sizeof(double) + 128;
+	const size_t ring_bulk = (size_t)8 * mf::ring_doubles(mf::RING_BULK_ROWS, mf::RING_BULK_STAGES) * sizeof(double) + 128;
 	const bool ring = pl->opt_chain_ring != 0;
 	if (deep && pl->opt_chain_ws)
 		mf::k_chain_ws<<<(unsigned)(wa + wb), mf::WS_THREADS, mf::WS_SMEM, st>>>(A, B, wa, a.F, a.ld);

@@ -52,6 +52,12 @@ __device__ __forceinline__ double2 ld2(const double *p)
 	return *reinterpret_cast<const double2 *>(p);
 }
 
+/* first 128-byte boundary of the dynamic shared memory (the launches add 128 bytes of slack) */
+__device__ __forceinline__ double *smem_lines(double *smem)
+{
+	return smem + ((128u - (smem_u32(smem) & 127u)) & 127u) / 8;
+}
+
 constexpr int KT = 16;        /* features per staged tile of the dot phase          */
 constexpr int TS = KT + 2;    /* tile row stride in doubles: TS/2 odd, so the 16-byte reads
                                  of 8 lanes (8 rows) fall in 8 distinct bank groups   */
@@ -78,7 +84,7 @@ __device__ __forceinline__ void stage_plan(StagePlan &sp, const double *__restri
 		const int row = min(p >> 3, cnt - 1), pc = p & 7;
 		const int jn = __shfl_sync(FULL, j, row);
 		sp.src[u] = src + (size_t)jn * ld + 2 * pc;
-		sp.dst[u] = row * TS + 2 * pc;
+		sp.dst[u] = row * KT + 2 * (pc ^ (row & 7));
 		sp.kofs[u] = 2 * pc;
 		if (p < pieces)
 			sp.n = u + 1;
@@ -91,6 +97,32 @@ __device__ __forceinline__ void stage_tile(double *dst, const StagePlan &sp, int
 	for (int u = 0; u < 8; u++)
 		if (u < sp.n && k0 + sp.kofs[u] < ld)
 			cp_async16(dst + sp.dst[u], sp.src[u] + k0);
+}
+
+/* Tile rows of the dot phases are 128 bytes (16 features) on 128-byte boundaries of shared memory,
+ * the 16-byte piece p of row r stored at position p ^ (r & 7).  Why not padded rows (stride 18):
+ * a cp.async whose 8 lanes' destination straddles two 128-byte lines of shared memory is split in
+ * two, and each half fetches its sectors of the SOURCE line on its own -- ncu counted 6 sectors
+ * per gathered 128-byte segment instead of 4 (77 M sectors per launch for the 50 M needed, the
+ * L2 at 73 % of its sector throughput).  With aligned rows a segment is one request of four
+ * sectors, and the swizzle keeps the transposed read (lane = row, all lanes the same p) free of
+ * bank conflicts: eight consecutive rows hit eight different 16-byte bank groups. */
+__device__ __forceinline__ double dot_tile_swz(double s, const double *l, int lsw, const double *r, int rsw, int kc)
+{
+	if (kc == KT) {
+#pragma unroll
+		for (int p = 0; p < KT / 2; p++) {
+			const double2 a = ld2(l + 2 * (p ^ lsw)), b = ld2(r + 2 * (p ^ rsw));
+			s = __dadd_rn(s, __dmul_rn(a.x, b.x));
+			s = __dadd_rn(s, __dmul_rn(a.y, b.y));
+		}
+	} else {
+		for (int k = 0; k < kc; k++) {
+			const int p = k >> 1, h = k & 1;
+			s = __dadd_rn(s, __dmul_rn(l[2 * (p ^ lsw) + h], r[2 * (p ^ rsw) + h]));
+		}
+	}
+	return s;
 }
 
 /* s = (s + l[0]*r[0]) + l[1]*r[1] + ... over one tile (mat2d.c:133-137 continued across tiles) */
@@ -312,7 +344,9 @@ __device__ __forceinline__ double chain_bulk(double acc, int lane, const int *__
  * src_g = first of the group's 32 features in row 0 of the gathered factor; gw = number of
  * valid doubles of the group in a row (even, <= 32). */
 /* doubles of one warp's ring: per stage RS gathered rows of 32 features and their RS e_n */
-__host__ __device__ constexpr int ring_doubles(int RS, int NST) { return NST * (RS * 32 + RS); }
+/* (the RS e_n of a stage take 16 doubles, so that every 256-byte row of the ring starts on a
+ * 128-byte line: a cp.async whose destination straddles two lines is split, see dot_tile_swz) */
+__host__ __device__ constexpr int ring_doubles(int RS, int NST) { return NST * (RS * 32 + 16); }
 
 template <int RS, int NST>
 __device__ __forceinline__ double chain_ring(double acc, int lane, const int *__restrict__ idx,
@@ -322,7 +356,7 @@ __device__ __forceinline__ double chain_ring(double acc, int lane, const int *__
 	constexpr int D = NST - 1;            /* stages in flight ahead of the one being added */
 	constexpr int SPB = 32 / RS;          /* stages per index block of 32 nonzeros        */
 	constexpr int NB = (SPB - 1 + D) / SPB + 2;   /* index blocks held in registers       */
-	constexpr int STAGE = RS * 32 + RS;
+	constexpr int STAGE = RS * 32 + 16;
 	int bi[NB];
 	auto load_blk = [&](int q, int &i_) { i_ = idx[min(q * 32 + lane, m - 1)]; };
 #pragma unroll
@@ -432,7 +466,7 @@ __device__ __forceinline__ double chunk_error(double *tiles, int td, const doubl
 		cp_async_wait<NT - 1>();      /* everything but the NT - 1 newest groups has landed */
 		__syncwarp();
 		if (lane < cnt)
-			s = dot_tile(s, Ls + t * KT, tiles + slot * td + lane * TS, min(KT, F - t * KT));
+			s = dot_tile_swz(s, Ls + t * KT, 0, tiles + slot * td + lane * KT, lane & 7, min(KT, F - t * KT));
 		__syncwarp();                 /* the slot may be overwritten by the next issue */
 		slot = slot + 1 == NT ? 0 : slot + 1;
 		fill = fill + 1 == NT ? 0 : fill + 1;
@@ -454,9 +488,9 @@ k_update_L(const LoopArgs p, const double *__restrict__ Lold, double *__restrict
 	extern __shared__ __align__(16) double smem[];
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 	const int F = p.F, ld = p.ld, CH = p.CH;
-	const int td = CH * TS;
-	const size_t per_warp = (size_t)NT * td + ld + 32;
-	double *tiles = smem + per_warp * warp;
+	const int td = CH * KT;
+	const size_t per_warp = ((size_t)NT * td + ld + 32 + 15) & ~(size_t)15;
+	double *tiles = smem_lines(smem) + per_warp * warp;
 	double *Ls = tiles + (size_t)NT * td;
 	double *es = Ls + ld;
 
@@ -590,31 +624,6 @@ __host__ __device__ constexpr size_t dot_units_doubles(int NT, int ld)
 	return (size_t)NT * DOT_ROWS * KT + 144;       /* 144: the unit data, rounded to whole 128-byte lines */
 }
 
-/* Tile rows of k_dot_units are 128 bytes (16 features) on 128-byte boundaries, the 16-byte piece p
- * of row r stored at position p ^ (r & 7).  Why not the padded rows of the older kernels (TS = 18):
- * a cp.async whose 8 lanes' destination straddles two 128-byte lines of shared memory is split in
- * two, and each half fetches its sectors of the SOURCE line on its own -- ncu counted 6 sectors
- * per gathered 128-byte segment instead of 4 (77 M sectors per launch for the 50 M needed, the
- * L2 at 73 % of its sector throughput).  With aligned rows a segment is one request of four
- * sectors, and the swizzle keeps the transposed read (lane = row, all lanes the same p) free of
- * bank conflicts: eight consecutive rows hit eight different 16-byte bank groups. */
-__device__ __forceinline__ double dot_tile_swz(double s, const double *l, int lsw, const double *r, int rsw, int kc)
-{
-	if (kc == KT) {
-#pragma unroll
-		for (int p = 0; p < KT / 2; p++) {
-			const double2 a = ld2(l + 2 * (p ^ lsw)), b = ld2(r + 2 * (p ^ rsw));
-			s = __dadd_rn(s, __dmul_rn(a.x, b.x));
-			s = __dadd_rn(s, __dmul_rn(a.y, b.y));
-		}
-	} else {
-		for (int k = 0; k < kc; k++) {
-			const int p = k >> 1, h = k & 1;
-			s = __dadd_rn(s, __dmul_rn(l[2 * (p ^ lsw) + h], r[2 * (p ^ rsw) + h]));
-		}
-	}
-	return s;
-}
 
 #ifndef MF_DOT_MINB
 #define MF_DOT_MINB 4
@@ -629,7 +638,7 @@ k_dot_units(const LoopArgs p, const int *__restrict__ units, int n_units,
 	const int F = p.F, ld = p.ld;
 	constexpr int td = DOT_ROWS * KT;
 	/* tile rows on 128-byte lines of shared memory (the launch adds 128 bytes of slack) */
-	double *tiles = smem + ((128u - (smem_u32(smem) & 127u)) & 127u) / 8 + dot_units_doubles(NT, ld) * warp;
+	double *tiles = smem_lines(smem) + dot_units_doubles(NT, ld) * warp;
 	double *m_a = tiles + (size_t)NT * td;         /* [parity][32] */
 	int *m_pos = (int *)(m_a + 64);                /* [parity][32] */
 	int *m_ep = m_pos + 64;                        /* [parity][32] */
@@ -1040,9 +1049,9 @@ k_dot(const LoopArgs p, const double *__restrict__ Lold, const double *__restric
 	extern __shared__ __align__(16) double smem[];
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 	const int F = p.F, ld = p.ld, CH = p.CH;
-	const int td = CH * TS;
-	const size_t per_warp = (size_t)NT * td + ld + 32;
-	double *tiles = smem + per_warp * warp;
+	const int td = CH * KT;
+	const size_t per_warp = ((size_t)NT * td + ld + 32 + 15) & ~(size_t)15;
+	double *tiles = smem_lines(smem) + per_warp * warp;
 	double *Ls = tiles + (size_t)NT * td;
 
 	const int c = (int)blockIdx.x * WARPS + warp;

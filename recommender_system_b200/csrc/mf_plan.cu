@@ -182,7 +182,6 @@ static size_t mf_g_bytes(const mfgpu_plan *pl)
 int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
 {
 	const int F = pl->F;
-	const int TS = 18;               /* mf::TS: row stride of a dot-phase tile */
 	int max_smem = 0;
 	CK(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, s->dev));
 	/* nonzeros per chunk = lanes of the dot phase: the whole row when it has <= 32 nonzeros */
@@ -198,18 +197,18 @@ int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
 	 * dot_stages / acc_rows select them for experiments. */
 	int NT = pl->opt_dot_stages > 2 ? 4 : 2;
 	s->acc_rows = pl->opt_acc_rows > 1 ? 3 : 1;
-	auto warp_doubles = [&](int ch) { return (size_t)NT * ch * TS + pl->ld + 32; };
+	auto warp_doubles = [&](int ch) { return ((size_t)NT * ch * 16 + pl->ld + 32 + 15) & ~(size_t)15; };   /* tiles of [ch][16], mf_loop.cuh */
 	int warps = 8;
-	if (8 * warp_doubles(CH) * sizeof(double) > (size_t)max_smem)
+	if (8 * warp_doubles(CH) * sizeof(double) + 128 > (size_t)max_smem)
 		NT = 2;
-	if (8 * warp_doubles(CH) * sizeof(double) > (size_t)max_smem) {
+	if (8 * warp_doubles(CH) * sizeof(double) + 128 > (size_t)max_smem) {
 		warps = 1;      /* one warp per CTA: k_update_L<1, 1, 2> */
 		s->acc_rows = 1;
 	}
-	if (warps * warp_doubles(CH) * sizeof(double) > (size_t)max_smem)
+	if (warps * warp_doubles(CH) * sizeof(double) + 128 > (size_t)max_smem)
 		return mf_fail(MFGPU_EINVAL, "features=%d does not fit shared memory (%d bytes)", F, max_smem);
 	s->warps = warps;
-	s->k1_smem = warps * warp_doubles(CH) * sizeof(double);
+	s->k1_smem = warps * warp_doubles(CH) * sizeof(double) + 128;      /* + slack to start on a 128-byte line */
 	/* Row classes.  A warp of k_update_L spends ~100 cycles per nonzero, so a row much longer
 	 * than the per-warp share of the shard (nnz / (8 warps x SMs)) would outlast the rest of
 	 * the launch: such rows have their dots spread over warps by k_dot.  Chains longer than
@@ -227,9 +226,10 @@ int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
 	if (pair_warps != 4 && pair_warps != 5 && pair_warps != 6 && pair_warps != 8)
 		pair_warps = 8;
 	auto pair_bytes = [&](int nt) { return pair_warps * ((size_t)nt * 34 * 16 + 144) * sizeof(double) + 128; };   /* mf::dot_units_doubles + alignment slack */
-	/* default: where it was measured ahead (inst60000 shape: 377 against 388..400 us per iteration;
-	 * behind on the MovieLens shapes and on one eighth of inst60000): wide factors, a big shard */
-	const int want_split = pl->opt_pair >= 0 ? pl->opt_pair : (F >= 128 && pt.nnz >= 400000);
+	/* default: where it was measured ahead of the fused kernels (us per iteration, split / fused):
+	 * inst60000 shape 316 / 401, one eighth of it 53 / 61, one eighth of the ML1M shape 52 / 59;
+	 * the whole ML1M shape 252 / 248 -- wide factors always, F >= 64 on shards below 6e5 nonzeros */
+	const int want_split = pl->opt_pair >= 0 ? pl->opt_pair : (F >= 128 || (F >= 64 && pt.nnz < 600000));
 	const bool split = warps == 8 && want_split && pair_bytes(2) <= (size_t)max_smem;
 	/* the ring of a k_dot_pair warp is what it has in flight from L2: as deep as one CTA of
 	 * eight warps per SM can hold (measured latency under load ~2000 cycles: ~100 KB in flight
