@@ -191,6 +191,7 @@ struct TraceClock {
 };
 
 int mf_kernels_prepare(int warps, size_t k1_smem, int res_ng, size_t res_smem, size_t pair_smem, int pair_warps, int pair_nt);   /* mf_iter.cu: kernels live in that TU only */
+int mf_kernels_preload(int F, int split, int nshards);      /* mf_iter.cu */
 extern mf_nccl_api g_nccl;
 
 #define CK(call)                                                                        \

@@ -340,6 +340,42 @@ static dot_units_fn dot_units_kernel(int w, int nt)
 #undef MF_ROW
 }
 
+/* k_acc<GW>: its function pointer */
+typedef void (*acc_fn)(const mf::ChainSide, const mf::ChainSide, long, long, int, int, unsigned long long *);
+static acc_fn acc_kernel(int gw)
+{
+	switch (gw) {
+	case 1: return mf::k_acc<1>;
+	case 2: return mf::k_acc<2>;
+	case 3: return mf::k_acc<3>;
+	case 4: return mf::k_acc<4>;
+	case 5: return mf::k_acc<5>;
+	case 6: return mf::k_acc<6>;
+	case 7: return mf::k_acc<7>;
+	default: return mf::k_acc<8>;
+	}
+}
+
+/* With CUDA's lazy module loading a kernel's code is loaded at its first launch (or capture):
+ * milliseconds per kernel, which a program that runs once (the CLI) would pay inside its loop.
+ * Asking for the attributes of the kernels a plan is going to use loads them at plan creation. */
+int mf_kernels_preload(int F, int split, int nshards)
+{
+	cudaFuncAttributes fa;
+	const int gw = std::min((F + 31) / 32, 8);
+	if (split)
+		CK(cudaFuncGetAttributes(&fa, acc_kernel(gw)));
+	CK(cudaFuncGetAttributes(&fa, mf::k_chain_ws));
+	CK(cudaFuncGetAttributes(&fa, mf::k_chain<8, mf::CHAIN_BULK_RING>));
+	CK(cudaFuncGetAttributes(&fa, mf::k_masked_argmax));
+	CK(cudaFuncGetAttributes(&fa, mf::k_argmax_final));
+	if (nshards > 1) {
+		CK(cudaFuncGetAttributes(&fa, mf::k_xchg_ll));
+		CK(cudaFuncGetAttributes(&fa, mf::k_argmax_block));
+	}
+	return MFGPU_OK;
+}
+
 int mf_kernels_prepare(int warps, size_t k1_smem, int res_ng, size_t res_smem, size_t pair_smem, int pair_warps, int pair_nt)
 {
 	const auto attr = cudaFuncAttributeMaxDynamicSharedMemorySize;
@@ -793,12 +829,17 @@ extern "C" int mfgpu_plan_iterate(mfgpu_plan *pl, int iters)
 		 * length between that and twice that which leaves the fewest iterations of this call to be
 		 * enqueued one by one (100 iterations: 5 graphs of 20 instead of 6 of 16 + 4 single) */
 		int gi = pl->graph_len ? pl->graph_len : pl->opt_graph_iters;
-		if (!pl->graph_len && pl->opt_graph && iters >= gi) {
-			int best = gi;
-			for (int g = gi; g <= 2 * pl->opt_graph_iters && g <= iters; g += 2)
-				if (iters % g < iters % best || (iters % g == iters % best && g > best))
-					best = g;
-			gi = best;
+		if (!pl->graph_len && pl->opt_graph) {
+			/* short runs get shorter graphs (capture and instantiation cost ~50 us per iteration
+			 * and shard; a run of 100 iterations is better off with 10 launches of 10) */
+			const int lo = (pl->opt_graph_iters == 16 && iters < 256) ? 8 : pl->opt_graph_iters;
+			if (iters >= lo) {
+				int best = lo;
+				for (int g = lo; g <= 2 * lo && g <= iters; g += 2)
+					if (iters % g < iters % best || (iters % g == iters % best && g > best))
+						best = g;
+				gi = best;
+			}
 		}
 		if (pl->opt_graph && left >= gi) {
 			pl->graph_len = gi;

@@ -311,6 +311,7 @@ int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
 		s->n_units = (int)(units.size() / 8);
 	}
 	TRY(mf_kernels_prepare(warps, s->k1_smem, s->res_ng, s->res_smem, s->pair_smem, s->pair_warps, s->pair_nt));
+	TRY(mf_kernels_preload(F, s->split, pl->nshards));
 
 	/* chunks of the long rows for k_dot */
 	std::vector<int> chunk_row, chunk_pos;
