@@ -1350,6 +1350,26 @@ template <int GW> struct AccGroups<GW, GW> {
 	static __device__ __forceinline__ void add(double (&)[GW], const double (&)[GW][ACC_SB], const double (&)[ACC_SB], int) {}
 };
 
+/* row pointers and e_n of the sub-block that starts at nonzero s0 of the warp's block of 32 */
+__device__ __forceinline__ void acc_prep(const int *sidx, const double *se, int s0, const double *srcb, int ld,
+                                         const double *(&rp)[ACC_SB], double (&e)[ACC_SB])
+{
+#pragma unroll
+	for (int n = 0; n < ACC_SB; n += 4) {
+		const int4 i4 = *reinterpret_cast<const int4 *>(sidx + s0 + n);
+		rp[n] = srcb + (size_t)i4.x * ld;           /* past the end: a valid row again, never added */
+		rp[n + 1] = srcb + (size_t)i4.y * ld;
+		rp[n + 2] = srcb + (size_t)i4.z * ld;
+		rp[n + 3] = srcb + (size_t)i4.w * ld;
+	}
+#pragma unroll
+	for (int n = 0; n < ACC_SB; n += 2) {
+		const double2 e2 = ld2(se + s0 + n);
+		e[n] = e2.x;
+		e[n + 1] = e2.y;
+	}
+}
+
 constexpr int ACC_WARPS = 4;
 
 template <int GW>
@@ -1429,23 +1449,7 @@ k_acc(const ChainSide A, const ChainSide B, long units_b, long units_total, int 
 				const int m = min(ACC_SB, mb - s0);
 				const double *rp[ACC_SB];
 				double e[ACC_SB];
-				{
-					int ii[ACC_SB];
-#pragma unroll
-					for (int n = 0; n < ACC_SB; n += 4) {
-						const int4 i4 = *reinterpret_cast<const int4 *>(&s_idx[warp][s0 + n]);
-						ii[n] = i4.x; ii[n + 1] = i4.y; ii[n + 2] = i4.z; ii[n + 3] = i4.w;
-					}
-#pragma unroll
-					for (int n = 0; n < ACC_SB; n += 2) {
-						const double2 e2 = ld2(&s_e[warp][s0 + n]);
-						e[n] = e2.x;
-						e[n + 1] = e2.y;
-					}
-#pragma unroll
-					for (int n = 0; n < ACC_SB; n++)      /* past the end: a valid row again, never added */
-						rp[n] = srcb + (size_t)ii[n] * ld;
-				}
+				acc_prep(s_idx[warp], s_e[warp], s0, srcb, ld, rp, e);
 				double x[GW][ACC_SB];
 				AccGroups<GW, 0>::load(x, rp, ok_last);
 				AccGroups<GW, 0>::add(acc, x, e, m);
