@@ -151,10 +151,11 @@ long long mfgpu_plan_launch_count(mfgpu_plan *plan);
 /* How the partial R gradients of the shards meet: 0 = one shard, nothing to exchange;
  * 1 = ncclAllReduce + apply (one process per GPU); 2 = one kernel that reads every rank's
  * gradient over NVLink peer memory (CUDA IPC) and applies the sum (one process per GPU);
- * 3 = the same inside one process driving N GPUs; 4 = chain kernels store the gradient rows
- * into the rank that owns the item, the owner reduces, applies and stores its rows of R_new
- * into every replica, ordered by fences and flag words; 5 = the same flow with (value, tag)
- * pairs polled by the readers, one launch (the default of one process per GPU). */
+ * 3 = the event-ordered pull inside one process driving N GPUs (option exchange = 2 there);
+ * 4 = chain kernels store the gradient rows into the rank that owns the item, the owner
+ * reduces, applies and stores its rows of R_new into every replica, ordered by fences and flag
+ * words; 5 = the same flow with (value, tag) pairs polled by the readers, one launch (the
+ * default of both N-GPU modes). */
 int mfgpu_plan_exchange_kind(mfgpu_plan *plan);
 /* Algorithmic bytes of ONE iteration, SURVEY.md section 8(d):
  * 16*F*(U_t + I_t) + 12*nnz, with U_t / I_t the users / items having >=1 nonzero. */
@@ -198,12 +199,25 @@ int mfgpu_plan_timer_stop(mfgpu_plan *plan, float *ms);
  *   "chain_ring"   1/0   k_chain gathers through a shared-memory ring / registers
  *   "dot_stages"   2/4   tiles in the dot-phase ring of a k_update_L / k_dot warp (default 2)
  *   "acc_rows"     1/3   rows in flight ahead of the addition in k_update_L (default 1)
- *   "exchange"     rank mode only, collective (every rank sets it at the same point):
+ *   "pair"         1/0/-1 split mode: the dots by k_dot_units (two short rows to a warp), the
+ *                        accumulations of both sides by k_acc / the fused kernels / by shape
+ *                        (default: F >= 128, or F >= 64 on a shard below 6e5 nonzeros)
+ *   "pair_warps"   4/5/6/8 warps per CTA of k_dot_units (default 4)
+ *   "pair_stages"  2..6  tiles in the ring of a k_dot_units warp (default 2)
+ *   "acc_gw"       1..8  feature groups per unit of k_acc (default: all, at most 8)
+ *   "cs_store"     1/0   rows of L_new stored evict-first by the fused kernels (default 0)
+ *   "argmax_items" 1/0/-1 one process, N GPUs: the arg-max sharded by items with a
+ *                        (value, index) merge / by users / by shape (default: items >= 8 users)
+ *   "comm_timeout_ms" n  device-side waits for a peer give up after n ms (default 30000, or
+ *                        MFGPU_COMM_TIMEOUT_MS); the next sync then returns MFGPU_ECOMM
+ *   "exchange"     N shards.  Rank mode (collective: every rank sets it at the same point):
  *                        0 ncclAllReduce + apply; otherwise over peer memory (CUDA IPC) when
  *                        every rank can map the others: 1 or -1 (default) (value, tag) pairs
  *                        polled by the readers, one launch; 2 pull (one kernel reads every
- *                        rank's gradient); 3 push with fences and flag words.  The three
- *                        peer-memory transports add in rank order (bit-identical results).
+ *                        rank's gradient); 3 push with fences and flag words.  One process,
+ *                        N GPUs: 2 = the event-ordered pull, anything else the (value, tag)
+ *                        exchange.  All peer-memory transports add in shard order
+ *                        (bit-identical results).
  * May be set between iterate calls (the plan is reconfigured); unknown names return
  * MFGPU_EINVAL. */
 int mfgpu_plan_set_option(mfgpu_plan *plan, const char *name, int value);
