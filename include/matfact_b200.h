@@ -33,7 +33,7 @@ extern "C" {
 #define MFGPU_ENOMEM   -2   /* host or device allocation failed                      */
 #define MFGPU_ENODEV   -3   /* no CUDA device / not an sm_100 device                 */
 #define MFGPU_ECUDA    -4   /* a CUDA runtime call failed                            */
-#define MFGPU_ECOMM    -5   /* a collective (NCCL) call failed                       */
+#define MFGPU_ECOMM    -5   /* a collective (NCCL) call failed, or a peer did not deliver in time */
 
 /* Same layout as the reference's non_zero_entry (datatypes.h:10-15;
  * deliverables/serial/matFact.c:148-153): 16 bytes, no padding. */

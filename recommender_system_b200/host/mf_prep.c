@@ -10,6 +10,24 @@
 
 #define MF_PREP_MAX_THREADS 8
 
+/* MFGPU_TRACE=1: wall clock of the phases of a pattern build on stderr */
+#include <stdio.h>
+#include <time.h>
+static double prep_now(void)
+{
+	struct timespec t;
+	clock_gettime(CLOCK_MONOTONIC, &t);
+	return t.tv_sec * 1e3 + t.tv_nsec * 1e-6;
+}
+#define PREP_LAP(what)                                                              \
+	do {                                                                            \
+		if (trace) {                                                                \
+			const double n_ = prep_now();                                           \
+			fprintf(stderr, "[mfgpu]   prep: %-22s %8.3f ms\n", what, n_ - t_last); \
+			t_last = n_;                                                            \
+		}                                                                           \
+	} while (0)
+
 static void *xcalloc(size_t n, size_t sz)
 {
 	return calloc(n ? n : 1, sz);
@@ -206,6 +224,8 @@ int mf_pattern_build_scan(mf_pattern *p, int users, int items, int nnz,
 		n_lo = scan->row_first[user_lo];
 		n_hi = scan->row_first[user_hi];
 	}
+	const int trace = getenv("MFGPU_TRACE") != NULL;
+	double t_last = trace ? prep_now() : 0.0;
 	const int T = prep_threads(n_hi - n_lo);
 	prep_slice sl[MF_PREP_MAX_THREADS];
 	int *cur = NULL;            /* threads 1..T-1: their per-row / per-column arrays */
@@ -236,7 +256,9 @@ int mf_pattern_build_scan(mf_pattern *p, int users, int items, int nnz,
 		sl[t].bad = 0;
 		sl[t].p = p;
 	}
+	PREP_LAP("alloc");
 	run_slices(sl, T, prep_count);
+	PREP_LAP("count (threads)");
 	int local = 0;
 	for (int t = 0; t < T; t++) {
 		if (sl[t].bad) {
@@ -272,6 +294,7 @@ int mf_pattern_build_scan(mf_pattern *p, int users, int items, int nnz,
 		if (col_count[j] > p->max_col_len)
 			p->max_col_len = col_count[j];
 
+	PREP_LAP("sum counts");
 	p->row_id = palloc(p, (size_t)(user_hi - user_lo), sizeof(int), 0);
 	p->col_id = palloc(p, (size_t)items, sizeof(int), 0);
 	if (!p->row_id || !p->col_id)
@@ -281,6 +304,7 @@ int mf_pattern_build_scan(mf_pattern *p, int users, int items, int nnz,
 	if (p->n_rows < 0 || p->n_cols < 0)
 		goto done;
 
+	PREP_LAP("order by length");
 	p->row_ptr = palloc(p, (size_t)p->n_rows + 1, sizeof(int), 1);
 	p->col_ptr = palloc(p, (size_t)p->n_cols + 1, sizeof(int), 1);
 	p->col_idx = palloc(p, (size_t)local, sizeof(int), 0);
@@ -311,6 +335,7 @@ int mf_pattern_build_scan(mf_pattern *p, int users, int items, int nnz,
 			at += k;
 		}
 	}
+	PREP_LAP("pointers");
 	/* rated-item mask, matFact.c:14-22: per user the items of its matched entries */
 	p->mask_ptr = palloc(p, (size_t)users + 1, sizeof(int), 1);
 	p->first_free = palloc(p, (size_t)users, sizeof(int), 0);
@@ -336,7 +361,9 @@ int mf_pattern_build_scan(mf_pattern *p, int users, int items, int nnz,
 		sl[t].mask_at = at;             /* local entries before the slice */
 		at += sl[t].local;
 	}
+	PREP_LAP("mask pointers");
 	run_slices(sl, T, prep_scatter);
+	PREP_LAP("scatter (threads)");
 
 	for (int i = 0; i < users; i++) {
 		int f = -1;
@@ -352,6 +379,7 @@ int mf_pattern_build_scan(mf_pattern *p, int users, int items, int nnz,
 		}
 		p->first_free[i] = f;
 	}
+	PREP_LAP("first_free");
 	rc = MFGPU_OK;
 done:
 	free(cur);
