@@ -228,8 +228,11 @@ int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
 	auto pair_bytes = [&](int nt) { return pair_warps * ((size_t)nt * 34 * 16 + 144) * sizeof(double) + 128; };   /* mf::dot_units_doubles + alignment slack */
 	/* default: where it was measured ahead of the fused kernels (us per iteration, split / fused):
 	 * inst60000 shape 316 / 401, one eighth of it 53 / 61, one eighth of the ML1M shape 52 / 59;
-	 * the whole ML1M shape 252 / 248 -- wide factors always, F >= 64 on shards below 6e5 nonzeros */
-	const int want_split = pl->opt_pair >= 0 ? pl->opt_pair : (F >= 128 || (F >= 64 && pt.nnz < 600000));
+	 * the whole ML1M shape 252 / 248 -- wide factors always, F >= 64 on shards below 6e5 nonzeros;
+	 * not for rows of a few nonzeros (two rows to a warp leave its lanes idle: inst50000-5000-100-2-5
+	 * 113 / 97, inst1e6-100-700-1-3 1331 / 1114): at least 8 nonzeros per row on average */
+	const int want_split = pl->opt_pair >= 0 ? pl->opt_pair
+	                       : ((F >= 128 || (F >= 64 && pt.nnz < 600000)) && (long)pt.nnz >= 8L * pt.n_rows);
 	const bool split = warps == 8 && want_split && pair_bytes(2) <= (size_t)max_smem;
 	/* the ring of a k_dot_pair warp is what it has in flight from L2: as deep as one CTA of
 	 * eight warps per SM can hold (measured latency under load ~2000 cycles: ~100 KB in flight
