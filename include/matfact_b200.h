@@ -201,7 +201,8 @@ int mfgpu_plan_timer_stop(mfgpu_plan *plan, float *ms);
  *   "acc_rows"     1/3   rows in flight ahead of the addition in k_update_L (default 1)
  *   "pair"         1/0/-1 split mode: the dots by k_dot_units (two short rows to a warp), the
  *                        accumulations of both sides by k_acc / the fused kernels / by shape
- *                        (default: F >= 128, or F >= 64 on a shard below 6e5 nonzeros)
+ *                        (default: F >= 128, or F >= 64 on a shard below 6e5 nonzeros, and
+ *                        rows of at least 8 nonzeros on average)
  *   "pair_warps"   4/5/6/8 warps per CTA of k_dot_units (default 4)
  *   "pair_stages"  2..6  tiles in the ring of a k_dot_units warp (default 2)
  *   "acc_gw"       1..8  feature groups per unit of k_acc (default: all, at most 8)
