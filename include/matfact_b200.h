@@ -209,6 +209,10 @@ int mfgpu_plan_timer_stop(mfgpu_plan *plan, float *ms);
  *   "cs_store"     1/0   rows of L_new stored evict-first by the fused kernels (default 0)
  *   "argmax_items" 1/0/-1 one process, N GPUs: the arg-max sharded by items with a
  *                        (value, index) merge / by users / by shape (default: items >= 8 users)
+ *   "xchg_fused"   1/0   N shards, split mode, (value, tag) exchange: the exchange inside the
+ *                        accumulation kernel (k_acc_ll: columns | reduce | rows | unpack)
+ *                        instead of a launch of its own (default 0: measured slower, DESIGN.md 5;
+ *                        same bits either way, a rank may choose for itself)
  *   "comm_timeout_ms" n  device-side waits for a peer give up after n ms (default 30000, or
  *                        MFGPU_COMM_TIMEOUT_MS); the next sync then returns MFGPU_ECOMM
  *   "exchange"     N shards.  Rank mode (collective: every rank sets it at the same point):

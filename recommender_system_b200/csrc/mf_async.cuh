@@ -150,6 +150,13 @@ __device__ __forceinline__ void st_pair(double *p, double v, unsigned long long 
 	             ::"l"(p), "l"(__double_as_longlong(v)), "l"(tag) : "memory");
 }
 
+/* one look at a pair (the callers issue several before they use the first) */
+__device__ __forceinline__ void ld_pair_try(const double *p, unsigned long long &v, unsigned long long &t)
+{
+	asm volatile("{\n\t.reg .b128 q;\n\tld.relaxed.sys.global.b128 q, [%2];\n\tmov.b128 {%0, %1}, q;\n\t}"
+	             : "=l"(v), "=l"(t) : "l"(p) : "memory");
+}
+
 __device__ __forceinline__ double ld_pair_when(const double *p, unsigned long long tag, const WaitCtl &w, int who)
 {
 	unsigned long long v, t;

@@ -70,6 +70,8 @@ struct mf_shard {
 	int me;                                  /* index of this shard among the nshards of the problem (rank mode: the rank) */
 	unsigned long long *d_sync;              /* this shard's sync block (MF_SYNC_WORDS words), mapped by every peer */
 	cudaStream_t st, st2;                    /* st2: the long-row launch runs beside the short rows */
+	void *d_ll_args;                         /* mf::LLArgs[2] for k_acc_ll (by factor parity), or null */
+	bool ll_fused;                           /* the iteration being enqueued has its exchange inside k_acc_ll */
 	mf_pattern pat;
 	int user_lo, user_hi;
 	/* sparse pattern on the device */
@@ -157,7 +159,7 @@ struct mfgpu_plan {
 	void *ipc_mapped[5 * MF_MAX_SHARDS];
 	int n_ipc_mapped;
 	/* options */
-	int opt_graph, opt_graph_iters, opt_long_row, opt_long_col, opt_ch, opt_chain_ring, opt_resident, opt_res_rows, opt_chain_ws, opt_exchange, opt_dot_stages, opt_acc_rows, opt_cs_store, opt_pair, opt_pair_stages, opt_pair_warps, opt_acc_gw, opt_comm_timeout_ms, opt_argmax_items;
+	int opt_graph, opt_graph_iters, opt_long_row, opt_long_col, opt_ch, opt_chain_ring, opt_resident, opt_res_rows, opt_chain_ws, opt_exchange, opt_dot_stages, opt_acc_rows, opt_cs_store, opt_pair, opt_pair_stages, opt_pair_warps, opt_acc_gw, opt_comm_timeout_ms, opt_argmax_items, opt_xchg_fused;
 };
 
 /* ---- shared helpers (defined in mf_capi.cu) ----------------------------------- */

@@ -293,6 +293,130 @@ k_xchg_ll(const LLArgs a)
 	}
 }
 
+/* ---- the same exchange inside k_acc (split mode; acc_body / NoTail in mf_loop.cuh) ----------
+ * Reduce unit: 32 elements of the own block, a lane each; unpack unit: 128 elements of the other
+ * blocks, four per lane.  A lane first looks at up to four pairs at once and only then waits for
+ * the ones that were not there: a warp of k_acc is worth ~14 KB of gathers in flight, and it
+ * should be back at them quickly.  The arithmetic is k_xchg_ll's, element for element. */
+constexpr int LL_RED_ELEMS = 32, LL_UNP_ELEMS = 128;
+
+__device__ __noinline__ void ll_reduce_unit(const LLArgs *ap, long u, int lane)
+{
+	const LLArgs &a = *ap;
+	const unsigned long long want = *(volatile unsigned long long *)(a.sync_own + MF_SYNC_EPOCH) + 1;
+	const long par = (long)(want & 1) * a.half;
+	const WaitCtl ctl{a.sync_own + MF_SYNC_ERR, a.timeout_ns};
+	const long t = u * LL_RED_ELEMS + lane;
+	if (t >= (long)a.cnt * a.F)
+		return;
+	const int q = (int)(t / a.F), k = (int)(t % a.F);
+	const int slot = a.lo + q, who = a.contrib[slot];
+	const size_t blk = (size_t)a.per * a.ld;
+	const double *g = a.recv + par + 2 * ((size_t)q * a.ld + k);
+	const size_t o = (size_t)a.touched_item[slot] * a.ld + k;
+	const double r_old = a.Rold[o];
+	double sum = 0.0;
+	for (int h0 = 0; h0 < a.n; h0 += 4) {
+		unsigned long long v[4], tg[4];
+#pragma unroll
+		for (int j = 0; j < 4; j++) {
+			const int h = h0 + j;
+			tg[j] = 0;                       /* never a tag: the first exchange waits for 1 */
+			if (h < a.n && ((who >> h) & 1))
+				ld_pair_try(g + 2 * h * blk, v[j], tg[j]);
+		}
+#pragma unroll
+		for (int j = 0; j < 4; j++) {
+			const int h = h0 + j;
+			if (h >= a.n)
+				break;
+			double c = 0.0;
+			if ((who >> h) & 1)
+				c = tg[j] == want ? __longlong_as_double((long long)v[j]) : ld_pair_when(g + 2 * h * blk, want, ctl, h);
+			sum = h == 0 ? c : __dadd_rn(sum, c);
+		}
+	}
+	const double val = __dadd_rn(r_old, sum);
+	a.Rnew[o] = val;
+	const size_t so = 2 * ((size_t)slot * a.ld + k);
+	for (int d = 1; d < a.n; d++) {              /* start with the neighbour: spread the links */
+		int h = a.me + d;
+		if (h >= a.n)
+			h -= a.n;
+		st_pair(a.stage[h] + par + so, val, want);
+	}
+}
+
+__device__ __noinline__ void ll_unpack_unit(const LLArgs *ap, long u, int lane)
+{
+	const LLArgs &a = *ap;
+	const unsigned long long want = *(volatile unsigned long long *)(a.sync_own + MF_SYNC_EPOCH) + 1;
+	const long par = (long)(want & 1) * a.half;
+	const WaitCtl ctl{a.sync_own + MF_SYNC_ERR, a.timeout_ns};
+	const long total = (long)(a.n_touched - a.cnt) * a.F;
+	const double *stage_own = a.stage_own + par;
+	unsigned long long v[4], tg[4];
+	int slot[4], k[4];
+#pragma unroll
+	for (int j = 0; j < 4; j++) {
+		const long e = u * LL_UNP_ELEMS + j * 32 + lane;
+		tg[j] = 0;
+		slot[j] = -1;
+		if (e < total) {
+			slot[j] = (int)(e / a.F);
+			k[j] = (int)(e % a.F);
+			if (slot[j] >= a.lo)
+				slot[j] += a.cnt;                     /* skip the own block */
+			ld_pair_try(stage_own + 2 * ((size_t)slot[j] * a.ld + k[j]), v[j], tg[j]);
+		}
+	}
+#pragma unroll
+	for (int j = 0; j < 4; j++) {
+		if (slot[j] < 0)
+			continue;
+		const double val = tg[j] == want ? __longlong_as_double((long long)v[j])
+		                                 : ld_pair_when(stage_own + 2 * ((size_t)slot[j] * a.ld + k[j]), want, ctl, slot[j] / a.per);
+		a.Rnew[(size_t)a.touched_item[slot[j]] * a.ld + k[j]] = val;
+	}
+}
+
+/* k_acc with the exchange in it (N shards, split mode), in four phases with a ticket counter each:
+ *   the columns | reduce units | the rows | unpack units
+ * The own block of items is reduced as soon as the columns are through and travels while the rows
+ * are being accumulated; the other blocks are taken at the end, when they have long arrived.
+ * A warp takes reduce units only when it has no column in hand, so a column that somebody waits
+ * for is always with a warp that is working on it, whatever the hardware's order of starting
+ * CTAs: no cycle, as in k_xchg_ll.  The last CTA to finish closes the iteration. */
+template <int GW>
+__global__ void __launch_bounds__(ACC_WARPS * 32, GW <= 2 ? 8 : GW <= 4 ? 6 : ACC_CTAS)
+k_acc_ll(const ChainSide A, const ChainSide B, long units_b, long units_a, int F, int ld,
+         unsigned long long *ticket, const LLArgs *xa, long r_units, long u_units)
+{
+	const int lane = threadIdx.x & 31;
+	auto take = [&](unsigned long long *t) {
+		unsigned long long v = 0;
+		if (lane == 0)
+			v = atomicAdd(t, 1ull);
+		return (long)__shfl_sync(FULL, v, 0);
+	};
+	acc_body<GW>(A, B, units_b, units_b, F, ld, ticket);
+	for (long u = take(ticket + 1); u < r_units; u = take(ticket + 1))
+		ll_reduce_unit(xa, u, lane);
+	acc_body<GW>(A, B, 0, units_a, F, ld, ticket + 2);
+	for (long u = take(ticket + 3); u < u_units; u = take(ticket + 3))
+		ll_unpack_unit(xa, u, lane);
+	__syncthreads();
+	if (threadIdx.x == 0) {
+		__threadfence();
+		volatile unsigned long long *sync = xa->sync_own;
+		const unsigned long long want = sync[MF_SYNC_EPOCH] + 1;
+		if (atomicAdd(xa->sync_own + MF_SYNC_CTAS, 1ull) == (unsigned long long)gridDim.x - 1) {
+			sync[MF_SYNC_CTAS] = 0;
+			sync[MF_SYNC_EPOCH] = want;
+		}
+	}
+}
+
 /* profiling only: this rank's contributions again, with the tag of the next exchange and no
  * chain kernels before it (the values do not matter: the exchange writes the output buffer) */
 __global__ void __launch_bounds__(256)
@@ -524,6 +648,30 @@ static int launch_dot(mfgpu_plan *pl, mf_shard *s, int c, cudaStream_t st)
 	return MFGPU_OK;
 }
 
+static bool has_deep(const mf_shard *s) { return s->la.n_deep_rows > 0 || s->la.n_deep_cols > 0; }
+
+static mf::LLArgs ll_args(const mfgpu_plan *pl, const mf_shard *s, int c);
+
+/* N shards, low-latency exchange, split mode: the exchange goes into k_acc (k_acc_ll) -- unless
+ * some of the shard's chains run in another launch beside it (k_chain_ws for the deepest): a
+ * reduce unit would wait for their contributions, and nothing promises that the hardware runs
+ * the two launches at the same time (two kernels that want different splits of an SM's
+ * L1 / shared memory do not share it: measured, the wait bound fired). */
+static bool ll_fusable(const mfgpu_plan *pl, const mf_shard *s)
+{
+	return pl->nshards > 1 && pl->xchg_ipc == 3 && s->split && pl->opt_xchg_fused != 0 &&
+	       !(s->dot_blocks > 0 || has_deep(s)) && (long)pl->n_touched * pl->F > 0;
+}
+
+template <int GW>
+static void launch_acc_ll_gw(const mf::ChainSide &A, const mf::ChainSide &B, long ub, long ut, int F, int ld,
+                             unsigned long long *ticket, int n_sm, const mf::LLArgs *xa, long ur, long uu, cudaStream_t st)
+{
+	const long ctas = std::min<long>((ut + ur + uu + mf::ACC_WARPS - 1) / mf::ACC_WARPS,
+	                                 (long)n_sm * (GW <= 2 ? 8 : GW <= 4 ? 6 : mf::ACC_CTAS));
+	mf::k_acc_ll<GW><<<(unsigned)ctas, mf::ACC_WARPS * 32, 0, st>>>(A, B, ub, ut - ub, F, ld, ticket, xa, ur, uu);
+}
+
 template <int GW>
 static void launch_acc_gw(const mf::ChainSide &A, const mf::ChainSide &B, long ub, long ut, int F, int ld,
                           unsigned long long *ticket, int n_sm, cudaStream_t st)
@@ -541,11 +689,33 @@ static int launch_acc(mfgpu_plan *pl, mf_shard *s, int c, double *rout, cudaStre
 	const int ng = (a.F + 31) / 32;
 	const int gw = pl->opt_acc_gw > 0 ? std::min(pl->opt_acc_gw, std::min(ng, 8)) : std::min(ng, 8), nb = (ng + gw - 1) / gw;
 	const long ub = (long)(B.end - B.begin) * nb, ut = ub + (long)(A.end - A.begin) * nb;
-	if (ut <= 0)
+	const bool fuse = rout == nullptr && ll_fusable(pl, s);
+	if (ut <= 0 && !fuse)
 		return MFGPU_OK;
 	int n_sm = 148;
 	CK(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, s->dev));
-	CK(cudaMemsetAsync(s->d_ticket, 0, sizeof(unsigned long long), st));
+	CK(cudaMemsetAsync(s->d_ticket, 0, (fuse ? 4 : 1) * sizeof(unsigned long long), st));
+	if (fuse) {
+		/* the exchange's arguments are read from global memory (s->d_ll_args, one copy per factor
+		 * parity, written by ll_args_upload before the first iteration): as a kernel parameter
+		 * their address stayed in registers across the accumulation loop, which has none to spare */
+		if (!s->d_ll_args)
+			return mf_fail(MFGPU_EINVAL, "k_acc_ll without its arguments (internal error)");
+		const mf::LLArgs *xa = (const mf::LLArgs *)s->d_ll_args + c;
+		const mf::LLArgs xh = ll_args(pl, s, c);
+		const long ur = ((long)xh.cnt * xh.F + mf::LL_RED_ELEMS - 1) / mf::LL_RED_ELEMS;
+		const long uu = ((long)(xh.n_touched - xh.cnt) * xh.F + mf::LL_UNP_ELEMS - 1) / mf::LL_UNP_ELEMS;
+#define MF_ACC_LL(G) case G: launch_acc_ll_gw<G>(A, B, ub, std::max(ut, 0L), a.F, a.ld, s->d_ticket, n_sm, xa, ur, uu, st); break;
+		switch (gw) {
+			MF_ACC_LL(1) MF_ACC_LL(2) MF_ACC_LL(3) MF_ACC_LL(4) MF_ACC_LL(5) MF_ACC_LL(6) MF_ACC_LL(7)
+		default: launch_acc_ll_gw<8>(A, B, ub, std::max(ut, 0L), a.F, a.ld, s->d_ticket, n_sm, xa, ur, uu, st); break;
+		}
+#undef MF_ACC_LL
+		CK(cudaGetLastError());
+		count_launches(pl);
+		s->ll_fused = true;          /* enqueue_iteration: no exchange launch after this one */
+		return MFGPU_OK;
+	}
 	switch (gw) {
 	case 1: launch_acc_gw<1>(A, B, ub, ut, a.F, a.ld, s->d_ticket, n_sm, st); break;
 	case 2: launch_acc_gw<2>(A, B, ub, ut, a.F, a.ld, s->d_ticket, n_sm, st); break;
@@ -591,8 +761,6 @@ static int launch_chain(mfgpu_plan *pl, mf_shard *s, int c, double *rout, bool d
 	count_launches(pl);
 	return MFGPU_OK;
 }
-
-static bool has_deep(const mf_shard *s) { return s->la.n_deep_rows > 0 || s->la.n_deep_cols > 0; }
 
 /* The kernels of one iteration on one shard; R-side results go to rout.
  *   st : k_update_L(short rows) ------------\                /-> k_chain<bulk> --\
@@ -703,13 +871,27 @@ static int enqueue_ll(mfgpu_plan *pl, mf_shard *s, int c)
 	return MFGPU_OK;
 }
 
+/* device copies of the exchange's arguments for k_acc_ll, both factor parities (not inside a capture) */
+static int ll_args_upload(mfgpu_plan *pl, mf_shard *s)
+{
+	if (s->d_ll_args || !ll_fusable(pl, s))
+		return MFGPU_OK;
+	const mf::LLArgs both[2] = {ll_args(pl, s, 0), ll_args(pl, s, 1)};
+	CK(cudaMalloc(&s->d_ll_args, sizeof both));
+	CK(cudaMemcpy(s->d_ll_args, both, sizeof both, cudaMemcpyHostToDevice));
+	return MFGPU_OK;
+}
+
 static int enqueue_iteration(mfgpu_plan *pl, mf_shard *s, int c)
 {
 	if (pl->nshards == 1)
 		return enqueue_loop_kernels(pl, s, c, s->R[1 - c]);
 	if (pl->xchg_ipc >= 2) {
+		s->ll_fused = false;
 		TRY(enqueue_loop_kernels(pl, s, c, nullptr));
-		return pl->xchg_ipc == 3 ? enqueue_ll(pl, s, c) : enqueue_push(pl, s, c);
+		if (pl->xchg_ipc == 3)
+			return s->ll_fused ? MFGPU_OK : enqueue_ll(pl, s, c);
+		return enqueue_push(pl, s, c);
 	}
 	/* rank mode: the gradient goes to G[c] for the peer-memory exchange (double buffered,
 	 * see k_apply_R_xchg), to G[0] for NCCL */
@@ -795,10 +977,11 @@ static long long launches_per_iteration(const mfgpu_plan *pl, const mf_shard *s)
 {
 	const mf::LoopArgs &a = s->la;
 	long long n = (s->k1_blocks > 0) + (s->n_units > 0) + (s->dot_blocks > 0);
-	n += (a.n_long - a.n_deep_rows > 0 || a.n_cols - a.n_deep_cols > 0);
+	const bool bulk = a.n_long - a.n_deep_rows > 0 || a.n_cols - a.n_deep_cols > 0;
+	n += bulk;
 	n += (a.n_deep_rows > 0 || a.n_deep_cols > 0);
 	if (pl->nshards > 1 && (long)pl->n_touched * pl->F > 0)
-		n += pl->xchg_ipc == 3 ? 1 : pl->xchg_ipc ? 2 : 1;
+		n += pl->xchg_ipc == 3 ? (ll_fusable(pl, s) && bulk ? 0 : 1) : pl->xchg_ipc ? 2 : 1;
 	return n;
 }
 
@@ -812,6 +995,7 @@ extern "C" int mfgpu_plan_iterate(mfgpu_plan *pl, int iters)
 	for (int g = 0; g < nl; g++) {
 		CK(cudaSetDevice(pl->sh[g].dev));
 		CK(cudaEventRecord(pl->sh[g].ev0, pl->sh[g].st));
+		TRY(ll_args_upload(pl, &pl->sh[g]));
 	}
 	int c = pl->cur;
 	if (pl->F == 0 || pl->nnz == 0) {

@@ -1373,9 +1373,8 @@ __device__ __forceinline__ void acc_prep(const int *sidx, const double *se, int 
 constexpr int ACC_WARPS = 4;
 
 template <int GW>
-__global__ void __launch_bounds__(ACC_WARPS * 32, GW <= 2 ? 8 : GW <= 4 ? 6 : ACC_CTAS)
-k_acc(const ChainSide A, const ChainSide B, long units_b, long units_total, int F, int ld,
-      unsigned long long *ticket)
+__device__ __forceinline__ void acc_body(const ChainSide &A, const ChainSide &B, long units_b, long units_total,
+                                         int F, int ld, unsigned long long *ticket)
 {
 	/* per warp: 32 indices (as doubles' worth of row offsets) and 32 e_n */
 	__shared__ __align__(16) int s_idx[ACC_WARPS][32];
@@ -1464,6 +1463,14 @@ k_acc(const ChainSide A, const ChainSide B, long units_b, long units_total, int 
 		w = wn;
 		cur = nxt;
 	}
+}
+
+template <int GW>
+__global__ void __launch_bounds__(ACC_WARPS * 32, GW <= 2 ? 8 : GW <= 4 ? 6 : ACC_CTAS)
+k_acc(const ChainSide A, const ChainSide B, long units_b, long units_total, int F, int ld,
+      unsigned long long *ticket)
+{
+	acc_body<GW>(A, B, units_b, units_total, F, ld, ticket);
 }
 
 /* N shards: R_new[item] = R_old[item] + G[slot] for the touched items. */

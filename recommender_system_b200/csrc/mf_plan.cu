@@ -613,6 +613,7 @@ static void shard_destroy(mf_shard *s, bool own_sync)
 	                s->am_L, s->am_mask_ptr, s->am_mask_col, s->am_first_free, s->am_part_v, s->am_out_v, s->am_part_j, s->am_nan, s->am_out_j};
 	for (void *q : ptrs)
 		dev_free(q, s->st);
+	if (s->d_ll_args) cudaFree(s->d_ll_args);
 	tc.lap("destroy: other buffers");
 	if (s->ev0) cudaEventDestroy(s->ev0);
 	if (s->ev1) cudaEventDestroy(s->ev1);
@@ -886,6 +887,9 @@ static int plan_create(mfgpu_plan **out, int users, int items, int features, int
 	pl->opt_resident = 1;
 	pl->opt_res_rows = 0;
 	pl->opt_chain_ws = 1;
+	pl->opt_xchg_fused = 0;      /* 1: the low-latency exchange inside k_acc (k_acc_ll; measured slower) */
+	if (const char *env = getenv("MFGPU_XCHG_FUSED"))
+		pl->opt_xchg_fused = atoi(env);
 	pl->opt_argmax_items = -1;   /* item-sharded arg-max when users << items (mfgpu_plan_recommend) */
 	pl->opt_pair = -1;           /* split mode by shape (mf_configure_shard) */
 	pl->opt_pair_warps = 4;
@@ -1298,6 +1302,7 @@ extern "C" int mfgpu_plan_set_option(mfgpu_plan *pl, const char *name, int value
 	else if (!strcmp(name, "pair_warps")) pl->opt_pair_warps = value;
 	else if (!strcmp(name, "acc_gw")) pl->opt_acc_gw = value;
 	else if (!strcmp(name, "argmax_items")) pl->opt_argmax_items = value;
+	else if (!strcmp(name, "xchg_fused")) pl->opt_xchg_fused = value;
 	else if (!strcmp(name, "comm_timeout_ms")) pl->comm_timeout_ns = (unsigned long long)std::max(1, value) * 1000000ull;
 	else if (!strcmp(name, "exchange")) {
 		/* rank mode, collective: 0 = ncclAllReduce; peer memory when available: 1 / -1 = low

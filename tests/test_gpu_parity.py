@@ -370,12 +370,14 @@ def test_init_factors_on_device(gpu, shape):
             assert bits_equal(L0, L1) and bits_equal(R0, R1)
 
 
-@pytest.mark.parametrize("options", [{}, {"exchange": 2}, {"pair": 1}, {"graph": 0}])
+@pytest.mark.parametrize("options", [{}, {"exchange": 2}, {"pair": 1}, {"graph": 0},
+                                     {"pair": 1, "xchg_fused": 1}])
 @pytest.mark.parametrize("nshards", [2, 4, 8])
 def test_multi_gpu_matches_sharded_oracle(gpu, oracle, nshards, options):
     """One process, N GPUs (what `MATFACT_NGPUS=N matFact file.in` runs): the low-latency
     exchange over peer memory inside CUDA graphs by default, the event-ordered pull with
-    exchange=2; both add in shard order == the oracle's N-shard ordering, bit for bit.  The
+    exchange=2, or (split mode, xchg_fused=1) the exchange inside the accumulation kernel; all
+    add in shard order == the oracle's N-shard ordering, bit for bit.  The
     iterations are split over several calls with odd counts (the buffers of the exchange
     alternate with the iteration, across calls too)."""
     if gpu.device_count() < nshards:
