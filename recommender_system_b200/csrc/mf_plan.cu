@@ -1325,6 +1325,10 @@ extern "C" int mfgpu_plan_set_option(mfgpu_plan *pl, const char *name, int value
 	for (int g = 0; g < local_shards(pl); g++) {
 		CK(cudaSetDevice(pl->sh[g].dev));
 		CK(cudaStreamSynchronize(pl->sh[g].st));
+		if (pl->sh[g].d_ll_args) {           /* k_acc_ll's copy of the exchange's arguments: made again by the next iterate */
+			CK(cudaFree(pl->sh[g].d_ll_args));
+			pl->sh[g].d_ll_args = nullptr;
+		}
 		TRY(mf_configure_shard(pl, &pl->sh[g]));
 	}
 	return MFGPU_OK;
