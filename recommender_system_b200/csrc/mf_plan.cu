@@ -290,6 +290,7 @@ int mf_configure_shard(mfgpu_plan *pl, mf_shard *s)
 		s->pair_nt = pair_nt;
 		s->pair_warps = pair_warps;
 		s->n_mid = n_long;
+		units.reserve(8 * ((size_t)(n_long ? pt.row_ptr[n_long] : 0) / 32 + (size_t)pt.n_rows + 1));
 		auto unit = [&](int ra, int basea, int la, int rb) {
 			const int ib = rb >= 0 ? pt.row_id[rb] - s->user_lo : 0;
 			const int baseb = rb >= 0 ? pt.row_ptr[rb] : 0, lb = rb >= 0 ? pt.row_ptr[rb + 1] - baseb : 0;

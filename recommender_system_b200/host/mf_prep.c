@@ -110,6 +110,12 @@ typedef struct {
 	int first_unsorted;         /* pass 1: first n in the slice that does not grow strictly in (row, col) */
 	int matched, mask_at;       /* pass 2: entries n < matched go to mask_col from position mask_at */
 	mf_pattern *p;
+	/* pass 2 in two steps (rows known never to decrease): */
+	int *pos;                   /* [n_hi - n_lo] by-item position of entry n_base + x */
+	int n_base;
+	int r0, r1;                 /* stored rows this thread fills in prep_fill_rows */
+	int first_free_here;        /* ... which also sets first_free of its users */
+	const int *row_first;
 } prep_slice;
 
 static void *prep_count(void *arg)
@@ -142,6 +148,20 @@ static void *prep_count(void *arg)
 	return NULL;
 }
 
+/* pass 1 for a list that mf_scan_entries has been over (valid, rows never decrease, so every
+ * entry of the slice is the shard's and the rows' counts are row_first's differences): columns only */
+static void *prep_count_cols(void *arg)
+{
+	prep_slice *s = arg;
+	const mfgpu_entry *en = s->entries;
+	int *col_cur = s->col_cur;
+	for (int n = s->n0; n < s->n1; n++)
+		col_cur[en[n].col]++;
+	s->local = s->n1 - s->n0;
+	s->first_unsorted = s->n1;
+	return NULL;
+}
+
 static void *prep_scatter(void *arg)
 {
 	prep_slice *s = arg;
@@ -157,6 +177,67 @@ static void *prep_scatter(void *arg)
 		p->row_idx[pc] = r;
 		if (n < s->matched)            /* the matched prefix is (row, col)-sorted: a linear fill */
 			p->mask_col[s->mask_at++] = c;
+	}
+	return NULL;
+}
+
+/* Pass 2 in two steps, for entry lists whose rows never decrease (a row's entries are then one
+ * piece of the file, row_first).  prep_scatter above writes the by-user arrays row block by
+ * row block in FILE order, and the stored rows are ordered by length: every ~15 entries three
+ * arrays jump to a cold line (~20 ns per entry, 3.1 of the 4.7 ms of a build at the inst60000
+ * shape).  Here the by-item side is done in file order (the only order that leaves a column's
+ * rows ascending) with each entry's by-item position kept in a scratch array, and the by-user
+ * arrays are then written front to back in STORED order, reading each row's piece of the file. */
+static void *prep_scatter_cols(void *arg)
+{
+	prep_slice *s = arg;
+	const mfgpu_entry *en = s->entries;
+	int *row_idx = s->p->row_idx, *mask_col = s->p->mask_col;
+	int *col_cur = s->col_cur, *pos = s->pos - s->n_base;
+	int mask_at = s->mask_at;
+	const int matched = s->matched;
+	for (int n = s->n0; n < s->n1; n++) {
+		const int c = en[n].col;
+		const int pc = col_cur[c]++;
+		row_idx[pc] = en[n].row;
+		pos[n] = pc;
+		if (n < matched)
+			mask_col[mask_at++] = c;
+	}
+	return NULL;
+}
+
+static void *prep_fill_rows(void *arg)
+{
+	prep_slice *s = arg;
+	const mf_pattern *p = s->p;
+	const mfgpu_entry *en = s->entries;
+	const int *pos = s->pos - s->n_base;
+	for (int r = s->r0; r < s->r1; r++) {
+		if (r + 8 < s->r1) {                 /* the piece of the file of a row soon to come */
+			const mfgpu_entry *nx = en + s->row_first[p->row_id[r + 8]];
+			__builtin_prefetch(nx);
+			__builtin_prefetch(nx + 4);
+			__builtin_prefetch(nx + 8);
+			__builtin_prefetch(nx + 12);
+		}
+		const int i = p->row_id[r];
+		int n = s->row_first[i];
+		if (s->first_free_here) {
+			/* every entry matched: the user's mask is its piece of the file, ascending and
+			 * distinct, and the first item the cursor does not skip is the first a with
+			 * col[a] != a (see the serial loop in mf_pattern_build_scan) */
+			const int cnt = p->row_ptr[r + 1] - p->row_ptr[r];
+			int a = 0;
+			while (a < cnt && en[n + a].col == a)
+				a++;
+			p->first_free[i] = a < p->items ? a : -1;
+		}
+		for (int k = p->row_ptr[r]; k < p->row_ptr[r + 1]; k++, n++) {
+			p->col_idx[k] = en[n].col;
+			p->val[k] = en[n].value;
+			p->epos[k] = pos[n];
+		}
 	}
 	return NULL;
 }
@@ -224,11 +305,14 @@ int mf_pattern_build_scan(mf_pattern *p, int users, int items, int nnz,
 		n_lo = scan->row_first[user_lo];
 		n_hi = scan->row_first[user_hi];
 	}
+	/* rows known never to decrease: the lighter passes (prep_count_cols, prep_scatter_cols + prep_fill_rows) */
+	const int two_step = scan && scan->by_row && scan->row_first && !getenv("MFGPU_PREP_ONE_STEP");
 	const int trace = getenv("MFGPU_TRACE") != NULL;
 	double t_last = trace ? prep_now() : 0.0;
 	const int T = prep_threads(n_hi - n_lo);
 	prep_slice sl[MF_PREP_MAX_THREADS];
 	int *cur = NULL;            /* threads 1..T-1: their per-row / per-column arrays */
+	int *pos = NULL;            /* pass 2 in two steps: by-item position of every entry of the slice */
 	int *row_count = xcalloc((size_t)users, sizeof *row_count);
 	int *col_count = xcalloc((size_t)items, sizeof *col_count);
 	int *row_slot = xcalloc((size_t)users, sizeof *row_slot);
@@ -257,7 +341,7 @@ int mf_pattern_build_scan(mf_pattern *p, int users, int items, int nnz,
 		sl[t].p = p;
 	}
 	PREP_LAP("alloc");
-	run_slices(sl, T, prep_count);
+	run_slices(sl, T, two_step ? prep_count_cols : prep_count);
 	PREP_LAP("count (threads)");
 	int local = 0;
 	for (int t = 0; t < T; t++) {
@@ -276,8 +360,11 @@ int mf_pattern_build_scan(mf_pattern *p, int users, int items, int nnz,
 		matched = scan->matched;         /* of the whole list, not of the slice */
 	for (int i = user_lo; i < user_hi; i++) {
 		int c = 0;
-		for (int t = 0; t < T; t++)
-			c += sl[t].row_cur[i];
+		if (two_step)
+			c = scan->row_first[i + 1] - scan->row_first[i];
+		else
+			for (int t = 0; t < T; t++)
+				c += sl[t].row_cur[i];
 		row_count[i] = c;
 	}
 	for (int j = 0; j < items; j++) {
@@ -319,7 +406,7 @@ int mf_pattern_build_scan(mf_pattern *p, int users, int items, int nnz,
 		const int i = p->row_id[r];
 		p->row_ptr[r + 1] = p->row_ptr[r] + row_count[i];
 		int at = p->row_ptr[r];
-		for (int t = 0; t < T; t++) {
+		for (int t = 0; t < T && !two_step; t++) {
 			const int k = sl[t].row_cur[i];
 			sl[t].row_cur[i] = at;
 			at += k;
@@ -362,10 +449,49 @@ int mf_pattern_build_scan(mf_pattern *p, int users, int items, int nnz,
 		at += sl[t].local;
 	}
 	PREP_LAP("mask pointers");
-	run_slices(sl, T, prep_scatter);
-	PREP_LAP("scatter (threads)");
+	/* every entry matched (the sorted files of the reference): first_free by the threads of the
+	 * by-user step; users without entries (not among the stored rows) are set here */
+	const int fused_ff = two_step && matched == nnz;
+	if (fused_ff)
+		for (int i = 0; i < users; i++)
+			p->first_free[i] = (i >= user_lo && i < user_hi && items > 0) ? 0 : -1;
+	if (two_step) {
+		pos = malloc(sizeof *pos * (size_t)(n_hi - n_lo + 1));
+		if (!pos) {
+			rc = MFGPU_ENOMEM;
+			goto done;
+		}
+		for (int t = 0; t < T; t++) {
+			sl[t].pos = pos;
+			sl[t].first_free_here = fused_ff;
+			sl[t].n_base = n_lo;
+			sl[t].row_first = scan->row_first;
+			/* stored rows by equal shares of the nonzeros */
+			const int want = (int)((long)local * t / T);
+			int a = 0, b = p->n_rows;
+			while (a < b) {                      /* first stored row that starts at or after `want` */
+				const int m = (a + b) / 2;
+				if (p->row_ptr[m] < want)
+					a = m + 1;
+				else
+					b = m;
+			}
+			sl[t].r0 = a;
+			if (t > 0)
+				sl[t - 1].r1 = a;
+		}
+		sl[0].r0 = 0;
+		sl[T - 1].r1 = p->n_rows;
+		run_slices(sl, T, prep_scatter_cols);
+		PREP_LAP("by item (threads)");
+		run_slices(sl, T, prep_fill_rows);
+		PREP_LAP("by user (threads)");
+	} else {
+		run_slices(sl, T, prep_scatter);
+		PREP_LAP("scatter (threads)");
+	}
 
-	for (int i = 0; i < users; i++) {
+	for (int i = 0; i < users && !fused_ff; i++) {
 		int f = -1;
 		if (i >= user_lo && i < user_hi) {
 			const int *m = p->mask_col + p->mask_ptr[i];
@@ -382,6 +508,7 @@ int mf_pattern_build_scan(mf_pattern *p, int users, int items, int nnz,
 	PREP_LAP("first_free");
 	rc = MFGPU_OK;
 done:
+	free(pos);
 	free(cur);
 	free(row_count);
 	free(col_count);

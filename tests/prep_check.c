@@ -66,6 +66,12 @@ int main(void)
 		}
 		if (trial % 3 == 2 && nnz > 10)
 			e[nnz / 2] = e[nnz / 2 - 1];
+		/* ... or columns out of order inside rows that still never decrease (the two-step build) */
+		if (trial % 4 == 0 && nnz > 10)
+			for (int a = 1; a + 1 < nnz; a += 7)
+				if (e[a].row == e[a + 1].row) {
+					mfgpu_entry t = e[a]; e[a] = e[a + 1]; e[a + 1] = t;
+				}
 		const int lo = trial % 2 ? users / 3 : 0, hi = trial % 2 ? users - users / 4 : users;
 		mf_pattern ref, got;
 		setenv("MFGPU_PREP_THREADS", "1", 1);
@@ -85,7 +91,7 @@ int main(void)
 			if (!compare(&ref, &got, users)) { printf("  (trial %d, %d threads)\n", trial, T); fails++; }
 			mf_pattern_free(&got);
 		}
-		if (mf_mask_prefix(users, items, nnz, e) < nnz && trial % 3 == 0) { printf("unexpected disorder\n"); fails++; }
+		if (mf_mask_prefix(users, items, nnz, e) < nnz && trial % 3 == 0 && trial % 4 != 0) { printf("unexpected disorder\n"); fails++; }
 		/* the one-pass scan (mf_scan_entries) against the passes it replaces, and the build from
 		 * its knowledge (only the slice of the shard's users is read) against the full build */
 		for (int T = 1; T <= 8; T += 7) {
