@@ -53,7 +53,8 @@ size_t mf_pattern_ws_bytes(int users, int items, int nnz, int user_lo, int user_
 {
 	size_t nu = (size_t)(user_hi - user_lo), n = (size_t)nnz, u = (size_t)users, it = (size_t)items;
 	size_t ints = nu + it + (nu + 1) + (it + 1) + 4 * n + (u + 1) + u;   /* ids, ptrs, col/row idx, epos, mask */
-	return ints * sizeof(int) + n * sizeof(double) + 16 * 64;
+	ints += n + 1;                                                       /* scratch of the two-step second pass */
+	return ints * sizeof(int) + n * sizeof(double) + 17 * 64;
 }
 
 /* Order `n_ids` ids by key[id] descending, ties by ascending id (counting sort). */
@@ -313,6 +314,7 @@ int mf_pattern_build_scan(mf_pattern *p, int users, int items, int nnz,
 	prep_slice sl[MF_PREP_MAX_THREADS];
 	int *cur = NULL;            /* threads 1..T-1: their per-row / per-column arrays */
 	int *pos = NULL;            /* pass 2 in two steps: by-item position of every entry of the slice */
+	int pos_heap = 0;
 	int *row_count = xcalloc((size_t)users, sizeof *row_count);
 	int *col_count = xcalloc((size_t)items, sizeof *col_count);
 	int *row_slot = xcalloc((size_t)users, sizeof *row_slot);
@@ -456,7 +458,14 @@ int mf_pattern_build_scan(mf_pattern *p, int users, int items, int nnz,
 		for (int i = 0; i < users; i++)
 			p->first_free[i] = (i >= user_lo && i < user_hi && items > 0) ? 0 : -1;
 	if (two_step) {
-		pos = malloc(sizeof *pos * (size_t)(n_hi - n_lo + 1));
+		/* from the workspace when there is room (page-locked and recycled between plans: no
+		 * page faults on 4 bytes per nonzero), else from the heap */
+		if (p->ws)
+			pos = palloc(p, (size_t)(n_hi - n_lo + 1), sizeof *pos, 0);
+		if (!pos) {
+			pos = malloc(sizeof *pos * (size_t)(n_hi - n_lo + 1));
+			pos_heap = 1;
+		}
 		if (!pos) {
 			rc = MFGPU_ENOMEM;
 			goto done;
@@ -508,7 +517,8 @@ int mf_pattern_build_scan(mf_pattern *p, int users, int items, int nnz,
 	PREP_LAP("first_free");
 	rc = MFGPU_OK;
 done:
-	free(pos);
+	if (pos_heap)
+		free(pos);
 	free(cur);
 	free(row_count);
 	free(col_count);
