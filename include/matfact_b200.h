@@ -211,8 +211,8 @@ int mfgpu_plan_timer_stop(mfgpu_plan *plan, float *ms);
  *                        (value, index) merge / by users / by shape (default: items >= 8 users)
  *   "xchg_fused"   1/0   N shards, split mode, (value, tag) exchange: the exchange inside the
  *                        accumulation kernel (k_acc_ll: columns | reduce | rows | unpack)
- *                        instead of a launch of its own (default 0: measured slower, DESIGN.md 5;
- *                        same bits either way, a rank may choose for itself)
+ *                        instead of a launch of its own (default 0, or MFGPU_XCHG_FUSED: measured
+ *                        slower; same bits either way, a rank may choose for itself)
  *   "comm_timeout_ms" n  device-side waits for a peer give up after n ms (default 30000, or
  *                        MFGPU_COMM_TIMEOUT_MS); the next sync then returns MFGPU_ECOMM
  *   "exchange"     N shards.  Rank mode (collective: every rank sets it at the same point):
